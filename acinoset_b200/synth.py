@@ -1,0 +1,92 @@
+"""Synthetic 6-camera fisheye scenes (SURVEY.md §8d generators).
+
+Data generation only: builds the inputs the tests and bench.py feed to the hot path
+(dense ``[frame*keypoint][camera]`` observation slots and the equivalent DeepLabCut-style
+DataFrame of src/lib/utils.py:77-151). Nothing here is on the product's compute path.
+"""
+import json
+import os
+import numpy as np
+
+# src/lib/misc.py:10-17 — the 20 body keypoints of get_markers('default') (lure excluded)
+MARKERS = [
+    'nose', 'r_eye', 'l_eye', 'neck_base', 'spine', 'tail_base', 'tail1', 'tail2',
+    'r_shoulder', 'r_front_knee', 'r_front_ankle', 'l_shoulder', 'l_front_knee', 'l_front_ankle',
+    'r_hip', 'r_back_knee', 'r_back_ankle', 'l_hip', 'l_back_knee', 'l_back_ankle',
+]
+
+_SCENE = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tests', 'golden', 'scene_6cam.json')
+
+
+def load_rig(path=None):
+    """Scene JSON in the reference's format (src/lib/utils.py:55-74) -> k(n,3,3) d(n,4,1) r(n,3,3) t(n,3,1)."""
+    with open(path or _SCENE) as f:
+        data = json.load(f)
+    cams = data['cameras']
+    k = np.array([c['k'] for c in cams], dtype=np.float64)
+    d = np.array([c['d'] for c in cams], dtype=np.float64)
+    r = np.array([c['r'] for c in cams], dtype=np.float64)
+    t = np.array([c['t'] for c in cams], dtype=np.float64)
+    return k, d, r, t, tuple(data['camera_resolution'])
+
+
+def _project_np(X, k, d, r, t):
+    # Kannala-Brandt projection, generator-side only (ground truth -> pixels)
+    Xc = X @ r.T + t.reshape(3)
+    a = Xc[:, 0] / Xc[:, 2]
+    b = Xc[:, 1] / Xc[:, 2]
+    rr = np.sqrt(a * a + b * b)
+    th = np.arctan(rr)
+    t2 = th * th
+    dd = d.reshape(-1)
+    thd = th * (1 + t2 * (dd[0] + t2 * (dd[1] + t2 * (dd[2] + t2 * dd[3]))))
+    s = np.where(rr > 1e-8, thd / np.maximum(rr, 1e-300), 1.0)
+    return np.stack([k[0, 0] * (a * s + k[0, 1] / k[0, 0] * b * s) + k[0, 2], k[1, 1] * b * s + k[1, 2]], axis=1)
+
+
+def make_rig_scene(n_frames, n_kpts=20, seed=0, noise_px=1.0, masked_frac=0.5, outlier_frac=0.0,
+                   outlier_px=50.0, rig=None, project=None):
+    """Ground-truth points uniform in the rig's common view volume x[-1,5] y[5,8] z[0,1] m,
+    projected into every camera, N(0, noise_px) pixel noise, likelihood ~ U(0,1) shifted so that
+    ``masked_frac`` of the slots fall at or below 0.5 (the bench's dlc_thresh).
+
+    Returns dict(uv (P,C,2) f64, lik (P,C) f64, gt (P,3), k,d,r,t) with P = n_frames*n_kpts and
+    point p = frame*n_kpts + keypoint."""
+    k, d, r, t, _ = rig if rig is not None else load_rig()
+    C = len(k)
+    rng = np.random.default_rng(seed)
+    P = n_frames * n_kpts
+    gt = np.empty((P, 3))
+    gt[:, 0] = rng.uniform(-1.0, 5.0, P)
+    gt[:, 1] = rng.uniform(5.0, 8.0, P)
+    gt[:, 2] = rng.uniform(0.0, 1.0, P)
+    uv = np.empty((P, C, 2))
+    proj = project or _project_np
+    for c in range(C):
+        uv[:, c, :] = proj(gt, k[c], d[c], r[c], t[c])
+    uv += rng.normal(0.0, noise_px, uv.shape)
+    if outlier_frac > 0:
+        out = rng.uniform(size=(P, C)) < outlier_frac
+        uv[out] += rng.normal(0.0, outlier_px, (int(out.sum()), 2))
+    u01 = rng.uniform(size=(P, C))
+    # likelihood > 0.5 with probability 1 - masked_frac
+    lik = np.where(u01 < masked_frac, 0.5 * u01 / max(masked_frac, 1e-12),
+                   0.5 + 0.5 * (u01 - masked_frac) / max(1 - masked_frac, 1e-12) + 1e-9)
+    lik = np.minimum(lik, 1.0)
+    return dict(uv=uv, lik=lik, gt=gt, k=k, d=d, r=r, t=t, n_frames=n_frames, n_kpts=n_kpts)
+
+
+def dense_to_df(uv, lik, n_kpts, first_frame=0, markers=None):
+    """Dense slots -> DataFrame[frame, camera, marker, x, y, likelihood], rows camera-major then
+    frame then marker, like load_dlc_points_as_df (src/lib/utils.py:139-147)."""
+    import pandas as pd
+    markers = markers or MARKERS[:n_kpts]
+    P, C = lik.shape
+    F = P // n_kpts
+    frame = np.repeat(np.arange(first_frame, first_frame + F), n_kpts)
+    marker = np.tile(np.array(markers, dtype=object), F)
+    dfs = []
+    for c in range(C):
+        dfs.append(pd.DataFrame({'frame': frame, 'camera': c, 'marker': marker,
+                                 'x': uv[:, c, 0], 'y': uv[:, c, 1], 'likelihood': lik[:, c]}))
+    return pd.concat(dfs, ignore_index=True)
