@@ -1,0 +1,210 @@
+// acino.cu — C ABI (include/acino_b200.h) over the sm_100a kernels. Single translation unit.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+#include "acino_common.cuh"
+#include "acino_tri.cuh"
+#include "acino_sba_points.cuh"
+#include "acino_sba_schur.cuh"
+
+namespace acino {
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+static inline unsigned grid_for(int64_t n, int block) { return (unsigned)((n + block - 1) / block); }
+
+// scoped device buffer for the host-pointer convenience entry points
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 1); }
+  template <class T> T* as() { return reinterpret_cast<T*>(p); }
+};
+}  // namespace acino
+using namespace acino;
+
+#define ARG_CHECK(cond, msg)                       \
+  do {                                             \
+    if (!(cond)) { set_error("invalid argument: %s", msg); return ACINO_EINVAL; } \
+  } while (0)
+
+extern "C" {
+
+const char* acino_last_error(void) { return g_err; }
+int acino_version(void) { return 100; }
+int acino_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) { cudaGetLastError(); return 0; }
+  if (e != cudaSuccess) { set_error("cudaGetDeviceCount: %s", cudaGetErrorString(e)); cudaGetLastError(); return ACINO_ECUDA; }
+  return n;
+}
+int acino_set_device(int device) { ACINO_CUDA(cudaSetDevice(device)); return ACINO_OK; }
+int acino_dev_alloc(void** out, int64_t bytes) {
+  ARG_CHECK(out && bytes >= 0, "dev_alloc");
+  ACINO_CUDA(cudaMalloc(out, bytes ? (size_t)bytes : 1));
+  return ACINO_OK;
+}
+int acino_dev_free(void* p) { ACINO_CUDA(cudaFree(p)); return ACINO_OK; }
+int acino_h2d(void* d, const void* s, int64_t bytes) { ACINO_CUDA(cudaMemcpy(d, s, (size_t)bytes, cudaMemcpyHostToDevice)); return ACINO_OK; }
+int acino_d2h(void* d, const void* s, int64_t bytes) { ACINO_CUDA(cudaMemcpy(d, s, (size_t)bytes, cudaMemcpyDeviceToHost)); return ACINO_OK; }
+int acino_sync(void) { ACINO_CUDA(cudaDeviceSynchronize()); return ACINO_OK; }
+
+// ---------------------------------------------------------------- K1 projection / residuals
+int acino_project_dev(const double* X_dev, int64_t N, const double* cam24_host, double* uv_dev, void* stream) {
+  ARG_CHECK(N >= 0 && cam24_host && (N == 0 || (X_dev && uv_dev)), "project_dev");
+  if (N == 0) return ACINO_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  DevBuf cam;
+  ACINO_CUDA(cam.alloc(CAM_STRIDE * sizeof(double)));
+  ACINO_CUDA(cudaMemcpyAsync(cam.p, cam24_host, CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice, st));
+  project_kernel<<<grid_for(N, 256), 256, 0, st>>>(X_dev, N, cam.as<double>(), (double2*)uv_dev);
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaStreamSynchronize(st));
+  return ACINO_OK;
+}
+
+int acino_project(const double* X, int64_t N, const double* cam24, double* uv) {
+  ARG_CHECK(N >= 0 && cam24 && (N == 0 || (X && uv)), "project");
+  if (N == 0) return ACINO_OK;
+  DevBuf dX, dUV;
+  ACINO_CUDA(dX.alloc(N * 3 * sizeof(double)));
+  ACINO_CUDA(dUV.alloc(N * 2 * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(dX.p, X, N * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  int rc = acino_project_dev(dX.as<double>(), N, cam24, dUV.as<double>(), nullptr);
+  if (rc) return rc;
+  ACINO_CUDA(cudaMemcpy(uv, dUV.p, N * 2 * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
+int acino_residuals_list(const double* X, int64_t n_points, const int32_t* point_idx, const int32_t* cam_idx,
+                         const double* points_2d, int64_t n_obs, const double* cams24, int n_cams, double* f) {
+  ARG_CHECK(n_points >= 0 && n_obs >= 0 && n_cams > 0 && n_cams <= 64 && cams24, "residuals_list");
+  if (n_obs == 0) return ACINO_OK;
+  ARG_CHECK(X && point_idx && cam_idx && points_2d && f, "residuals_list null pointer");
+  for (int64_t o = 0; o < n_obs; ++o) {
+    if (point_idx[o] < 0 || point_idx[o] >= n_points || cam_idx[o] < 0 || cam_idx[o] >= n_cams) {
+      set_error("residuals_list: observation %lld has point %d / camera %d out of range", (long long)o, point_idx[o], cam_idx[o]);
+      return ACINO_EINVAL;
+    }
+  }
+  DevBuf dX, dP, dC, dO, dF, dCam;
+  ACINO_CUDA(dX.alloc(n_points * 3 * sizeof(double)));
+  ACINO_CUDA(dP.alloc(n_obs * sizeof(int32_t)));
+  ACINO_CUDA(dC.alloc(n_obs * sizeof(int32_t)));
+  ACINO_CUDA(dO.alloc(n_obs * 2 * sizeof(double)));
+  ACINO_CUDA(dF.alloc(n_obs * 2 * sizeof(double)));
+  ACINO_CUDA(dCam.alloc(n_cams * CAM_STRIDE * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(dX.p, X, n_points * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dP.p, point_idx, n_obs * sizeof(int32_t), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dC.p, cam_idx, n_obs * sizeof(int32_t), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dO.p, points_2d, n_obs * 2 * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dCam.p, cams24, n_cams * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  residuals_list_kernel<<<grid_for(n_obs, 256), 256, n_cams * CAM_STRIDE * sizeof(double)>>>(
+      dX.as<double>(), dP.as<int32_t>(), dC.as<int32_t>(), dO.as<double2>(), n_obs, dCam.as<double>(), n_cams, dF.as<double2>());
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaMemcpy(f, dF.p, n_obs * 2 * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
+__global__ void rodrigues_kernel(const double* rv, int n, double* R) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) rodrigues(rv + 3 * i, R + 9 * i);
+}
+int acino_rodrigues(const double* rvecs, int n, double* R_out) {
+  ARG_CHECK(n >= 0 && (n == 0 || (rvecs && R_out)), "rodrigues");
+  if (n == 0) return ACINO_OK;
+  DevBuf dv, dR;
+  ACINO_CUDA(dv.alloc(n * 3 * sizeof(double)));
+  ACINO_CUDA(dR.alloc(n * 9 * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(dv.p, rvecs, n * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  rodrigues_kernel<<<grid_for(n, 64), 64>>>(dv.as<double>(), n, dR.as<double>());
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaMemcpy(R_out, dR.p, n * 9 * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
+// ---------------------------------------------------------------- K2 triangulation
+int acino_triangulate_pair(const double* uv1, const double* uv2, int64_t M, const double* cam24_a,
+                           const double* cam24_b, double* xyz) {
+  ARG_CHECK(M >= 0 && cam24_a && cam24_b && (M == 0 || (uv1 && uv2 && xyz)), "triangulate_pair");
+  if (M == 0) return ACINO_OK;
+  DevBuf d1, d2, dX, dCam;
+  ACINO_CUDA(d1.alloc(M * 2 * sizeof(double)));
+  ACINO_CUDA(d2.alloc(M * 2 * sizeof(double)));
+  ACINO_CUDA(dX.alloc(M * 3 * sizeof(double)));
+  ACINO_CUDA(dCam.alloc(2 * CAM_STRIDE * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(d1.p, uv1, M * 2 * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(d2.p, uv2, M * 2 * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dCam.p, cam24_a, CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dCam.as<double>() + CAM_STRIDE, cam24_b, CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  tri_pair_kernel<<<grid_for(M, 128), 128>>>(d1.as<double2>(), d2.as<double2>(), M, dCam.as<double>(), dX.as<double>());
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaMemcpy(xyz, dX.p, M * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
+}  // extern "C"
+template <int C>
+static void launch_tri_ring(const double* uv, const double* lik, double thresh, int64_t P, const double* cams,
+                            double* xyz, uint8_t* mask, uint8_t* exists, cudaStream_t st) {
+  tri_ring_kernel<C><<<grid_for(P, 128), 128, 0, st>>>((const double2*)uv, lik, thresh, P, cams, xyz, mask, exists);
+}
+extern "C" {
+
+int acino_triangulate_ring_dev(const double* uv_dev, const double* lik_dev, double thresh, int64_t P, int C,
+                               const double* cams24_host, double* xyz_dev, uint8_t* obs_mask_dev,
+                               uint8_t* exists_dev, void* stream) {
+  ARG_CHECK(P >= 0 && C >= 2 && C <= MAX_CAMS && cams24_host, "triangulate_ring_dev (2 <= C <= 8)");
+  if (P == 0) return ACINO_OK;
+  ARG_CHECK(uv_dev && lik_dev && xyz_dev && obs_mask_dev && exists_dev, "triangulate_ring_dev null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  DevBuf cam;
+  ACINO_CUDA(cam.alloc(C * CAM_STRIDE * sizeof(double)));
+  ACINO_CUDA(cudaMemcpyAsync(cam.p, cams24_host, C * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice, st));
+  const double* dc = cam.as<double>();
+  switch (C) {
+    case 2: launch_tri_ring<2>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;
+    case 3: launch_tri_ring<3>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;
+    case 4: launch_tri_ring<4>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;
+    case 5: launch_tri_ring<5>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;
+    case 6: launch_tri_ring<6>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;
+    case 7: launch_tri_ring<7>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;
+    default: launch_tri_ring<8>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;
+  }
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaStreamSynchronize(st));
+  return ACINO_OK;
+}
+
+int acino_triangulate_ring(const double* uv, const double* lik, double thresh, int64_t P, int C,
+                           const double* cams24, double* xyz, uint8_t* obs_mask, uint8_t* exists) {
+  ARG_CHECK(P >= 0 && C >= 2 && C <= MAX_CAMS && cams24, "triangulate_ring (2 <= C <= 8)");
+  if (P == 0) return ACINO_OK;
+  ARG_CHECK(uv && lik && xyz && obs_mask && exists, "triangulate_ring null pointer");
+  DevBuf dUV, dL, dX, dM, dE;
+  ACINO_CUDA(dUV.alloc(P * C * 2 * sizeof(double)));
+  ACINO_CUDA(dL.alloc(P * C * sizeof(double)));
+  ACINO_CUDA(dX.alloc(P * 3 * sizeof(double)));
+  ACINO_CUDA(dM.alloc(P));
+  ACINO_CUDA(dE.alloc(P));
+  ACINO_CUDA(cudaMemcpy(dUV.p, uv, P * C * 2 * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dL.p, lik, P * C * sizeof(double), cudaMemcpyHostToDevice));
+  int rc = acino_triangulate_ring_dev(dUV.as<double>(), dL.as<double>(), thresh, P, C, cams24, dX.as<double>(),
+                                      dM.as<uint8_t>(), dE.as<uint8_t>(), nullptr);
+  if (rc) return rc;
+  ACINO_CUDA(cudaMemcpy(xyz, dX.p, P * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+  ACINO_CUDA(cudaMemcpy(obs_mask, dM.p, P, cudaMemcpyDeviceToHost));
+  ACINO_CUDA(cudaMemcpy(exists, dE.p, P, cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
+}  // extern "C"
+
+#include "acino_sba_api.inl"

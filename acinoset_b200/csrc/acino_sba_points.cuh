@@ -1,0 +1,237 @@
+// acino_sba_points.cuh — K1 (dense residuals) and K3 (points-only robust LM).
+// Replaces cost_func_points_only (src/lib/sba.py:149-153) and the scipy least_squares call of
+// bundle_adjust_points_only (src/lib/sba.py:181-195). With cameras fixed the normal matrix is
+// block-diagonal, one 3x3 block per point, so every point is an independent
+// 3-parameter Cauchy-robust problem: one thread owns one point, keeps its <=C observations, the
+// 3x3 block, the gradient and the damping in registers, and runs LM iterations without touching HBM.
+#pragma once
+#include "acino_common.cuh"
+
+namespace acino {
+
+struct NormalEq {
+  double F;       // robust cost of this point: 0.5 C^2 log(prod(1+z))
+  double g[3];    // J^T rho' f
+  double V[6];    // xx xy xz yy yz zz
+};
+
+// residual + Jacobian + normal equations of one point over its observed cameras
+// uvr: this thread's observations in shared memory, camera c at uvr[c * stride]
+template <int C>
+__device__ __forceinline__ void eval_point(const double* __restrict__ sc, const double2* uvr, int stride, unsigned m,
+                                           double X, double Y, double Z, double inv_c2, double half_c2,
+                                           NormalEq& ne) {
+  double pm1 = 0.0;
+  double g0 = 0, g1 = 0, g2 = 0, v0 = 0, v1 = 0, v2 = 0, v3 = 0, v4 = 0, v5 = 0;
+#pragma unroll 1
+  for (int c = 0; c < C; ++c) {
+    if (m >> c & 1) {
+      const double* cam = sc + c * CAM_STRIDE;
+      double x, y, z, u, v, Ju[3], Jv[3], ju[3], jv[3];
+      to_camera(cam, X, Y, Z, x, y, z);
+      fisheye_uv_jac(cam, x, y, z, u, v, Ju, Jv);
+      mul_R(cam, Ju, ju);
+      mul_R(cam, Jv, jv);
+      double2 ob = uvr[c * stride];
+      double fu = u - ob.x, fv = v - ob.y;
+      Robust w = cauchy_weights(fu, fv, inv_c2, pm1);
+      double gu = w.gu * fu, gv = w.gv * fv;
+      g0 = fma(ju[0], gu, fma(jv[0], gv, g0));
+      g1 = fma(ju[1], gu, fma(jv[1], gv, g1));
+      g2 = fma(ju[2], gu, fma(jv[2], gv, g2));
+      double a0 = w.hu * ju[0], a1 = w.hu * ju[1], a2 = w.hu * ju[2];
+      double b0 = w.hv * jv[0], b1 = w.hv * jv[1], b2 = w.hv * jv[2];
+      v0 = fma(a0, ju[0], fma(b0, jv[0], v0));
+      v1 = fma(a0, ju[1], fma(b0, jv[1], v1));
+      v2 = fma(a0, ju[2], fma(b0, jv[2], v2));
+      v3 = fma(a1, ju[1], fma(b1, jv[1], v3));
+      v4 = fma(a1, ju[2], fma(b1, jv[2], v4));
+      v5 = fma(a2, ju[2], fma(b2, jv[2], v5));
+    }
+  }
+  ne.F = half_c2 * log1p(pm1);
+  ne.g[0] = g0; ne.g[1] = g1; ne.g[2] = g2;
+  ne.V[0] = v0; ne.V[1] = v1; ne.V[2] = v2; ne.V[3] = v3; ne.V[4] = v4; ne.V[5] = v5;
+}
+
+// solve (V + lam*D) d = -g by LDL^T, D = diag(V) floored; returns predicted reduction of the model
+__device__ __forceinline__ double lm_step3(const NormalEq& ne, double lam, double* d) {
+  double dmax = fmax(ne.V[0], fmax(ne.V[3], ne.V[5]));
+  double flo = fmax(1e-9 * dmax, 1e-300);
+  double D0 = fmax(ne.V[0], flo), D1 = fmax(ne.V[3], flo), D2 = fmax(ne.V[5], flo);
+  double a = fma(lam, D0, ne.V[0]), b = ne.V[1], c = ne.V[2];
+  double dd = fma(lam, D1, ne.V[3]), e = ne.V[4], f = fma(lam, D2, ne.V[5]);
+  double ia = 1.0 / a;
+  double l10 = b * ia, l20 = c * ia;
+  double d1 = fma(-l10, b, dd);
+  double e1 = fma(-l20, b, e);
+  double id1 = 1.0 / d1;
+  double l21 = e1 * id1;
+  double f2 = fma(-l21, e1, fma(-l20, c, f));
+  double if2 = 1.0 / f2;
+  double y0 = -ne.g[0];
+  double y1 = fma(-l10, y0, -ne.g[1]);
+  double y2 = fma(-l21, y1, fma(-l20, y0, -ne.g[2]));
+  double x2 = y2 * if2;
+  double x1 = fma(-l21, x2, y1 * id1);
+  double x0 = fma(-l20, x2, fma(-l10, x1, y0 * ia));
+  d[0] = x0; d[1] = x1; d[2] = x2;
+  double gd = ne.g[0] * x0 + ne.g[1] * x1 + ne.g[2] * x2;
+  double dDd = D0 * x0 * x0 + D1 * x1 * x1 + D2 * x2 * x2;
+  return 0.5 * (lam * dDd - gd);
+}
+
+#define ST_ACTIVE 0
+#define ST_CONVERGED 1
+#define ST_STALLED 2
+
+struct LmParams {
+  double inv_c2, half_c2, gtol, xtol, lambda0;
+  int inner_iters, force;
+};
+
+// One launch = up to inner_iters LM iterations of every active point. cost_p[p] = robust cost of the
+// point at exit; counters[0] += points still active at exit.
+template <int C>
+__global__ void __launch_bounds__(128)
+lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
+                 const double* __restrict__ cams, double* __restrict__ Xp, double* __restrict__ lam_p,
+                 double* __restrict__ cost_p, uint8_t* __restrict__ status, LmParams prm,
+                 unsigned long long* __restrict__ counters) {
+  __shared__ double sc[C * CAM_STRIDE];
+  __shared__ double2 s_uv[C * 128];
+  for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[i] = cams[i];
+  __syncthreads();
+  int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double2* uvr = s_uv + threadIdx.x;
+  unsigned still = 0;
+  if (p < P) {
+    unsigned m = obs_mask[p];
+    uint8_t st = status[p];
+    if (m != 0 && (st == ST_ACTIVE || prm.force)) {
+#pragma unroll
+      for (int c = 0; c < C; ++c)
+        if (m >> c & 1) uvr[c * 128] = uv[p * C + c];
+      double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
+      double lam = lam_p[p];
+      if (!(lam > 0.0)) lam = prm.lambda0;
+      NormalEq ne;
+      eval_point<C>(sc, uvr, 128, m, X, Y, Z, prm.inv_c2, prm.half_c2, ne);
+      double nu = 2.0;
+      st = ST_ACTIVE;
+#pragma unroll 1
+      for (int it = 0; it < prm.inner_iters; ++it) {
+        double gmax = fmax(fabs(ne.g[0]), fmax(fabs(ne.g[1]), fabs(ne.g[2])));
+        if (!prm.force && !(gmax > prm.gtol)) { st = ST_CONVERGED; break; }
+        double d[3];
+        double pred = lm_step3(ne, lam, d);
+        NormalEq nt;
+        eval_point<C>(sc, uvr, 128, m, X + d[0], Y + d[1], Z + d[2], prm.inv_c2, prm.half_c2, nt);
+        double act = ne.F - nt.F;
+        if (act > 0.0 && pred > 0.0) {          // NaN-safe: comparisons fail on a non-finite trial cost
+          double rho = act / pred;
+          double q = 2.0 * rho - 1.0;
+          lam *= fmax(1.0 / 3.0, 1.0 - q * q * q);
+          lam = fmax(lam, 1e-12);
+          nu = 2.0;
+          double dmax = fmax(fabs(d[0]), fmax(fabs(d[1]), fabs(d[2])));
+          double xmax = fmax(fabs(X), fmax(fabs(Y), fabs(Z)));
+          X += d[0]; Y += d[1]; Z += d[2];
+          ne = nt;
+          if (!prm.force && dmax <= prm.xtol * (xmax + prm.xtol)) { st = ST_CONVERGED; break; }
+        } else {
+          lam *= nu;
+          nu *= 2.0;
+          if (lam > 1e16) {                      // no descent left at fp64 resolution
+            if (!prm.force) { st = ST_STALLED; break; }
+            lam = 1e16;
+          }
+        }
+      }
+      Xp[3 * p] = X; Xp[3 * p + 1] = Y; Xp[3 * p + 2] = Z;
+      lam_p[p] = lam;
+      cost_p[p] = ne.F;
+      status[p] = st;
+      still = (st == ST_ACTIVE);
+    }
+  }
+  unsigned cnt = __popc(__ballot_sync(0xffffffffu, still));
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&counters[0], (unsigned long long)cnt);
+}
+
+// deterministic two-stage sum of a double array (scene cost)
+__global__ void __launch_bounds__(256) sum_kernel(const double* __restrict__ x, int64_t n, double* __restrict__ partial) {
+  __shared__ double red[8];
+  double s = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) s += x[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    partial[blockIdx.x] = t;
+  }
+}
+
+// K1 dense: f[p][c] = proj - obs for every observed slot, 0 elsewhere (cost_func_points_only in slot order)
+template <int C>
+__global__ void __launch_bounds__(256)
+residuals_dense_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
+                       const double* __restrict__ cams, const double* __restrict__ Xp, double2* __restrict__ f) {
+  __shared__ double sc[C * CAM_STRIDE];
+  for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[i] = cams[i];
+  __syncthreads();
+  int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  unsigned m = obs_mask[p];
+  double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    double2 r = make_double2(0.0, 0.0);
+    if (m >> c & 1) {
+      double x, y, z, u, v;
+      to_camera(sc + c * CAM_STRIDE, X, Y, Z, x, y, z);
+      fisheye_uv(sc + c * CAM_STRIDE, x, y, z, u, v);
+      double2 o = uv[p * C + c];
+      r.x = u - o.x; r.y = v - o.y;
+    }
+    f[p * C + c] = r;
+  }
+}
+
+// K1 list form: one thread per observation (cost_func_points_only / _extrinsics ordering)
+__global__ void __launch_bounds__(256)
+residuals_list_kernel(const double* __restrict__ Xp, const int32_t* __restrict__ pidx, const int32_t* __restrict__ cidx,
+                      const double2* __restrict__ obs, int64_t n_obs, const double* __restrict__ cams, int n_cams,
+                      double2* __restrict__ f) {
+  extern __shared__ double sc[];
+  for (int i = threadIdx.x; i < n_cams * CAM_STRIDE; i += blockDim.x) sc[i] = cams[i];
+  __syncthreads();
+  int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= n_obs) return;
+  int64_t p = pidx[o];
+  const double* cam = sc + cidx[o] * CAM_STRIDE;
+  double x, y, z, u, v;
+  to_camera(cam, Xp[3 * p], Xp[3 * p + 1], Xp[3 * p + 2], x, y, z);
+  fisheye_uv(cam, x, y, z, u, v);
+  double2 q = obs[o];
+  f[o] = make_double2(u - q.x, v - q.y);
+}
+
+// K1 plain projection of N points into one camera (project_points_fisheye)
+__global__ void __launch_bounds__(256)
+project_kernel(const double* __restrict__ Xp, int64_t N, const double* __restrict__ cam, double2* __restrict__ uv) {
+  __shared__ double sc[CAM_STRIDE];
+  if (threadIdx.x < CAM_STRIDE) sc[threadIdx.x] = cam[threadIdx.x];
+  __syncthreads();
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  double x, y, z, u, v;
+  to_camera(sc, Xp[3 * i], Xp[3 * i + 1], Xp[3 * i + 2], x, y, z);
+  fisheye_uv(sc, x, y, z, u, v);
+  uv[i] = make_double2(u, v);
+}
+
+}  // namespace acino

@@ -1,0 +1,172 @@
+"""Dense-slot entry points: the array layout the CUDA kernels consume.
+
+Point p = (frame, keypoint); slot (p, c) = camera c's observation of it. ``uv`` is (P, C, 2) float64,
+``lik`` (P, C) float64 likelihoods, ``obs_mask`` (P,) uint8 bitmask. These are what the DataFrame / list
+front-ends in utils.py and sba.py lower to, and what bench.py drives directly at full scale.
+"""
+import ctypes as ct
+import numpy as np
+from . import _capi
+from ._capi import SbaOpts, SbaStats, MODE_POINTS_ONLY, MODE_POINTS_AND_EXTRINSICS
+
+
+def triangulate_ring(uv, lik, thresh, k_arr, d_arr, r_arr, t_arr):
+    """Ring-pair DLT of src/lib/utils.py:319-349 fused with `likelihood > thresh` (src/core/tri.py:41).
+    Returns xyz (P,3) (NaN where absent), exists (P,) bool, obs_mask (P,) uint8."""
+    _capi.require_gpu()
+    uv = _capi.f64(uv)
+    P, C = uv.shape[0], uv.shape[1]
+    lik = _capi.f64(lik).reshape(P, C)
+    cams = _capi.pack_cams(k_arr, d_arr, r_arr, t_arr)
+    xyz = np.empty((P, 3))
+    mask = np.empty(P, dtype=np.uint8)
+    exists = np.empty(P, dtype=np.uint8)
+    _capi.check(_capi.lib().acino_triangulate_ring(_capi.ptr(uv), _capi.ptr(lik), float(thresh), P, C, _capi.ptr(cams),
+                                                   _capi.ptr(xyz), _capi.ptr(mask), _capi.ptr(exists)))
+    return xyz, exists.astype(bool), mask
+
+
+class DeviceArray:
+    """A caller-owned HBM buffer (acino_dev_alloc) with numpy upload / download."""
+
+    def __init__(self, shape, dtype):
+        self.shape = tuple(int(s) for s in np.atleast_1d(shape))
+        self.dtype = np.dtype(dtype)
+        self.nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        p = ct.c_void_p()
+        _capi.check(_capi.lib().acino_dev_alloc(ct.byref(p), self.nbytes))
+        self.ptr = p
+
+    @classmethod
+    def from_host(cls, a):
+        a = np.ascontiguousarray(a)
+        d = cls(a.shape, a.dtype)
+        d.upload(a)
+        return d
+
+    def upload(self, a):
+        a = np.ascontiguousarray(a, dtype=self.dtype)
+        assert a.nbytes == self.nbytes
+        _capi.check(_capi.lib().acino_h2d(self.ptr, _capi.ptr(a), self.nbytes))
+
+    def download(self, out=None):
+        if out is None:
+            out = np.empty(self.shape, dtype=self.dtype)
+        _capi.check(_capi.lib().acino_d2h(_capi.ptr(out), self.ptr, self.nbytes))
+        return out
+
+    def free(self):
+        if self.ptr is not None and self.ptr.value:
+            _capi.lib().acino_dev_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def default_opts(mode=MODE_POINTS_ONLY, **kw):
+    o = SbaOpts()
+    _capi.lib().acino_sba_default_opts(ct.byref(o), mode)
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise TypeError(f'unknown solver option {k}')
+        setattr(o, k, v)
+    return o
+
+
+class SbaSolver:
+    """One solver handle = one GPU = one stream (include/acino_b200.h: acino_sba_*)."""
+
+    def __init__(self, n_cams, n_points):
+        _capi.require_gpu()
+        self.C, self.P = int(n_cams), int(n_points)
+        self._h = _capi.lib().acino_sba_create(self.C, self.P)
+        if not self._h:
+            raise _capi.AcinoError('acino_sba_create: ' + _capi.lib().acino_last_error().decode())
+        self._keep = []
+
+    def close(self):
+        if self._h:
+            _capi.lib().acino_sba_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_cameras(self, k_arr, d_arr, r_arr, t_arr):
+        cams = _capi.pack_cams(k_arr, d_arr, r_arr, t_arr)
+        assert cams.shape[0] == self.C
+        _capi.check(_capi.lib().acino_sba_set_cameras(self._h, _capi.ptr(cams)))
+
+    def set_observations(self, uv, obs_mask):
+        uv = _capi.f64(uv).reshape(self.P, self.C, 2)
+        m = np.ascontiguousarray(obs_mask, dtype=np.uint8).reshape(self.P)
+        _capi.check(_capi.lib().acino_sba_set_observations(self._h, _capi.ptr(uv), _capi.ptr(m)))
+
+    def set_observations_dev(self, uv_dev: DeviceArray, mask_dev: DeviceArray):
+        self._keep = [uv_dev, mask_dev]
+        _capi.check(_capi.lib().acino_sba_set_observations_dev(self._h, uv_dev.ptr, mask_dev.ptr))
+
+    def set_points(self, xyz):
+        x = _capi.f64(xyz).reshape(self.P, 3)
+        _capi.check(_capi.lib().acino_sba_set_points(self._h, _capi.ptr(x)))
+
+    def set_points_dev(self, xyz_dev: DeviceArray):
+        _capi.check(_capi.lib().acino_sba_set_points_dev(self._h, xyz_dev.ptr))
+
+    def set_rvec_t(self, rvecs, tvecs):
+        rv = _capi.f64(rvecs).reshape(self.C, 3)
+        tv = _capi.f64(tvecs).reshape(self.C, 3)
+        _capi.check(_capi.lib().acino_sba_set_rvec_t(self._h, _capi.ptr(rv), _capi.ptr(tv)))
+
+    def get_rvec_t(self):
+        rv = np.empty((self.C, 3)); tv = np.empty((self.C, 3))
+        _capi.check(_capi.lib().acino_sba_get_rvec_t(self._h, _capi.ptr(rv), _capi.ptr(tv)))
+        return rv, tv
+
+    def get_points(self):
+        x = np.empty((self.P, 3))
+        _capi.check(_capi.lib().acino_sba_get_points(self._h, _capi.ptr(x)))
+        return x
+
+    def get_cameras(self):
+        c = np.empty((self.C, _capi.CAM_STRIDE))
+        _capi.check(_capi.lib().acino_sba_get_cameras(self._h, _capi.ptr(c)))
+        return c
+
+    def residuals(self):
+        f = np.empty((self.P, self.C, 2))
+        _capi.check(_capi.lib().acino_sba_residuals(self._h, _capi.ptr(f)))
+        return f
+
+    def reset_state(self):
+        _capi.check(_capi.lib().acino_sba_reset_state(self._h))
+
+    def solve(self, opts=None, **kw):
+        o = opts or default_opts(**kw)
+        st = SbaStats()
+        _capi.check(_capi.lib().acino_sba_solve(self._h, ct.byref(o), ct.byref(st)))
+        return st.as_dict()
+
+    def iterate(self, opts):
+        _capi.check(_capi.lib().acino_sba_iterate(self._h, ct.byref(opts)))
+
+    @property
+    def stream(self):
+        return _capi.lib().acino_sba_stream(self._h)
+
+    def comm_init(self, unique_id: bytes, rank: int, nranks: int):
+        buf = ct.create_string_buffer(unique_id, 128)
+        _capi.check(_capi.lib().acino_sba_comm_init(self._h, buf, rank, nranks))
+
+
+def nccl_unique_id() -> bytes:
+    buf = ct.create_string_buffer(128)
+    _capi.check(_capi.lib().acino_nccl_unique_id(buf))
+    return buf.raw

@@ -1,0 +1,130 @@
+/* acino_b200 — C ABI of the B200-native AcinoSet TRI + SBA hot path.
+ *
+ * The reference (DenDen047/AcinoSet) has no FFI: its seam is Python function injection
+ * (src/lib/app.py:123-138 passes triangulate_func / project_func into src/lib/sba.py and
+ * src/lib/utils.py). Each entry point below names the reference function whose arithmetic it
+ * replaces; acinoset_b200/{calib,utils,sba}.py bind them with ctypes behind the reference's own
+ * signatures. Plain pointers and sizes only; every function returns 0 on success or a negative
+ * ACINO_E* code (message via acino_last_error()); nothing throws or exits.
+ *
+ * Camera block ("cam24"): 24 doubles per camera
+ *   [0] fx [1] fy [2] cx [3] cy [4] alpha=K01/K00 [5..8] k1..k4 [9..17] R row-major (world->camera)
+ *   [18..20] t [21..23] reserved (0)            (scene arrays of src/lib/utils.py:55-74)
+ * Dense observation store: point p = (frame, keypoint); slot (p, c) holds camera c's pixel:
+ *   uv   double[P][C][2]      obs_mask uint8[P]  (bit c set <=> slot (p,c) is an observation)
+ * All arithmetic is fp64. Pointers named *_dev are device pointers on the current CUDA device.
+ */
+#ifndef ACINO_B200_H
+#define ACINO_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ACINO_CAM_STRIDE 24
+#define ACINO_MAX_CAMS 8
+
+#define ACINO_OK 0
+#define ACINO_EINVAL (-1)   /* bad argument */
+#define ACINO_ECUDA (-2)    /* CUDA runtime error (no device, launch failure, OOM) */
+#define ACINO_ESTATE (-3)   /* call order violated (e.g. solve before set_observations) */
+#define ACINO_ENCCL (-4)    /* NCCL unavailable or failed */
+
+const char* acino_last_error(void);
+int acino_version(void);
+int acino_device_count(void);           /* <0 on error, 0 when no CUDA device is visible */
+int acino_set_device(int device);
+
+/* device memory helpers so that a ctypes host can keep inputs resident in HBM */
+int acino_dev_alloc(void** out_dev, int64_t bytes);
+int acino_dev_free(void* dev);
+int acino_h2d(void* dst_dev, const void* src_host, int64_t bytes);
+int acino_d2h(void* dst_host, const void* src_dev, int64_t bytes);
+int acino_sync(void);
+
+/* K1 — project_points_fisheye, src/lib/calib.py:132-136 (cv::fisheye::projectPoints).
+ * X double[N][3] -> uv double[N][2]. Host pointers. */
+int acino_project(const double* X, int64_t N, const double* cam24, double* uv);
+int acino_project_dev(const double* X_dev, int64_t N, const double* cam24_host, double* uv_dev, void* stream);
+
+/* K1 — cost_func_points_only / cost_func_points_extrinsics, src/lib/sba.py:142-153, on observation
+ * lists: f[2*o], f[2*o+1] = proj(X[point_idx[o]], cam cam_idx[o]) - points_2d[o]. Host pointers. */
+int acino_residuals_list(const double* X, int64_t n_points, const int32_t* point_idx, const int32_t* cam_idx,
+                         const double* points_2d, int64_t n_obs, const double* cams24, int n_cams, double* f);
+
+/* cv::Rodrigues(rvec)->R for n vectors (src/lib/sba.py:29), the device routine the extrinsics solver uses. */
+int acino_rodrigues(const double* rvecs, int n, double* R_out);
+
+/* K2 — triangulate_points_fisheye, src/lib/calib.py:120-129: fisheye undistort (Newton, <=10 steps,
+ * eps 1e-8) of both pixels, 4x4 homogeneous DLT with P=[R|t], dehomogenise. uv1, uv2 double[M][2]. */
+int acino_triangulate_pair(const double* uv1, const double* uv2, int64_t M, const double* cam24_a,
+                           const double* cam24_b, double* xyz);
+
+/* K2 — get_pairwise_3d_points_from_df, src/lib/utils.py:319-349, fused with the caller's
+ * `likelihood > dlc_thresh` (src/core/tri.py:41, strict >): ring pairs (c,(c+1)%C), unweighted mean of
+ * the pair estimates; a point exists iff some ring pair has both views. Outputs xyz double[P][3]
+ * (NaN when absent), exists uint8[P], and obs_mask uint8[P] = thresholded slots of existing points (0 for
+ * absent points): exactly the observations the inner merge at src/lib/sba.py:299 hands to SBA. */
+int acino_triangulate_ring(const double* uv, const double* lik, double thresh, int64_t P, int C,
+                           const double* cams24, double* xyz, uint8_t* obs_mask, uint8_t* exists);
+int acino_triangulate_ring_dev(const double* uv_dev, const double* lik_dev, double thresh, int64_t P, int C,
+                               const double* cams24_host, double* xyz_dev, uint8_t* obs_mask_dev,
+                               uint8_t* exists_dev, void* stream);
+
+/* ---- SBA solver handle: bundle_adjust_points_only (src/lib/sba.py:181-195) and
+ * bundle_adjust_points_and_extrinsics (src/lib/sba.py:158-178) ---- */
+typedef struct acino_sba acino_sba_t;
+
+#define ACINO_MODE_POINTS_ONLY 0
+#define ACINO_MODE_POINTS_AND_EXTRINSICS 1
+
+typedef struct {
+  int32_t mode;            /* ACINO_MODE_* */
+  int32_t max_iter;        /* LM iterations (per point in points-only mode) */
+  int32_t inner_iters;     /* points-only: LM iterations fused into one kernel launch (>=1) */
+  int32_t force_iters;     /* !=0: never early-out on convergence (fixed work per iteration; bench) */
+  double f_scale;          /* Cauchy scale C: cost = 0.5*C^2*sum(log1p((f/C)^2)), src/lib/sba.py:181 */
+  double gtol;             /* stop when max|g| <= gtol */
+  double xtol;             /* stop when an accepted step has max|dx| <= xtol*(max|x|+xtol) */
+  double lambda0;          /* initial Marquardt damping */
+  double reserved[4];
+} acino_sba_opts;
+
+typedef struct {
+  int64_t n_points, n_obs;
+  int64_t n_unconverged;   /* points (points-only) / 0-1 (extrinsics) not converged at exit */
+  int32_t iterations;      /* LM iterations executed (sweeps) */
+  int32_t launches;        /* CUDA kernel launches issued by the solve */
+  double cost_initial, cost_final;   /* scipy-convention robust cost */
+  double solve_ms;         /* device time of the solve (CUDA events) */
+  double reserved[4];
+} acino_sba_stats;
+
+void acino_sba_default_opts(acino_sba_opts* o, int mode);
+acino_sba_t* acino_sba_create(int n_cams, int64_t n_points);      /* NULL on error */
+void acino_sba_destroy(acino_sba_t* h);
+int acino_sba_set_cameras(acino_sba_t* h, const double* cams24);                    /* host */
+int acino_sba_set_observations(acino_sba_t* h, const double* uv, const uint8_t* obs_mask);      /* host, copied */
+int acino_sba_set_observations_dev(acino_sba_t* h, const double* uv_dev, const uint8_t* obs_mask_dev); /* borrowed */
+int acino_sba_set_points(acino_sba_t* h, const double* xyz);                        /* host */
+int acino_sba_set_points_dev(acino_sba_t* h, const double* xyz_dev);                /* d2d copy */
+int acino_sba_get_points(acino_sba_t* h, double* xyz);
+int acino_sba_get_cameras(acino_sba_t* h, double* cams24);
+int acino_sba_get_rvec_t(acino_sba_t* h, double* rvecs, double* tvecs);             /* extrinsics mode parameters */
+int acino_sba_set_rvec_t(acino_sba_t* h, const double* rvecs, const double* tvecs);
+/* dense residuals f double[P][C][2] at the current parameters (0 in empty slots) */
+int acino_sba_residuals(acino_sba_t* h, double* f);
+int acino_sba_solve(acino_sba_t* h, const acino_sba_opts* opts, acino_sba_stats* stats);
+/* one LM iteration over the whole scene on the handle's stream, no host sync (bench / roofline) */
+int acino_sba_iterate(acino_sba_t* h, const acino_sba_opts* opts);
+int acino_sba_reset_state(acino_sba_t* h);
+void* acino_sba_stream(acino_sba_t* h);
+
+/* multi-GPU (frame-sharded) — one handle per rank; NCCL is dlopen'ed from the process */
+int acino_nccl_unique_id(void* id128);
+int acino_sba_comm_init(acino_sba_t* h, const void* id128, int rank, int nranks);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

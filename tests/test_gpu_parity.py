@@ -1,0 +1,133 @@
+"""GPU parity tests: the CUDA path through the C ABI / reference-shaped Python API versus
+(a) golden fixtures produced by the real reference and (b) the numpy oracle on seeded inputs.
+
+Tolerances (BASELINE.json north_star): masking / indexing bit-exact; residuals 1e-9 relative;
+triangulated points 1e-9 m; converged SBA points 0.1 mm, RMSE 1e-4 px.
+"""
+import os
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from acinoset_b200 import calib, utils, sba, dense, synth, _capi
+from oracle import fisheye_np as oracle
+
+
+def _rel(a, b):
+    return np.abs(a - b) / np.maximum(1.0, np.abs(b))
+
+
+@pytest.fixture(scope='module')
+def gcam(golden_dir):
+    return np.load(os.path.join(golden_dir, 'golden_camera.npz'))
+
+
+@pytest.fixture(scope='module')
+def gc1(golden_dir):
+    return np.load(os.path.join(golden_dir, 'golden_c1.npz'))
+
+
+def test_library_loaded_and_device():
+    assert _capi.require_gpu() >= 1
+    assert _capi.lib().acino_version() == 100
+
+
+def test_project_vs_reference_golden(rig, gcam):
+    k, d, r, t, _ = rig
+    for c in range(6):
+        uv = calib.project_points_fisheye(gcam['X'], k[c], d[c], r[c], t[c])
+        assert uv.shape == (2000, 2) and uv.dtype == np.float64
+        assert _rel(uv, gcam['uv'][c]).max() < 1e-9
+        uvw = calib.project_points_fisheye(gcam['Xw'], k[c], d[c], r[c], t[c])
+        assert _rel(uvw, gcam['uvw'][c]).max() < 1e-9
+
+
+def test_project_shapes(rig):
+    k, d, r, t, _ = rig
+    one = calib.project_points_fisheye(np.array([1.0, 6.0, 0.5]), k[1], d[1].reshape(4), r[1], t[1].reshape(3))
+    assert one.shape == (1, 2)
+    ref = oracle.project_points_fisheye(np.array([[1.0, 6.0, 0.5]]), k[1], d[1], r[1], t[1])
+    assert _rel(one, ref).max() < 1e-12
+    f32 = calib.project_points_fisheye(np.array([[1.0, 6.0, 0.5]], dtype=np.float32), k[1], d[1], r[1], t[1])
+    assert f32.dtype == np.float64
+    assert calib.project_points_fisheye(np.zeros((0, 3)), k[0], d[0], r[0], t[0]).shape == (0, 2)
+
+
+def test_project_on_axis_and_behind(rig):
+    k, d, r, t, _ = rig
+    # camera 0: R maps world (x,y,z)->(x,-z,y), t=0. Points on / near the optical axis and behind the camera.
+    X = np.array([[0.0, 5.0, 0.0], [1e-10, 5.0, 0.0], [1e-7, 5.0, -1e-7], [0.3, -4.0, 0.2], [2.0, -1.0, 1.0]])
+    got = calib.project_points_fisheye(X, k[0], d[0], r[0], t[0])
+    ref = oracle.project_points_fisheye(X, k[0], d[0], r[0], t[0])
+    assert _rel(got, ref).max() < 1e-9
+
+
+def test_triangulate_pair_vs_reference_golden(rig, gcam):
+    k, d, r, t, _ = rig
+    for c in range(6):
+        b = (c + 1) % 6
+        X = calib.triangulate_points_fisheye(gcam['noisy'][c].reshape(-1, 1, 2), gcam['noisy'][b].reshape(-1, 1, 2),
+                                             k[c], d[c], r[c], t[c], k[b], d[b], r[b], t[b])
+        assert X.shape == (2000, 3)
+        assert np.abs(X - gcam['tri'][c]).max() < 1e-9
+
+
+def test_rodrigues_vs_opencv_golden(gcam):
+    rv = np.ascontiguousarray(gcam['rv'])
+    R = np.empty((len(rv), 3, 3))
+    _capi.check(_capi.lib().acino_rodrigues(_capi.ptr(rv), len(rv), _capi.ptr(R)))
+    assert np.abs(R - gcam['rmat']).max() < 1e-14
+    back = np.stack([sba.rotation_matrix_to_rvec(m) for m in gcam['rmat']])
+    assert np.abs(back - gcam['rv_back']).max() < 1e-9
+
+
+def test_ring_triangulation_c1_golden(gc1):
+    """get_pairwise_3d_points_from_df on config C1: row order and existence bit-exact, xyz to 1e-9 m."""
+    sc = synth.make_rig_scene(102, 20, seed=0)
+    df = synth.dense_to_df(sc['uv'], sc['lik'], 20, first_frame=69)
+    df = df.query('likelihood > 0.5')
+    df = df[df['frame'].between(69, 170)]
+    out = utils.get_pairwise_3d_points_from_df(df, sc['k'], sc['d'].reshape(-1, 4), sc['r'], sc['t'],
+                                               calib.triangulate_points_fisheye, verbose=False)
+    assert list(out.columns) == ['frame', 'marker', 'x', 'y', 'z']
+    assert len(out) == len(gc1['points_3d'])
+    assert (out['frame'].to_numpy().astype(np.int64) == gc1['frame']).all()
+    assert (out['marker'].to_numpy().astype(str) == gc1['marker']).all()
+    assert np.abs(out[['x', 'y', 'z']].to_numpy() - gc1['points_3d']).max() < 1e-9
+
+
+def test_residuals_c1_golden(rig, gc1):
+    k, d, r, t, _ = rig
+    n = len(gc1['points_3d'])
+    f0 = sba.cost_func_points_only(gc1['points_3d'].ravel(), n, gc1['point_indices'], gc1['camera_indices'], k, d, r, t,
+                                   gc1['points_2d'], calib.project_points_fisheye)
+    assert f0.shape == gc1['f_before'].shape
+    assert _rel(f0, gc1['f_before']).max() < 1e-9
+    fp = sba.cost_func_points_only(gc1['x_pert'], n, gc1['point_indices'], gc1['camera_indices'], k, d, r, t,
+                                   gc1['points_2d'], calib.project_points_fisheye)
+    assert _rel(fp, gc1['f_pert']).max() < 1e-9
+
+
+def test_sba_points_only_c1_golden(rig, gc1, capsys):
+    """bundle_adjust_points_only vs the reference's scipy result on C1."""
+    k, d, r, t, _ = rig
+    obj, res = sba.bundle_adjust_points_only(gc1['points_2d'], gc1['points_3d'], gc1['point_indices'], gc1['camera_indices'],
+                                             k, d, r, t, calib.project_points_fisheye, f_scale=50)
+    assert 'Optimization took' in capsys.readouterr().out
+    assert _rel(res['before'], gc1['f_before']).max() < 1e-9
+    cost_ref = oracle.cauchy_cost(gc1['f_after'], 50.0)
+    cost_new = oracle.cauchy_cost(res['after'], 50.0)
+    assert cost_new <= cost_ref * (1 + 1e-9)
+    rmse_ref = np.sqrt(np.mean(gc1['f_after'] ** 2))
+    rmse_new = np.sqrt(np.mean(res['after'] ** 2))
+    assert abs(rmse_new - rmse_ref) < 1e-4
+    dist = np.linalg.norm(obj - gc1['obj_pts'], axis=1)
+    assert dist.max() < 1e-4, f'max point distance {dist.max()} m'
+
+
+def test_non_fisheye_callable_rejected(rig, gc1):
+    k, d, r, t, _ = rig
+    with pytest.raises(NotImplementedError):
+        sba.bundle_adjust_points_only(gc1['points_2d'], gc1['points_3d'], gc1['point_indices'], gc1['camera_indices'],
+                                      k, d, r, t, lambda *a: None)
