@@ -170,3 +170,40 @@ def nccl_unique_id() -> bytes:
     buf = ct.create_string_buffer(128)
     _capi.check(_capi.lib().acino_nccl_unique_id(buf))
     return buf.raw
+
+
+def solve_scene_host(uv, lik, thresh, k_arr, d_arr, r_arr, t_arr, mode=MODE_POINTS_ONLY, out_points=None, rvec_t0=None,
+                     **solver_opts):
+    """Whole pipeline on host buffers (what core.tri + core.sba do, src/core/tri.py:41-47, src/core/sba.py:41-43):
+    upload observations and likelihoods, threshold + ring triangulation (K2), SBA solve, download the points.
+    Returns the solver statistics; absent points are NaN rows of ``out_points``."""
+    _capi.require_gpu()
+    uv = _capi.f64(uv)
+    P, C = uv.shape[0], uv.shape[1]
+    lik = _capi.f64(lik).reshape(P, C)
+    cams = _capi.pack_cams(k_arr, d_arr, r_arr, t_arr)
+    L = _capi.lib()
+    uv_d = DeviceArray.from_host(uv)
+    lik_d = DeviceArray.from_host(lik)
+    xyz_d = DeviceArray((P, 3), np.float64)
+    mask_d = DeviceArray((P,), np.uint8)
+    ex_d = DeviceArray((P,), np.uint8)
+    solver = SbaSolver(C, P)
+    try:
+        _capi.check(L.acino_triangulate_ring_dev(uv_d.ptr, lik_d.ptr, float(thresh), P, C, _capi.ptr(cams), xyz_d.ptr,
+                                                 mask_d.ptr, ex_d.ptr, ct.c_void_p(solver.stream)))
+        solver.set_cameras(k_arr, d_arr, r_arr, t_arr)
+        if mode == MODE_POINTS_AND_EXTRINSICS and rvec_t0 is not None and rvec_t0[0] is not None:
+            solver.set_rvec_t(rvec_t0[0], rvec_t0[1])
+        solver.set_observations_dev(uv_d, mask_d)
+        solver.set_points_dev(xyz_d)
+        st = solver.solve(default_opts(mode, **solver_opts))
+        if out_points is None:
+            out_points = np.empty((P, 3))
+        _capi.check(L.acino_sba_get_points(solver._h, _capi.ptr(out_points)))
+        st['points'] = out_points
+    finally:
+        solver.close()
+        for a in (uv_d, lik_d, xyz_d, mask_d, ex_d):
+            a.free()
+    return st

@@ -1,0 +1,112 @@
+"""CPU tests of the boundary: the C-ABI library loads, exports every symbol include/acino_b200.h declares, and the
+host-side lowering (DataFrame / observation lists -> dense slots) is exact. No compute calls (no GPU here)."""
+import os
+import re
+import numpy as np
+import pandas as pd
+import pytest
+
+from acinoset_b200 import _capi, utils, sba, synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_symbols():
+    src = open(os.path.join(ROOT, 'include', 'acino_b200.h')).read()
+    src = re.sub(r'/\*.*?\*/', '', src, flags=re.S)
+    return sorted(set(re.findall(r'\b(acino_[a-z0-9_]+)\s*\(', src)))
+
+
+def test_library_exports_every_declared_symbol():
+    L = _capi.lib()
+    names = _header_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(L, n), f'{n} declared in include/acino_b200.h but not exported'
+    assert set(names) == set(_capi.SIGNATURES), 'ctypes signature table and header disagree'
+
+
+def test_no_gpu_means_loud_failure():
+    if _capi.lib().acino_device_count() > 0:
+        pytest.skip('a GPU is visible')
+    with pytest.raises(_capi.AcinoError):
+        _capi.require_gpu()
+    from acinoset_b200 import calib
+    k, d, r, t, _ = synth.load_rig()
+    with pytest.raises(_capi.AcinoError):
+        calib.project_points_fisheye(np.zeros((1, 3)), k[0], d[0], r[0], t[0])
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, 'acinoset_b200')
+    for fn in os.listdir(pkg):
+        if fn.endswith('.py'):
+            assert 'oracle' not in open(os.path.join(pkg, fn)).read(), fn
+
+
+def test_pack_cam_layout(rig):
+    k, d, r, t, _ = rig
+    c = _capi.pack_cam(k[2], d[2], r[2], t[2])
+    assert c.shape == (24,)
+    assert c[0] == k[2][0, 0] and c[1] == k[2][1, 1] and c[2] == k[2][0, 2] and c[3] == k[2][1, 2]
+    assert (c[5:9] == d[2].ravel()).all() and (c[9:18] == r[2].ravel()).all() and (c[18:21] == t[2].ravel()).all()
+    assert (_capi.pack_cam(k[2], d[2].reshape(4), r[2], t[2].reshape(3)) == c).all()
+    with pytest.raises(ValueError):
+        _capi.pack_cam(k[2], np.zeros(5), r[2], t[2])
+
+
+def test_df_to_dense_order_and_masking():
+    """Point order = sorted (frame, marker name) (groupby at src/lib/utils.py:348); strict > threshold applied by caller."""
+    sc = synth.make_rig_scene(4, 20, seed=2)
+    df = synth.dense_to_df(sc['uv'], sc['lik'], 20, first_frame=10)
+    dft = df.query('likelihood > 0.5')
+    uv, present, frames, markers, slot = utils.df_to_dense(dft, 6)
+    keys = sorted(set(zip(dft['frame'], dft['marker'])))
+    assert list(zip(frames, markers)) == keys
+    assert present.sum() == len(dft)
+    # every row lands in its slot
+    flat = uv.reshape(-1, 2)
+    assert (flat[slot, 0] == dft['x'].to_numpy()).all() and (flat[slot, 1] == dft['y'].to_numpy()).all()
+    # against the generator's mask
+    m = sc['lik'] > 0.5
+    assert present.sum() == m.sum()
+
+
+def test_df_to_dense_rejects_duplicates_and_bad_cameras():
+    df = pd.DataFrame({'frame': [1, 1], 'camera': [0, 0], 'marker': ['a', 'a'], 'x': [0., 1.], 'y': [0., 1.]})
+    with pytest.raises(ValueError):
+        utils.df_to_dense(df, 6)
+    df = pd.DataFrame({'frame': [1], 'camera': [7], 'marker': ['a'], 'x': [0.], 'y': [0.]})
+    with pytest.raises(ValueError):
+        utils.df_to_dense(df, 6)
+    out = utils.df_to_dense(df.iloc[:0], 6)
+    assert out[0].shape == (0, 6, 2)
+
+
+def test_lists_to_dense_roundtrip():
+    rng = np.random.default_rng(0)
+    P, C = 50, 6
+    pairs = [(p, c) for p in range(P) for c in range(C) if rng.uniform() < 0.5]
+    rng.shuffle(pairs)
+    pidx = np.array([p for p, _ in pairs]); cidx = np.array([c for _, c in pairs])
+    obs = rng.normal(size=(len(pairs), 2))
+    uv, mask, slot = sba._lists_to_dense(obs, pidx, cidx, P, C)
+    assert (uv.reshape(-1, 2)[slot] == obs).all()
+    want = np.zeros(P, dtype=np.uint8)
+    for p, c in pairs:
+        want[p] |= 1 << c
+    assert (mask == want).all()
+    with pytest.raises(NotImplementedError):
+        sba._lists_to_dense(np.zeros((2, 2)), np.array([0, 0]), np.array([1, 1]), P, C)
+    with pytest.raises(ValueError):
+        sba._lists_to_dense(np.zeros((1, 2)), np.array([P]), np.array([0]), P, C)
+
+
+def test_rotation_matrix_to_rvec_matches_opencv():
+    import cv2
+    rng = np.random.default_rng(1)
+    for _ in range(50):
+        v = rng.normal(0, 1.2, 3)
+        R = cv2.Rodrigues(v)[0]
+        assert np.abs(sba.rotation_matrix_to_rvec(R) - cv2.Rodrigues(R)[0].ravel()).max() < 1e-9
+    assert np.abs(sba.rotation_matrix_to_rvec(np.eye(3))).max() == 0.0

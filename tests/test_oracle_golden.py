@@ -1,0 +1,110 @@
+"""CPU tests: pin the oracle (oracle/fisheye_np.py restatement and oracle/ref_port.py port) against fixtures produced
+by the REAL reference (oracle/make_golden.py, run in the build container), and check the host-side logic.
+No GPU needed."""
+import os
+import numpy as np
+import pytest
+
+from oracle import fisheye_np as oracle
+from oracle import ref_port
+from acinoset_b200 import synth
+
+
+def _rel(a, b):
+    return np.abs(a - b) / np.maximum(1.0, np.abs(b))
+
+
+@pytest.fixture(scope='module')
+def gcam(golden_dir):
+    return np.load(os.path.join(golden_dir, 'golden_camera.npz'))
+
+
+@pytest.fixture(scope='module')
+def gc1(golden_dir):
+    return np.load(os.path.join(golden_dir, 'golden_c1.npz'))
+
+
+def test_projection_restatement_vs_reference(rig, gcam):
+    k, d, r, t, _ = rig
+    for c in range(6):
+        assert _rel(oracle.project_points_fisheye(gcam['X'], k[c], d[c], r[c], t[c]), gcam['uv'][c]).max() < 1e-10
+        assert _rel(oracle.project_points_fisheye(gcam['Xw'], k[c], d[c], r[c], t[c]), gcam['uvw'][c]).max() < 1e-9
+
+
+def test_undistort_restatement_vs_opencv(rig, gcam):
+    k, d, r, t, _ = rig
+    for c in range(6):
+        assert np.abs(oracle.undistort_points_fisheye(gcam['noisy'][c], k[c], d[c]) - gcam['und'][c]).max() < 1e-13
+    e = oracle.undistort_points_fisheye(gcam['edge'], k[0], d[0])
+    ref = gcam['und_edge']
+    assert np.allclose(e, ref, rtol=1e-12, atol=1e-13)
+
+
+def test_two_view_dlt_restatement_vs_reference(rig, gcam):
+    k, d, r, t, _ = rig
+    for c in range(6):
+        b = (c + 1) % 6
+        X = oracle.triangulate_points_fisheye(gcam['noisy'][c], gcam['noisy'][b], k[c], d[c], r[c], t[c], k[b], d[b], r[b], t[b])
+        assert np.abs(X - gcam['tri'][c]).max() < 1e-10
+
+
+def test_rodrigues_restatement_vs_opencv(gcam):
+    R = np.stack([oracle.rodrigues_vec_to_mat(v) for v in gcam['rv']])
+    assert np.abs(R - gcam['rmat']).max() < 1e-14
+
+
+def test_ring_triangulation_restatement_c1(gc1):
+    """Dense-slot restatement of get_pairwise_3d_points_from_df reproduces the reference's rows (order = frame, then
+    marker name) and values on config C1."""
+    sc = synth.make_rig_scene(102, 20, seed=0)
+    xyz, exists, mask = oracle.ring_triangulate_dense(sc['uv'], sc['lik'], 0.5, sc['k'], sc['d'], sc['r'], sc['t'])
+    frames = 69 + np.repeat(np.arange(102), 20)
+    markers = np.tile(np.array(synth.MARKERS), 102)
+    order = np.lexsort((markers[exists], frames[exists]))
+    assert (frames[exists][order] == gc1['frame']).all()
+    assert (markers[exists][order] == gc1['marker']).all()
+    assert np.abs(xyz[exists][order] - gc1['points_3d']).max() < 1e-10
+
+
+def test_residual_restatement_c1(rig, gc1):
+    k, d, r, t, _ = rig
+    n = len(gc1['points_3d'])
+    f = oracle.residuals_points_only(gc1['points_3d'].ravel(), n, gc1['point_indices'], gc1['camera_indices'], k, d, r, t, gc1['points_2d'])
+    assert _rel(f, gc1['f_before']).max() < 1e-10
+    f = oracle.residuals_points_only(gc1['x_pert'], n, gc1['point_indices'], gc1['camera_indices'], k, d, r, t, gc1['points_2d'])
+    assert _rel(f, gc1['f_pert']).max() < 1e-10
+
+
+def test_ref_port_cost_function_is_the_reference_loop(rig, gc1):
+    """The per-observation OpenCV loop of the port gives the reference's residual vector bit-for-bit (same library calls)."""
+    k, d, r, t, _ = rig
+    sel = slice(0, 300)
+    fn = ref_port.CostCounter(gc1['point_indices'][sel], gc1['camera_indices'][sel], gc1['points_2d'][sel], k, d, r, t)
+    f = fn.points_only(gc1['points_3d'].ravel())
+    assert np.array_equal(f, gc1['f_before'][:600])
+
+
+def test_ref_port_scene_pipeline_matches_reference_on_c1_prefix(gc1):
+    """TRI + merge + scipy solve of the port on the first frames of C1 lands on the reference's converged points.
+    (Points are independent problems, SURVEY.md F4, so a prefix of the scene converges to the same per-point minimisers
+    up to scipy's global stopping rule: agreement is asserted at 0.05 mm.)"""
+    sc = synth.make_rig_scene(102, 20, seed=0)
+    nf = 6
+    out = ref_port.sba_points_scene(sc['uv'][:nf * 20], sc['lik'][:nf * 20], 0.5, sc['k'], sc['d'], sc['r'], sc['t'])
+    n = out['n_points']
+    assert (out['frame'] + 69 == gc1['frame'][:n]).all() and (out['marker'] == gc1['marker'][:n]).all()
+    assert np.abs(out['X0'] - gc1['points_3d'][:n]).max() < 1e-12
+    assert (out['pidx'].max() == n - 1)
+    assert np.linalg.norm(out['points'] - gc1['obj_pts'][:n], axis=1).max() < 5e-5
+
+
+def test_sparsity_pattern_shapes():
+    cidx = np.array([0, 1, 1, 2]); pidx = np.array([0, 0, 1, 1])
+    A = ref_port.sparsity_pattern(3, 0, cidx, 2, pidx).toarray()
+    assert A.shape == (8, 6) and A.sum() == 8 * 3
+    S = ref_port.sparsity_pattern(3, 6, cidx, 2, pidx, layout='shipped').toarray()
+    Cn = ref_port.sparsity_pattern(3, 6, cidx, 2, pidx, layout='consistent').toarray()
+    assert S.shape == Cn.shape == (8, 24) and S.sum() == Cn.sum() == 8 * 9
+    # shipped: obs 0 (camera 0) marks columns 0..5; consistent: rvec 0..2 and tvec 9..11
+    assert S[0, :6].all() and not S[0, 6:18].any()
+    assert Cn[0, [0, 1, 2, 9, 10, 11]].all() and Cn[0, :18].sum() == 6
