@@ -21,14 +21,14 @@ class AcinoError(RuntimeError):
 class SbaOpts(ct.Structure):
     _fields_ = [('mode', ct.c_int32), ('max_iter', ct.c_int32), ('inner_iters', ct.c_int32), ('force_iters', ct.c_int32),
                 ('f_scale', ct.c_double), ('gtol', ct.c_double), ('xtol', ct.c_double), ('lambda0', ct.c_double),
-                ('reserved', ct.c_double * 4)]
+                ('ftol', ct.c_double), ('reserved', ct.c_double * 3)]
 
 
 class SbaStats(ct.Structure):
     _fields_ = [('n_points', ct.c_int64), ('n_obs', ct.c_int64), ('n_unconverged', ct.c_int64),
                 ('iterations', ct.c_int32), ('launches', ct.c_int32),
                 ('cost_initial', ct.c_double), ('cost_final', ct.c_double), ('solve_ms', ct.c_double),
-                ('reserved', ct.c_double * 4)]
+                ('status', ct.c_double), ('n_accept', ct.c_double), ('lambda_final', ct.c_double), ('gmax', ct.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != 'reserved'}
@@ -74,6 +74,10 @@ SIGNATURES = {
     'acino_sba_iterate': (_I, [_P, ct.POINTER(SbaOpts)]),
     'acino_sba_reset_state': (_I, [_P]),
     'acino_sba_stream': (_P, [_P]),
+    'acino_sba_profile': (_I, [_P, _I]),
+    'acino_sba_profile_read': (_I, [_P, ct.POINTER(_D), ct.POINTER(_D), ct.POINTER(_I)]),
+    'acino_sba_lm_state': (_I, [_P, _P]),
+    'acino_fp64_peak': (_I, [ct.POINTER(_D)]),
     'acino_nccl_unique_id': (_I, [_P]),
     'acino_sba_comm_init': (_I, [_P, _P, _I, _I]),
 }

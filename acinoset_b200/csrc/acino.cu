@@ -37,7 +37,7 @@ using namespace acino;
 extern "C" {
 
 const char* acino_last_error(void) { return g_err; }
-int acino_version(void) { return 100; }
+int acino_version(void) { return 200; }
 int acino_device_count(void) {
   int n = 0;
   cudaError_t e = cudaGetDeviceCount(&n);

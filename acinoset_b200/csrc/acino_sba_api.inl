@@ -31,6 +31,8 @@ namespace acino {
 static int schur_reset(acino_sba*);
 static int solve_schur(acino_sba*, const acino_sba_opts*, acino_sba_stats*);
 static int schur_iterate(acino_sba*, const acino_sba_opts*);
+static int schur_sync_current(acino_sba*);
+static void schur_free(SchurState&);
 static void comm_destroy(acino_sba*);
 
 #define DISPATCH_C(C_, CALL)            \
@@ -149,8 +151,9 @@ void acino_sba_default_opts(acino_sba_opts* o, int mode) {
     o->max_iter = 200;
     o->inner_iters = 1;
     o->f_scale = 1.0;          // scipy default f_scale, src/lib/sba.py:170-173
-    o->gtol = 1e-9;
-    o->xtol = 1e-13;
+    o->gtol = 1e-8;
+    o->xtol = 1e-14;
+    o->ftol = 1e-14;
     o->lambda0 = 1e-4;
   } else {
     o->max_iter = 200;
@@ -193,7 +196,6 @@ acino_sba_t* acino_sba_create(int n_cams, int64_t n_points) {
     ok(cudaMemset(h->cost_p, 0, P * sizeof(double)));
     ok(cudaMemset(h->status, 0, P));
   }
-  if (e == cudaSuccess) ok(schur_alloc(h->schur, n_cams, n_points));
   if (e != cudaSuccess) {
     set_error("acino_sba_create: %s", cudaGetErrorString(e));
     cudaGetLastError();
@@ -223,6 +225,7 @@ void* acino_sba_stream(acino_sba_t* h) { return h ? (void*)h->stream : nullptr; 
 int acino_sba_set_cameras(acino_sba_t* h, const double* cams24) {
   H_CHECK(h);
   ARG_CHECK(cams24, "set_cameras");
+  { int rc = schur_sync_current(h); if (rc) return rc; }
   memcpy(h->h_cams, cams24, h->C * CAM_STRIDE * sizeof(double));
   ACINO_CUDA(cudaMemcpyAsync(h->cams, cams24, h->C * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice, h->stream));
   ACINO_CUDA(cudaStreamSynchronize(h->stream));
@@ -265,6 +268,8 @@ int acino_sba_reset_state(acino_sba_t* h) {
     ACINO_CUDA(cudaMemsetAsync(h->lam, 0, P * sizeof(double), h->stream));
     ACINO_CUDA(cudaMemsetAsync(h->status, 0, P, h->stream));
   }
+  if (h->have_cams)     // extrinsics mode moves the cameras: back to the ones last set by the caller
+    ACINO_CUDA(cudaMemcpyAsync(h->cams, h->h_cams, h->C * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice, h->stream));
   return schur_reset(h);
 }
 
@@ -290,6 +295,7 @@ int acino_sba_set_points(acino_sba_t* h, const double* xyz) {
 int acino_sba_get_points(acino_sba_t* h, double* xyz) {
   H_CHECK(h);
   ARG_CHECK(h->P == 0 || xyz, "get_points");
+  { int rc = schur_sync_current(h); if (rc) return rc; }
   if (h->P) {
     ACINO_CUDA(cudaMemcpyAsync(xyz, h->X, h->P * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     ACINO_CUDA(cudaStreamSynchronize(h->stream));
@@ -300,6 +306,7 @@ int acino_sba_get_points(acino_sba_t* h, double* xyz) {
 int acino_sba_get_cameras(acino_sba_t* h, double* cams24) {
   H_CHECK(h);
   ARG_CHECK(cams24, "get_cameras");
+  { int rc = schur_sync_current(h); if (rc) return rc; }
   ACINO_CUDA(cudaMemcpyAsync(cams24, h->cams, h->C * CAM_STRIDE * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   ACINO_CUDA(cudaStreamSynchronize(h->stream));
   return ACINO_OK;
@@ -319,6 +326,8 @@ int acino_sba_residuals(acino_sba_t* h, double* f) {
   if (rc) return rc;
   if (h->P == 0) return ACINO_OK;
   ARG_CHECK(f, "residuals");
+  rc = schur_sync_current(h);
+  if (rc) return rc;
   DevBuf dF;
   ACINO_CUDA(dF.alloc(h->P * h->C * sizeof(double2)));
   DISPATCH_C(h->C, (residuals_dense_kernel<CC><<<grid_for(h->P, 256), 256, 0, h->stream>>>(
@@ -343,7 +352,11 @@ int acino_sba_solve(acino_sba_t* h, const acino_sba_opts* opts, acino_sba_stats*
     stats->n_obs = (int64_t)h->h_counters[0];
     stats->n_points = (int64_t)h->h_counters[1];
   }
-  if (opts->mode == ACINO_MODE_POINTS_ONLY) return solve_points_only(h, opts, stats);
+  if (opts->mode == ACINO_MODE_POINTS_ONLY) {
+    rc = schur_sync_current(h);
+    if (rc) return rc;
+    return solve_points_only(h, opts, stats);
+  }
   if (opts->mode == ACINO_MODE_POINTS_AND_EXTRINSICS) return solve_schur(h, opts, stats);
   set_error("unknown mode %d", opts->mode);
   return ACINO_EINVAL;

@@ -1,11 +1,701 @@
-// acino_sba_schur.cuh — K4/K5/K6: points+extrinsics LM with Schur elimination.
+// acino_sba_schur.cuh — K4/K5/K6: points+extrinsics Levenberg-Marquardt with Schur elimination.
+// Replaces the scipy least_squares call of bundle_adjust_points_and_extrinsics (src/lib/sba.py:158-178):
+// same objective (Cauchy on every scalar residual), analytic Jacobian, per-point 3x3 blocks eliminated into
+// the 6C x 6C reduced camera system (SURVEY.md §8a "Schur structure").
+//
+// Camera chart: a world-frame twist (w, tau) per camera, Xc = R (X + w x X + tau) + t, applied as
+// R <- R Exp(w), t <- t + R tau. With N = d(u,v)/dX (2x3, curvature-weighted) the camera Jacobian of an
+// observation is A = [X x n_0 | n_0 ; X x n_1 | n_1] (2x6), so only N (6 doubles) and the residual pair are
+// staged per observation. The minimiser is chart-independent (the reference's additive rvec covers the same R).
+//
+// Reduced-camera-system vector ("RCS"), NU = C(C+1)/2 units of 40 doubles + 8 scalars:
+//   unit c   (c < C)      : [0..20] S_cc upper triangle, [21..26] rhs_c, [27..32] g_c, [33..38] diag(U_c)
+//   unit C+k (pair c<c')  : [0..35] S_cc' row-major
+//   scalars               : [0] robust cost at the current parameters
 #pragma once
 #include "acino_common.cuh"
 
 namespace acino {
-struct SchurState {
-  int dummy = 0;
+
+#define RCS_UNIT 40
+__host__ __device__ constexpr int rcs_units(int C) { return C * (C + 1) / 2; }
+__host__ __device__ constexpr int rcs_len(int C) { return rcs_units(C) * RCS_UNIT + 8; }
+__host__ __device__ constexpr int schur_bt(int C) { return C <= 6 ? 384 : 256; }
+
+// device-resident LM state: every decision is taken on the device from (all-reduced) sums, identically on all ranks
+struct SchurLm {
+  double lambda, nu;
+  double F;          // cost at the current parameters (written by the solve kernel from the RCS scalar)
+  double F_trial, pred, rho;
+  double gmax, dxmax, xmax;
+  double F0;         // cost at the first linearisation
+  double pred_cam;
+  int cur;           // which of the two parameter buffers is current
+  int status;        // 0 running, 1 gtol, 2 ftol, 3 xtol, 4 stalled (damping exhausted), 6 step failed (kept running)
+  int iter, n_accept, n_reject, chol_fail, skip;
+  int pad;
 };
-static inline cudaError_t schur_alloc(SchurState&, int, int64_t) { return cudaSuccess; }
-static inline void schur_free(SchurState&) {}
+
+struct SchurParams {
+  double inv_c2, half_c2, gtol, ftol, xtol;
+  int force;
+};
+
+// ---- symmetric 3x3: V + lam*D -> inverse (via LDL^T), D = floored diag(V) --------------------------------
+struct Sym3Inv { double i00, i01, i02, i11, i12, i22, D0, D1, D2; };
+__device__ __forceinline__ Sym3Inv damped_inverse3(double v00, double v01, double v02, double v11, double v12, double v22,
+                                                   double lam) {
+  Sym3Inv r;
+  double dmax = fmax(v00, fmax(v11, v22));
+  double flo = fmax(1e-9 * dmax, 1e-300);
+  r.D0 = fmax(v00, flo); r.D1 = fmax(v11, flo); r.D2 = fmax(v22, flo);
+  double a = fma(lam, r.D0, v00), d = fma(lam, r.D1, v11), f = fma(lam, r.D2, v22);
+  double ia = 1.0 / a;
+  double l10 = v01 * ia, l20 = v02 * ia;
+  double d1 = fma(-l10, v01, d);
+  double e1 = fma(-l20, v01, v12);
+  double id1 = 1.0 / d1;
+  double l21 = e1 * id1;
+  double f2 = fma(-l21, e1, fma(-l20, v02, f));
+  double if2 = 1.0 / f2;
+  double m20 = fma(l10, l21, -l20);
+  r.i22 = if2;
+  r.i12 = -l21 * if2;
+  r.i02 = m20 * if2;
+  r.i11 = fma(l21 * l21, if2, id1);
+  r.i01 = fma(-l21 * m20, if2, -l10 * id1);
+  r.i00 = fma(m20 * m20, if2, fma(l10 * l10, id1, ia));
+  return r;
+}
+
+// one observation: weighted point Jacobian rows n0, n1 (sqrt(curvature weight) * d(u,v)/dX), scaled residual e
+// (rho' f / sqrt(w)) so that N^T e is the exact robust gradient and N^T N the Gauss-Newton block
+struct ObsLin { double n0[3], n1[3], e0, e1; };
+__device__ __forceinline__ ObsLin linearise_obs(const double* __restrict__ cam, double X, double Y, double Z, double ou,
+                                                double ov, double inv_c2, double& prod_m1) {
+  double x, y, z, u, v, Ju[3], Jv[3], ju[3], jv[3];
+  to_camera(cam, X, Y, Z, x, y, z);
+  fisheye_uv_jac(cam, x, y, z, u, v, Ju, Jv);
+  mul_R(cam, Ju, ju);
+  mul_R(cam, Jv, jv);
+  double fu = u - ou, fv = v - ov;
+  Robust w = cauchy_weights(fu, fv, inv_c2, prod_m1);
+  double su = sqrt(w.hu), sv = sqrt(w.hv);
+  ObsLin o;
+  o.n0[0] = su * ju[0]; o.n0[1] = su * ju[1]; o.n0[2] = su * ju[2];
+  o.n1[0] = sv * jv[0]; o.n1[1] = sv * jv[1]; o.n1[2] = sv * jv[2];
+  o.e0 = w.gu * fu / su;
+  o.e1 = w.gv * fv / sv;
+  return o;
+}
+
+// reduce-scatter of 40 lane-private doubles over a warp: three halving exchanges (xor 16, 8, 4) then a butterfly
+// over the remaining 4 lanes. On return slot i (i < 5) of every lane holds the warp total of entry
+// i + 5*bit2(lane) + 10*bit3(lane) + 20*bit4(lane).
+__device__ __forceinline__ void warp_reduce_scatter40(double (&a)[RCS_UNIT], int lane) {
+  {
+    const bool up = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 20; ++i) {
+      double keep = up ? a[i + 20] : a[i];
+      double send = up ? a[i] : a[i + 20];
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+  }
+  {
+    const bool up = lane & 8;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+      double keep = up ? a[i + 10] : a[i];
+      double send = up ? a[i] : a[i + 10];
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+  }
+  {
+    const bool up = lane & 4;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      double keep = up ? a[i + 5] : a[i];
+      double send = up ? a[i] : a[i + 5];
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    a[i] += __shfl_xor_sync(0xffffffffu, a[i], 2);
+    a[i] += __shfl_xor_sync(0xffffffffu, a[i], 1);
+  }
+}
+
+// ---- K4: residual + Jacobian + per-point blocks + Schur accumulation ------------------------------------
+// Persistent CTAs of BT threads loop over tiles of BT points.
+//   phase 1 (one thread per point): linearise the point's observations, build V, g, invert V + lam D, stage
+//            N (6 doubles) and e (2) per observation and X, V^-1, h = V^-1 g per point in shared memory, and
+//            append the point to the list of every camera pair (unit) it is observed by.
+//   phase 2 (one warp per unit, lanes over the unit's point list): accumulate the unit's 6x6 block (+ rhs, gradient
+//            and diag(U) for diagonal units) in registers, reduce-scatter over the warp, add into the CTA's
+//            shared RCS. Lists, unit order and the reduction tree are fixed, so the result is deterministic.
+// At the end every CTA writes its RCS partial; the solve kernel (or the reduce kernel before the NCCL
+// allreduce) sums the partials in a fixed order.
+template <int C>
+struct SchurSmem {
+  static constexpr int BT = schur_bt(C);
+  static constexpr int NU = rcs_units(C);
+  static constexpr int NW = BT / 32;
+  static constexpr int LEN = rcs_len(C);
+  static constexpr size_t n_doubles = (size_t)C * CAM_STRIDE + (size_t)C * 8 * BT + 12 * BT + LEN;
+  static constexpr size_t bytes = n_doubles * 8 + (size_t)NU * BT * 2 + (size_t)NU * NW * 4 + NU * 4 + 16 + NU * 2;
+};
+
+template <int C>
+__global__ void __launch_bounds__(schur_bt(C), 1)
+schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
+                   const double* __restrict__ cams0, const double* __restrict__ cams1,
+                   const double* __restrict__ X0, const double* __restrict__ X1,
+                   const SchurLm* __restrict__ lm, SchurParams prm,
+                   double* __restrict__ rcs_partial, double* __restrict__ max_partial) {
+  using L = SchurSmem<C>;
+  constexpr int BT = L::BT, NU = L::NU, NW = L::NW, LEN = L::LEN;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* sc = reinterpret_cast<double*>(smem_raw);
+  double* sN = sc + C * CAM_STRIDE;          // [(c*6+k)*BT + q]
+  double* sE = sN + (size_t)C * 6 * BT;      // [(c*2+k)*BT + q]
+  double* sX = sE + (size_t)C * 2 * BT;      // [k*BT + q], k<3
+  double* sVi = sX + 3 * BT;                 // [k*BT + q], k<6: 00 01 02 11 12 22
+  double* sH = sVi + 6 * BT;                 // [k*BT + q], k<3
+  double* sS = sH + 3 * BT;                  // [LEN]
+  unsigned short* list = reinterpret_cast<unsigned short*>(sS + LEN);   // [u*BT + i]
+  int* cnt = reinterpret_cast<int*>(list + (size_t)NU * BT);            // [u*NW + w]
+  int* unit_n = cnt + NU * NW;                                          // [u]
+  int* next_unit = unit_n + NU;                                         // [1] (+3 pad)
+  unsigned char* u_c = reinterpret_cast<unsigned char*>(next_unit + 4); // [u] first camera
+  unsigned char* u_cp = u_c + NU;                                       // [u] second camera
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int skip = (lm->status != 0 && !prm.force);
+  const int cur = lm->cur;
+  const double lam = lm->lambda;
+  const double* __restrict__ cams = cur ? cams1 : cams0;
+  const double* __restrict__ Xp = cur ? X1 : X0;
+
+  for (int i = tid; i < C * CAM_STRIDE; i += BT) sc[i] = cams[i];
+  for (int i = tid; i < LEN; i += BT) sS[i] = 0.0;
+  if (tid == 0) {
+    int u = C;
+    for (int c = 0; c < C; ++c) { u_c[c] = c; u_cp[c] = c; }
+    for (int c = 0; c < C; ++c)
+      for (int d = c + 1; d < C; ++d) { u_c[u] = c; u_cp[u] = d; ++u; }
+  }
+  __syncthreads();
+
+  double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0;
+  const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    // ---------------- phase 1
+    const int64_t p = tile * BT + tid;
+    unsigned m = (p < P) ? obs_mask[p] : 0u;
+    if (m) {
+      double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
+      double pm1 = 0.0;
+      double g0 = 0, g1 = 0, g2 = 0, v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0;
+#pragma unroll 1
+      for (int c = 0; c < C; ++c) {
+        if (m >> c & 1) {
+          double2 ob = uv[p * C + c];
+          ObsLin o = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, ob.x, ob.y, prm.inv_c2, pm1);
+          double* n = sN + (size_t)(c * 6) * BT + tid;
+          n[0] = o.n0[0]; n[BT] = o.n0[1]; n[2 * BT] = o.n0[2];
+          n[3 * BT] = o.n1[0]; n[4 * BT] = o.n1[1]; n[5 * BT] = o.n1[2];
+          sE[(size_t)(c * 2) * BT + tid] = o.e0;
+          sE[(size_t)(c * 2 + 1) * BT + tid] = o.e1;
+          g0 = fma(o.n0[0], o.e0, fma(o.n1[0], o.e1, g0));
+          g1 = fma(o.n0[1], o.e0, fma(o.n1[1], o.e1, g1));
+          g2 = fma(o.n0[2], o.e0, fma(o.n1[2], o.e1, g2));
+          v00 = fma(o.n0[0], o.n0[0], fma(o.n1[0], o.n1[0], v00));
+          v01 = fma(o.n0[0], o.n0[1], fma(o.n1[0], o.n1[1], v01));
+          v02 = fma(o.n0[0], o.n0[2], fma(o.n1[0], o.n1[2], v02));
+          v11 = fma(o.n0[1], o.n0[1], fma(o.n1[1], o.n1[1], v11));
+          v12 = fma(o.n0[1], o.n0[2], fma(o.n1[1], o.n1[2], v12));
+          v22 = fma(o.n0[2], o.n0[2], fma(o.n1[2], o.n1[2], v22));
+        }
+      }
+      Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
+      sX[tid] = X; sX[BT + tid] = Y; sX[2 * BT + tid] = Z;
+      sVi[tid] = iv.i00; sVi[BT + tid] = iv.i01; sVi[2 * BT + tid] = iv.i02;
+      sVi[3 * BT + tid] = iv.i11; sVi[4 * BT + tid] = iv.i12; sVi[5 * BT + tid] = iv.i22;
+      sH[tid] = fma(iv.i00, g0, fma(iv.i01, g1, iv.i02 * g2));
+      sH[BT + tid] = fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
+      sH[2 * BT + tid] = fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
+      cost_acc += prm.half_c2 * log1p(pm1);
+      gmax_acc = fmax(gmax_acc, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+      xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
+    }
+    // unit membership counts per warp
+#pragma unroll 1
+    for (int u = 0; u < NU; ++u) {
+      bool in = (m >> u_c[u] & 1) && (m >> u_cp[u] & 1);
+      unsigned b = __ballot_sync(0xffffffffu, in);
+      if (lane == 0) cnt[u * NW + warp] = __popc(b);
+    }
+    if (tid == 0) *next_unit = 0;
+    __syncthreads();
+#pragma unroll 1
+    for (int u = 0; u < NU; ++u) {
+      bool in = (m >> u_c[u] & 1) && (m >> u_cp[u] & 1);
+      unsigned b = __ballot_sync(0xffffffffu, in);
+      int base = 0;
+      for (int w = 0; w < warp; ++w) base += cnt[u * NW + w];
+      if (in) list[(size_t)u * BT + base + __popc(b & ((1u << lane) - 1u))] = (unsigned short)tid;
+      if (tid == BT - 1) unit_n[u] = base + __popc(b);     // last warp, last lane: total
+    }
+    __syncthreads();
+    // ---------------- phase 2: warps take units (longest first: diagonal units lead) until none is left
+    for (;;) {
+      int u = 0;
+      if (lane == 0) u = atomicAdd(next_unit, 1);
+      u = __shfl_sync(0xffffffffu, u, 0);
+      if (u >= NU) break;
+      const int n = unit_n[u];
+      if (n == 0) continue;
+      const int c = u_c[u], cp = u_cp[u];
+      const bool diag = (c == cp);
+      double acc[RCS_UNIT];
+#pragma unroll
+      for (int i = 0; i < RCS_UNIT; ++i) acc[i] = 0.0;
+      const double* nc = sN + (size_t)(c * 6) * BT;
+      const double* ncp = sN + (size_t)(cp * 6) * BT;
+      const double* ec = sE + (size_t)(c * 2) * BT;
+#pragma unroll 1
+      for (int base = 0; base < n; base += 32) {
+        if (base + lane < n) {
+          const int q = list[(size_t)u * BT + base + lane];
+          const double X = sX[q], Y = sX[BT + q], Z = sX[2 * BT + q];
+          const double n0x = nc[q], n0y = nc[BT + q], n0z = nc[2 * BT + q];
+          const double n1x = nc[3 * BT + q], n1y = nc[4 * BT + q], n1z = nc[5 * BT + q];
+          const double i00 = sVi[q], i01 = sVi[BT + q], i02 = sVi[2 * BT + q];
+          const double i11 = sVi[3 * BT + q], i12 = sVi[4 * BT + q], i22 = sVi[5 * BT + q];
+          double a0[6], a1[6];
+          a0[0] = fma(Y, n0z, -Z * n0y); a0[1] = fma(Z, n0x, -X * n0z); a0[2] = fma(X, n0y, -Y * n0x);
+          a0[3] = n0x; a0[4] = n0y; a0[5] = n0z;
+          a1[0] = fma(Y, n1z, -Z * n1y); a1[1] = fma(Z, n1x, -X * n1z); a1[2] = fma(X, n1y, -Y * n1x);
+          a1[3] = n1x; a1[4] = n1y; a1[5] = n1z;
+          // Q = N V^-1 (2x3)
+          const double q0x = fma(n0x, i00, fma(n0y, i01, n0z * i02));
+          const double q0y = fma(n0x, i01, fma(n0y, i11, n0z * i12));
+          const double q0z = fma(n0x, i02, fma(n0y, i12, n0z * i22));
+          const double q1x = fma(n1x, i00, fma(n1y, i01, n1z * i02));
+          const double q1y = fma(n1x, i01, fma(n1y, i11, n1z * i12));
+          const double q1z = fma(n1x, i02, fma(n1y, i12, n1z * i22));
+          if (diag) {
+            const double m00 = 1.0 - fma(q0x, n0x, fma(q0y, n0y, q0z * n0z));
+            const double m01 = -fma(q0x, n1x, fma(q0y, n1y, q0z * n1z));
+            const double m11 = 1.0 - fma(q1x, n1x, fma(q1y, n1y, q1z * n1z));
+            double t0[6], t1[6];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) {
+              t0[j] = fma(m00, a0[j], m01 * a1[j]);
+              t1[j] = fma(m01, a0[j], m11 * a1[j]);
+            }
+            int k = 0;
+#pragma unroll
+            for (int i = 0; i < 6; ++i)
+#pragma unroll
+              for (int j = i; j < 6; ++j) { acc[k] = fma(a0[i], t0[j], fma(a1[i], t1[j], acc[k])); ++k; }
+            const double e0 = ec[q], e1 = ec[BT + q];
+            const double hx = sH[q], hy = sH[BT + q], hz = sH[2 * BT + q];
+            const double b0 = e0 - fma(n0x, hx, fma(n0y, hy, n0z * hz));
+            const double b1 = e1 - fma(n1x, hx, fma(n1y, hy, n1z * hz));
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+              acc[21 + i] = fma(a0[i], b0, fma(a1[i], b1, acc[21 + i]));
+              acc[27 + i] = fma(a0[i], e0, fma(a1[i], e1, acc[27 + i]));
+              acc[33 + i] = fma(a0[i], a0[i], fma(a1[i], a1[i], acc[33 + i]));
+            }
+          } else {
+            const double p0x = ncp[q], p0y = ncp[BT + q], p0z = ncp[2 * BT + q];
+            const double p1x = ncp[3 * BT + q], p1y = ncp[4 * BT + q], p1z = ncp[5 * BT + q];
+            double b0[6], b1[6];
+            b0[0] = fma(Y, p0z, -Z * p0y); b0[1] = fma(Z, p0x, -X * p0z); b0[2] = fma(X, p0y, -Y * p0x);
+            b0[3] = p0x; b0[4] = p0y; b0[5] = p0z;
+            b1[0] = fma(Y, p1z, -Z * p1y); b1[1] = fma(Z, p1x, -X * p1z); b1[2] = fma(X, p1y, -Y * p1x);
+            b1[3] = p1x; b1[4] = p1y; b1[5] = p1z;
+            const double m00 = -fma(q0x, p0x, fma(q0y, p0y, q0z * p0z));
+            const double m01 = -fma(q0x, p1x, fma(q0y, p1y, q0z * p1z));
+            const double m10 = -fma(q1x, p0x, fma(q1y, p0y, q1z * p0z));
+            const double m11 = -fma(q1x, p1x, fma(q1y, p1y, q1z * p1z));
+#pragma unroll
+            for (int j = 0; j < 6; ++j) {
+              const double t0 = fma(m00, b0[j], m01 * b1[j]);
+              const double t1 = fma(m10, b0[j], m11 * b1[j]);
+#pragma unroll
+              for (int i = 0; i < 6; ++i) acc[i * 6 + j] = fma(a0[i], t0, fma(a1[i], t1, acc[i * 6 + j]));
+            }
+          }
+        }
+      }
+      warp_reduce_scatter40(acc, lane);
+      if ((lane & 3) == 0) {
+        const int e0 = 5 * ((lane >> 2) & 1) + 10 * ((lane >> 3) & 1) + 20 * ((lane >> 4) & 1);
+        double* dst = sS + u * RCS_UNIT + e0;
+#pragma unroll
+        for (int i = 0; i < 5; ++i) dst[i] += acc[i];
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---------------- CTA totals: cost (sum) and gradient / coordinate maxima
+  __shared__ double red[3][32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cost_acc += __shfl_xor_sync(0xffffffffu, cost_acc, o);
+    gmax_acc = fmax(gmax_acc, __shfl_xor_sync(0xffffffffu, gmax_acc, o));
+    xmax_acc = fmax(xmax_acc, __shfl_xor_sync(0xffffffffu, xmax_acc, o));
+  }
+  if (lane == 0) { red[0][warp] = cost_acc; red[1][warp] = gmax_acc; red[2][warp] = xmax_acc; }
+  __syncthreads();
+  if (tid == 0) {
+    double cs = 0, gm = 0, xm = 0;
+    for (int w = 0; w < NW; ++w) { cs += red[0][w]; gm = fmax(gm, red[1][w]); xm = fmax(xm, red[2][w]); }
+    sS[NU * RCS_UNIT] = cs;
+    max_partial[2 * blockIdx.x] = gm;
+    max_partial[2 * blockIdx.x + 1] = xm;
+  }
+  __syncthreads();
+  for (int i = tid; i < LEN; i += BT) rcs_partial[(size_t)blockIdx.x * LEN + i] = sS[i];
+}
+
+// ---- K5: reduced camera system: sum the partials, damp, Cholesky-solve in shared memory, trial cameras -----
+// One CTA. partial = [n_partial][LEN] (the build kernel's per-CTA partials, or the single all-reduced vector);
+// maxp = [n_max][2] maxima (|g_p|, |X|).
+template <int C>
+__global__ void __launch_bounds__(256)
+schur_solve_kernel(const double* __restrict__ partial, int n_partial, const double* __restrict__ maxp, int n_max,
+                   const double* __restrict__ cams0, const double* __restrict__ cams1, double* __restrict__ cams_trial0,
+                   double* __restrict__ cams_trial1, SchurLm* __restrict__ lm, SchurParams prm,
+                   double* __restrict__ delta_c) {
+  constexpr int NU = rcs_units(C), LEN = rcs_len(C), n = 6 * C;
+  __shared__ double r[LEN];
+  __shared__ double A[n][n + 1];
+  __shared__ double rhs[n], gbar[n], D[n], dl[n];
+  __shared__ double smax[2];
+  __shared__ int fail;
+  const int tid = threadIdx.x;
+  if (lm->status != 0 && !prm.force) return;
+  for (int i = tid; i < LEN; i += blockDim.x) {
+    double s = 0.0;
+    for (int b = 0; b < n_partial; ++b) s += partial[(size_t)b * LEN + i];
+    r[i] = s;
+  }
+  if (tid < 2) {
+    double mx = 0.0;
+    for (int b = 0; b < n_max; ++b) mx = fmax(mx, maxp[2 * b + tid]);
+    smax[tid] = mx;
+  }
+  if (tid == 0) fail = 0;
+  __syncthreads();
+  // assemble the symmetric 6C x 6C matrix
+  for (int e = tid; e < n * n; e += blockDim.x) {
+    int i = e / n, j = e % n;
+    int ci = i / 6, cj = j / 6, a = i % 6, b = j % 6;
+    double v;
+    if (ci == cj) {
+      int lo = a < b ? a : b, hi = a < b ? b : a;
+      v = r[ci * RCS_UNIT + lo * 6 - lo * (lo - 1) / 2 + (hi - lo)];
+    } else {
+      int c0 = ci < cj ? ci : cj, c1 = ci < cj ? cj : ci;
+      int u = C + c0 * C - c0 * (c0 + 1) / 2 + (c1 - c0 - 1);
+      v = ci < cj ? r[u * RCS_UNIT + a * 6 + b] : r[u * RCS_UNIT + b * 6 + a];
+    }
+    A[i][j] = v;
+  }
+  if (tid < n) {
+    int c = tid / 6, a = tid % 6;
+    rhs[tid] = r[c * RCS_UNIT + 21 + a];
+    gbar[tid] = r[c * RCS_UNIT + 27 + a];
+    D[tid] = r[c * RCS_UNIT + 33 + a];
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double dmax = 0.0, gm = smax[0];
+    for (int i = 0; i < n; ++i) { dmax = fmax(dmax, D[i]); gm = fmax(gm, fabs(gbar[i])); }
+    double flo = fmax(1e-12 * dmax, 1e-300);
+    for (int i = 0; i < n; ++i) D[i] = fmax(D[i], flo);
+    lm->F = r[NU * RCS_UNIT];
+    if (lm->iter == 0) lm->F0 = r[NU * RCS_UNIT];
+    lm->gmax = gm;
+    lm->xmax = smax[1];
+    lm->skip = 0;
+    if (!(gm > prm.gtol) && !prm.force) { lm->status = 1; lm->skip = 1; }
+  }
+  __syncthreads();
+  const double lam = lm->lambda;
+  if (tid < n) A[tid][tid] = fma(lam, D[tid], A[tid][tid]);
+  __syncthreads();
+  // in-place Cholesky (lower), right-looking; n <= 48
+  for (int k = 0; k < n; ++k) {
+    if (tid == 0) {
+      double d = A[k][k];
+      if (!(d > 0.0)) { fail = 1; d = 1.0; }
+      A[k][k] = sqrt(d);
+    }
+    __syncthreads();
+    if (tid > k && tid < n) A[tid][k] /= A[k][k];
+    __syncthreads();
+    for (int e = tid; e < (n - k - 1) * (n - k - 1); e += blockDim.x) {
+      int i = k + 1 + e / (n - k - 1), j = k + 1 + e % (n - k - 1);
+      if (j <= i) A[i][j] = fma(-A[i][k], A[j][k], A[i][j]);
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    // L y = -rhs ; L^T d = y
+    for (int i = 0; i < n; ++i) {
+      double s = -rhs[i];
+      for (int j = 0; j < i; ++j) s = fma(-A[i][j], dl[j], s);
+      dl[i] = s / A[i][i];
+    }
+    for (int i = n - 1; i >= 0; --i) {
+      double s = dl[i];
+      for (int j = i + 1; j < n; ++j) s = fma(-A[j][i], dl[j], s);
+      dl[i] = s / A[i][i];
+    }
+    double pc = 0.0;
+    bool bad = fail != 0;
+    for (int i = 0; i < n; ++i) {
+      if (!isfinite(dl[i])) bad = true;
+      pc += 0.5 * (lam * D[i] * dl[i] * dl[i] - gbar[i] * dl[i]);
+    }
+    if (bad) {
+      for (int i = 0; i < n; ++i) dl[i] = 0.0;
+      pc = 0.0;
+      lm->chol_fail += 1;
+    }
+    lm->pred_cam = pc;
+    fail = bad;
+  }
+  __syncthreads();
+  if (tid < n) delta_c[tid] = dl[tid];
+  if (tid == 0) delta_c[n] = fail ? 1.0 : 0.0;
+  // trial cameras: R <- R Exp(w), t <- t + R tau
+  if (tid < C) {
+    const int cur = lm->cur;
+    const double* cam = (cur ? cams1 : cams0) + tid * CAM_STRIDE;
+    double* out = (cur ? cams_trial0 : cams_trial1) + tid * CAM_STRIDE;
+    double E[9];
+    rodrigues(&dl[6 * tid], E);
+    for (int i = 0; i < CAM_STRIDE; ++i) out[i] = cam[i];
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j)
+        out[9 + 3 * i + j] = cam[9 + 3 * i] * E[j] + cam[9 + 3 * i + 1] * E[3 + j] + cam[9 + 3 * i + 2] * E[6 + j];
+    for (int i = 0; i < 3; ++i)
+      out[18 + i] = cam[18 + i] + cam[9 + 3 * i] * dl[6 * tid + 3] + cam[9 + 3 * i + 1] * dl[6 * tid + 4] + cam[9 + 3 * i + 2] * dl[6 * tid + 5];
+  }
+}
+
+// ---- K6: back-substitution + trial evaluation --------------------------------------------------------------
+// One thread per point (grid-stride): re-linearise at the current parameters (V, g and s = sum_c N_c^T N_c d_c with
+// d_c = w_c x X + tau_c, in one pass, nothing is stored per observation), dX = -(V + lam D)^-1 (g + s), write the
+// trial point, evaluate the robust cost at the trial parameters. Per-block partials: [trial cost, predicted
+// reduction of the point blocks, max |dX|, 0].
+template <int C>
+__global__ void __launch_bounds__(128)
+schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
+                     const double* __restrict__ cams0, const double* __restrict__ cams1,
+                     const double* __restrict__ X0, const double* __restrict__ X1, double* __restrict__ Xt0,
+                     double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
+                     const double* __restrict__ delta_c, double* __restrict__ scal_partial) {
+  __shared__ double sc[C * CAM_STRIDE];
+  __shared__ double st[C * CAM_STRIDE];
+  __shared__ double sd[6 * C];
+  __shared__ double red[3][4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int skip = (lm->status != 0 && !prm.force);
+  const int cur = lm->cur;
+  const double lam = lm->lambda;
+  const double* __restrict__ cams = cur ? cams1 : cams0;
+  const double* __restrict__ camt = cur ? cams0 : cams1;
+  const double* __restrict__ Xp = cur ? X1 : X0;
+  double* __restrict__ Xt = cur ? Xt0 : Xt1;
+  for (int i = tid; i < C * CAM_STRIDE; i += blockDim.x) { sc[i] = cams[i]; st[i] = camt[i]; }
+  if (tid < 6 * C) sd[tid] = delta_c[tid];
+  __syncthreads();
+  double f_acc = 0.0, pred_acc = 0.0, dx_acc = 0.0;
+  if (!skip) {
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + tid; p < P; p += (int64_t)gridDim.x * blockDim.x) {
+      unsigned m = obs_mask[p];
+      if (!m) continue;
+      double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
+      double pm1 = 0.0;
+      double g0 = 0, g1 = 0, g2 = 0, v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0;
+      double h0 = 0, h1 = 0, h2 = 0;     // pure point gradient N^T e (for the predicted reduction)
+#pragma unroll 1
+      for (int c = 0; c < C; ++c) {
+        if (m >> c & 1) {
+          double2 ob = uv[p * C + c];
+          ObsLin o = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, ob.x, ob.y, prm.inv_c2, pm1);
+          h0 = fma(o.n0[0], o.e0, fma(o.n1[0], o.e1, h0));
+          h1 = fma(o.n0[1], o.e0, fma(o.n1[1], o.e1, h1));
+          h2 = fma(o.n0[2], o.e0, fma(o.n1[2], o.e1, h2));
+          const double* d = sd + 6 * c;
+          double dx = fma(d[1], Z, -d[2] * Y) + d[3];
+          double dy = fma(d[2], X, -d[0] * Z) + d[4];
+          double dz = fma(d[0], Y, -d[1] * X) + d[5];
+          double y0 = o.e0 + fma(o.n0[0], dx, fma(o.n0[1], dy, o.n0[2] * dz));   // e + N d: g + s in one go
+          double y1 = o.e1 + fma(o.n1[0], dx, fma(o.n1[1], dy, o.n1[2] * dz));
+          g0 = fma(o.n0[0], y0, fma(o.n1[0], y1, g0));
+          g1 = fma(o.n0[1], y0, fma(o.n1[1], y1, g1));
+          g2 = fma(o.n0[2], y0, fma(o.n1[2], y1, g2));
+          v00 = fma(o.n0[0], o.n0[0], fma(o.n1[0], o.n1[0], v00));
+          v01 = fma(o.n0[0], o.n0[1], fma(o.n1[0], o.n1[1], v01));
+          v02 = fma(o.n0[0], o.n0[2], fma(o.n1[0], o.n1[2], v02));
+          v11 = fma(o.n0[1], o.n0[1], fma(o.n1[1], o.n1[1], v11));
+          v12 = fma(o.n0[1], o.n0[2], fma(o.n1[1], o.n1[2], v12));
+          v22 = fma(o.n0[2], o.n0[2], fma(o.n1[2], o.n1[2], v22));
+        }
+      }
+      Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
+      double d0 = -fma(iv.i00, g0, fma(iv.i01, g1, iv.i02 * g2));
+      double d1 = -fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
+      double d2 = -fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
+      // predicted reduction: over all parameters m(0) - m(delta) = 0.5 (lam delta^T D delta - g^T delta) with the
+      // undamped gradient g; this is the point part (the solve kernel adds the camera part).
+      pred_acc += 0.5 * (lam * (iv.D0 * d0 * d0 + iv.D1 * d1 * d1 + iv.D2 * d2 * d2) - (h0 * d0 + h1 * d1 + h2 * d2));
+      double Xn = X + d0, Yn = Y + d1, Zn = Z + d2;
+      Xt[3 * p] = Xn; Xt[3 * p + 1] = Yn; Xt[3 * p + 2] = Zn;
+      dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
+      double pt = 0.0;
+#pragma unroll 1
+      for (int c = 0; c < C; ++c) {
+        if (m >> c & 1) {
+          double x, y, z, u, v;
+          to_camera(st + c * CAM_STRIDE, Xn, Yn, Zn, x, y, z);
+          fisheye_uv(st + c * CAM_STRIDE, x, y, z, u, v);
+          double2 ob = uv[p * C + c];
+          cauchy_accum(u - ob.x, v - ob.y, prm.inv_c2, pt);
+        }
+      }
+      f_acc += prm.half_c2 * log1p(pt);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    f_acc += __shfl_xor_sync(0xffffffffu, f_acc, o);
+    pred_acc += __shfl_xor_sync(0xffffffffu, pred_acc, o);
+    dx_acc = fmax(dx_acc, __shfl_xor_sync(0xffffffffu, dx_acc, o));
+  }
+  if (lane == 0) { red[0][warp] = f_acc; red[1][warp] = pred_acc; red[2][warp] = dx_acc; }
+  __syncthreads();
+  if (tid == 0) {
+    double a = 0, b = 0, c = 0;
+    for (int w = 0; w < 4; ++w) { a += red[0][w]; b += red[1][w]; c = fmax(c, red[2][w]); }
+    scal_partial[4 * blockIdx.x] = a;
+    scal_partial[4 * blockIdx.x + 1] = b;
+    scal_partial[4 * blockIdx.x + 2] = c;
+    scal_partial[4 * blockIdx.x + 3] = 0.0;
+  }
+}
+
+// ---- K7: accept / reject and damping update, on the device ----------------------------------------------------
+// scal = [n_scal][4] partials of the back-substitution kernel (or one all-reduced row).
+__global__ void __launch_bounds__(256)
+schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* __restrict__ dx_override,
+                    const double* __restrict__ delta_c, int n6, SchurLm* __restrict__ lm, SchurParams prm) {
+  __shared__ double red[3][8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (lm->status != 0 && !prm.force) return;
+  double a = 0, b = 0, c = 0;
+  for (int i = tid; i < n_scal; i += blockDim.x) {
+    a += scal[4 * i]; b += scal[4 * i + 1];
+    c = fmax(c, dx_override ? dx_override[0] : scal[4 * i + 2]);
+  }
+  for (int i = tid; i < n6; i += blockDim.x) c = fmax(c, fabs(delta_c[i]));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+    c = fmax(c, __shfl_xor_sync(0xffffffffu, c, o));
+  }
+  if (lane == 0) { red[0][warp] = a; red[1][warp] = b; red[2][warp] = c; }
+  __syncthreads();
+  if (tid != 0) return;
+  a = 0; b = 0; c = 0;
+  for (int w = 0; w < 8; ++w) { a += red[0][w]; b += red[1][w]; c = fmax(c, red[2][w]); }
+  const bool failed = delta_c[n6] != 0.0;
+  const double F = lm->F, Ft = a, pred = b + lm->pred_cam, act = F - Ft;
+  lm->F_trial = Ft;
+  lm->pred = pred;
+  lm->dxmax = c;
+  lm->iter += 1;
+  if (!failed && act > 0.0 && pred > 0.0) {          // comparisons fail on NaN: a non-finite trial is rejected
+    double rho = act / pred;
+    double q = 2.0 * rho - 1.0;
+    lm->rho = rho;
+    lm->lambda = fmax(lm->lambda * fmax(1.0 / 3.0, 1.0 - q * q * q), 1e-14);
+    lm->nu = 2.0;
+    lm->cur ^= 1;
+    lm->F = Ft;
+    lm->n_accept += 1;
+    if (!prm.force) {
+      if (act <= prm.ftol * F) lm->status = 2;
+      else if (c <= prm.xtol * (lm->xmax + prm.xtol)) lm->status = 3;
+    }
+  } else {
+    lm->rho = 0.0;
+    lm->n_reject += 1;
+    double l = lm->lambda * lm->nu;
+    lm->nu = fmin(lm->nu * 2.0, 1e8);
+    if (l > 1e16) {
+      l = 1e16;
+      if (!prm.force) lm->status = 4;
+    }
+    lm->lambda = l;
+  }
+}
+
+// multi-GPU: fold the per-CTA partials before the NCCL allreduce (sum rows, max rows)
+__global__ void __launch_bounds__(256)
+fold_partials_kernel(const double* __restrict__ partial, int n_partial, int len, double* __restrict__ out_sum,
+                     const double* __restrict__ maxp, int n_max, int max_w, int max_stride, int max_off,
+                     double* __restrict__ out_max) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < len) {
+    double s = 0.0;
+    for (int b = 0; b < n_partial; ++b) s += partial[(size_t)b * len + i];
+    out_sum[i] = s;
+  }
+  if (i < max_w) {
+    double m = 0.0;
+    for (int b = 0; b < n_max; ++b) m = fmax(m, maxp[(size_t)b * max_stride + max_off + i]);
+    out_max[i] = m;
+  }
+}
+
+__global__ void schur_init_kernel(SchurLm* lm, double lambda0) {
+  SchurLm z;
+  memset(&z, 0, sizeof(z));
+  z.lambda = lambda0;
+  z.nu = 2.0;
+  *lm = z;
+}
+
+// host-side state of the points+extrinsics solver (owned by the handle)
+struct SchurState {
+  static constexpr int PROF_MAX = 256;
+  bool ready = false, inited = false, prof_on = false;
+  int grid_build = 0, grid_back = 0, launches = 0, prof_n = 0;
+  double* cams_alt = nullptr;
+  double* X_alt = nullptr;
+  double* rcs_partial = nullptr;
+  double* max_partial = nullptr;
+  double* rcs = nullptr;
+  double* mx = nullptr;
+  double* delta_c = nullptr;
+  double* scal_partial = nullptr;
+  double* scal = nullptr;
+  SchurLm* lm = nullptr;
+  SchurLm* h_lm = nullptr;
+  cudaEvent_t prof_ev[4 * PROF_MAX] = {};
+};
+
 }  // namespace acino

@@ -157,6 +157,20 @@ class SbaSolver:
     def iterate(self, opts):
         _capi.check(_capi.lib().acino_sba_iterate(self._h, ct.byref(opts)))
 
+    def profile(self, enable=True):
+        _capi.check(_capi.lib().acino_sba_profile(self._h, int(bool(enable))))
+
+    def profile_read(self):
+        """Average device ms of the build (K4) and back-substitution (K6) kernels over the profiled iterations."""
+        b, k, n = ct.c_double(), ct.c_double(), ct.c_int()
+        _capi.check(_capi.lib().acino_sba_profile_read(self._h, ct.byref(b), ct.byref(k), ct.byref(n)))
+        return dict(build_ms=b.value, backsub_ms=k.value, iterations=n.value)
+
+    def lm_state(self):
+        out = np.empty(6)
+        _capi.check(_capi.lib().acino_sba_lm_state(self._h, _capi.ptr(out)))
+        return dict(cost=out[0], lam=out[1], gmax=out[2], iterations=int(out[3]), accepted=int(out[4]), status=int(out[5]))
+
     @property
     def stream(self):
         return _capi.lib().acino_sba_stream(self._h)
@@ -207,3 +221,11 @@ def solve_scene_host(uv, lik, thresh, k_arr, d_arr, r_arr, t_arr, mode=MODE_POIN
         for a in (uv_d, lik_d, xyz_d, mask_d, ex_d):
             a.free()
     return st
+
+
+def fp64_peak_tflops():
+    """Measured fp64 FMA throughput of the current device (acino_fp64_peak)."""
+    _capi.require_gpu()
+    v = ct.c_double()
+    _capi.check(_capi.lib().acino_fp64_peak(ct.byref(v)))
+    return v.value

@@ -90,3 +90,73 @@ def dense_to_df(uv, lik, n_kpts, first_frame=0, markers=None):
         dfs.append(pd.DataFrame({'frame': frame, 'camera': c, 'marker': marker,
                                  'x': uv[:, c, 0], 'y': uv[:, c, 1], 'likelihood': lik[:, c]}))
     return pd.concat(dfs, ignore_index=True)
+
+
+def board_object_points(board_shape=(9, 6), square=0.088):
+    """Planar checkerboard corner grid, same ordering as create_board_object_pts (src/lib/utils.py:313-316)."""
+    g = np.zeros((board_shape[0] * board_shape[1], 3))
+    g[:, :2] = np.mgrid[0:board_shape[0], 0:board_shape[1]].T.reshape(-1, 2) * square
+    return g
+
+
+def _rot_from_axis_angle(v):
+    th = np.linalg.norm(v)
+    if th < 1e-15:
+        return np.eye(3)
+    kx, ky, kz = v / th
+    K = np.array([[0, -kz, ky], [kz, 0, -kx], [-ky, kx, 0]])
+    return np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * (K @ K)
+
+
+def make_board_scene(n_boards, seed=3, noise_px=0.3, board_shape=(9, 6), square=0.088, rig=None,
+                     rvec_sigma=8e-4, t_sigma=3e-3, project=None):
+    """Synthetic extrinsic-calibration input: ``n_boards`` checkerboard poses, each seen by two
+    ring-adjacent cameras (+ a third with probability 0.5), N(0, noise_px) corner noise, stored float32 per camera in
+    the reference's load_points layout (img_pts_arr[cam] (n_img, 54, 1, 2) f32, fnames_arr[cam] list of names).
+    Also returns perturbed initial extrinsics (truth + N(0, rvec_sigma) rad, N(0, t_sigma) m)."""
+    k, d, r, t, res = rig if rig is not None else load_rig()
+    C = len(k)
+    rng = np.random.default_rng(seed)
+    grid = board_object_points(board_shape, square)
+    grid = grid - grid.mean(axis=0)
+    proj = project or _project_np
+    img_pts = [[] for _ in range(C)]
+    fnames = [[] for _ in range(C)]
+    gt_pts = []
+    b = 0
+    tries = 0
+    while b < n_boards and tries < 200 * n_boards:
+        tries += 1
+        yaw = rng.uniform(0, 2 * np.pi)
+        tilt = rng.uniform(-0.3, 0.3, 2)
+        Rb = _rot_from_axis_angle(np.array([0, 0, yaw])) @ _rot_from_axis_angle(np.array([tilt[0], tilt[1], 0.0]))
+        centre = np.array([rng.uniform(0, 4), rng.uniform(5.5, 7.5), rng.uniform(0.3, 1.0)])
+        Xw = grid @ Rb.T + centre
+        a = int(rng.integers(0, C))
+        cams = [a, (a + 1) % C]
+        if rng.uniform() < 0.5:
+            cams.append((a + 2) % C)
+        ok = True
+        pix = {}
+        for c in cams:
+            Xc = Xw @ r[c].T + t[c].reshape(3)
+            uv = proj(Xw, k[c], d[c], r[c], t[c])
+            if (Xc[:, 2] < 0.5).any() or (uv[:, 0] < 0).any() or (uv[:, 0] > res[0]).any() or (uv[:, 1] < 0).any() or (uv[:, 1] > res[1]).any():
+                ok = False
+                break
+            pix[c] = uv + rng.normal(0, noise_px, uv.shape)
+        if not ok:
+            continue
+        name = f'img{b:05d}.jpg'
+        for c in sorted(cams):
+            img_pts[c].append(pix[c].astype(np.float32).reshape(-1, 1, 2))
+            fnames[c].append(name)
+        gt_pts.append(Xw)
+        b += 1
+    if b < n_boards:
+        raise RuntimeError('could not place the requested number of boards in view')
+    img_pts = [np.array(p, dtype=np.float32).reshape(-1, grid.shape[0], 1, 2) for p in img_pts]
+    r0 = np.array([r[c] @ _rot_from_axis_angle(rng.normal(0, rvec_sigma, 3)) for c in range(C)])
+    t0 = t + rng.normal(0, t_sigma, t.shape)
+    return dict(img_pts_arr=img_pts, fnames_arr=fnames, board_shape=board_shape, square=square, k=k, d=d, r=r, t=t,
+                r0=r0, t0=t0, gt=np.array(gt_pts), cam_res=res)

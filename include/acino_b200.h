@@ -87,7 +87,8 @@ typedef struct {
   double gtol;             /* stop when max|g| <= gtol */
   double xtol;             /* stop when an accepted step has max|dx| <= xtol*(max|x|+xtol) */
   double lambda0;          /* initial Marquardt damping */
-  double reserved[4];
+  double ftol;             /* points+extrinsics: stop when an accepted step reduces the cost by <= ftol*cost */
+  double reserved[3];
 } acino_sba_opts;
 
 typedef struct {
@@ -97,7 +98,10 @@ typedef struct {
   int32_t launches;        /* CUDA kernel launches issued by the solve */
   double cost_initial, cost_final;   /* scipy-convention robust cost */
   double solve_ms;         /* device time of the solve (CUDA events) */
-  double reserved[4];
+  double status;           /* points+extrinsics exit reason: 1 gtol, 2 ftol, 3 xtol, 4 stalled, 0 max_iter */
+  double n_accept;         /* accepted LM steps */
+  double lambda_final;     /* Marquardt damping at exit */
+  double gmax;             /* max |gradient| at the last linearisation */
 } acino_sba_stats;
 
 void acino_sba_default_opts(acino_sba_opts* o, int mode);
@@ -120,9 +124,22 @@ int acino_sba_iterate(acino_sba_t* h, const acino_sba_opts* opts);
 int acino_sba_reset_state(acino_sba_t* h);
 void* acino_sba_stream(acino_sba_t* h);
 
-/* multi-GPU (frame-sharded) — one handle per rank; NCCL is dlopen'ed from the process */
+/* per-kernel device times of acino_sba_iterate in points+extrinsics mode (CUDA events on the handle's stream):
+ * enable, run <=256 iterations, read the averages in ms (build = K4 residual+Jacobian+Schur, backsub = K6). */
+int acino_sba_profile(acino_sba_t* h, int enable);
+int acino_sba_profile_read(acino_sba_t* h, double* build_ms, double* backsub_ms, int* n_iterations);
+/* LM state after iterate / solve: out[0]=cost, [1]=lambda, [2]=gmax, [3]=iterations, [4]=accepted, [5]=status */
+int acino_sba_lm_state(acino_sba_t* h, double* out6);
+
+/* multi-GPU (frame-sharded) — one handle per rank; NCCL is dlopen'ed from the process (libnccl.so.2). Every rank
+ * calls solve / iterate collectively; the reduced camera system (6C x 6C + gradient + cost) is all-reduced once per LM
+ * iteration and the trial cost once more, each a single grouped NCCL launch. */
 int acino_nccl_unique_id(void* id128);
 int acino_sba_comm_init(acino_sba_t* h, const void* id128, int rank, int nranks);
+
+/* fp64 FMA throughput of the device (dependent-chain-free DFMA microbenchmark), TFLOP/s: the second roofline
+ * denominator bench.py reports next to the measured HBM bandwidth. */
+int acino_fp64_peak(double* tflops);
 
 #ifdef __cplusplus
 }
