@@ -138,15 +138,15 @@ struct Robust {
   double gu, gv;   // gradient weights rho'(zu), rho'(zv)
   double hu, hv;   // curvature weights
 };
-__device__ __forceinline__ Robust cauchy_weights(double fu, double fv, double inv_c2, double& prod_m1) {
+__device__ __forceinline__ Robust cauchy_weights(double fu, double fv, double inv_c2, double& prod_m1, double hfloor = 0.1) {
   double zu = fu * fu * inv_c2, zv = fv * fv * inv_c2;
   double ou = 1.0 + zu, ov = 1.0 + zv;
   double inv = rcp_nr(ou * ov);
   Robust w;
   w.gu = ov * inv;
   w.gv = ou * inv;
-  w.hu = w.gu * fmax((1.0 - zu) * w.gu, 0.1);
-  w.hv = w.gv * fmax((1.0 - zv) * w.gv, 0.1);
+  w.hu = w.gu * fmax((1.0 - zu) * w.gu, hfloor);
+  w.hv = w.gv * fmax((1.0 - zv) * w.gv, hfloor);
   // prod(1+z) - 1 accumulated without cancellation: p <- p + z (1 + p)
   prod_m1 = fma(zu, 1.0 + prod_m1, prod_m1);
   prod_m1 = fma(zv, 1.0 + prod_m1, prod_m1);

@@ -154,6 +154,7 @@ void acino_sba_default_opts(acino_sba_opts* o, int mode) {
     o->gtol = 1e-8;
     o->xtol = 1e-14;
     o->ftol = 1e-14;
+    o->hess_floor = 0.3;
     o->lambda0 = 1e-4;
   } else {
     o->max_iter = 200;

@@ -37,7 +37,7 @@ struct SchurLm {
 };
 
 struct SchurParams {
-  double inv_c2, half_c2, gtol, ftol, xtol;
+  double inv_c2, half_c2, gtol, ftol, xtol, hfloor;
   int force;
 };
 
@@ -72,14 +72,14 @@ __device__ __forceinline__ Sym3Inv damped_inverse3(double v00, double v01, doubl
 // (rho' f / sqrt(w)) so that N^T e is the exact robust gradient and N^T N the Gauss-Newton block
 struct ObsLin { double n0[3], n1[3], e0, e1; };
 __device__ __forceinline__ ObsLin linearise_obs(const double* __restrict__ cam, double X, double Y, double Z, double ou,
-                                                double ov, double inv_c2, double& prod_m1) {
+                                                double ov, double inv_c2, double hfloor, double& prod_m1) {
   double x, y, z, u, v, Ju[3], Jv[3], ju[3], jv[3];
   to_camera(cam, X, Y, Z, x, y, z);
   fisheye_uv_jac(cam, x, y, z, u, v, Ju, Jv);
   mul_R(cam, Ju, ju);
   mul_R(cam, Jv, jv);
   double fu = u - ou, fv = v - ov;
-  Robust w = cauchy_weights(fu, fv, inv_c2, prod_m1);
+  Robust w = cauchy_weights(fu, fv, inv_c2, prod_m1, hfloor);
   double su = sqrt(w.hu), sv = sqrt(w.hv);
   ObsLin o;
   o.n0[0] = su * ju[0]; o.n0[1] = su * ju[1]; o.n0[2] = su * ju[2];
@@ -202,7 +202,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       for (int c = 0; c < C; ++c) {
         if (m >> c & 1) {
           double2 ob = uv[p * C + c];
-          ObsLin o = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, ob.x, ob.y, prm.inv_c2, pm1);
+          ObsLin o = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
           double* n = sN + (size_t)(c * 6) * BT + tid;
           n[0] = o.n0[0]; n[BT] = o.n0[1]; n[2 * BT] = o.n0[2];
           n[3 * BT] = o.n1[0]; n[4 * BT] = o.n1[1]; n[5 * BT] = o.n1[2];
@@ -533,7 +533,7 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
       for (int c = 0; c < C; ++c) {
         if (m >> c & 1) {
           double2 ob = uv[p * C + c];
-          ObsLin o = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, ob.x, ob.y, prm.inv_c2, pm1);
+          ObsLin o = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
           h0 = fma(o.n0[0], o.e0, fma(o.n1[0], o.e1, h0));
           h1 = fma(o.n0[1], o.e0, fma(o.n1[1], o.e1, h1));
           h2 = fma(o.n0[2], o.e0, fma(o.n1[2], o.e1, h2));

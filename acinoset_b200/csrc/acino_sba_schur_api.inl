@@ -108,6 +108,7 @@ static SchurParams make_schur_params(const acino_sba_opts* o) {
   p.gtol = o->gtol;
   p.ftol = o->ftol;
   p.xtol = o->xtol;
+  p.hfloor = o->hess_floor > 0 ? o->hess_floor : 0.3;
   p.force = o->force_iters;
   return p;
 }

@@ -204,6 +204,8 @@ def native_arm(args):
 
     for _ in range(max(args.warmup, 3)):
         solver.iterate(opts)
+    if mode == 'extrinsics':
+        solver.profile(True)          # CUDA events around K4 / K6 on the solver's stream, inside the timed region
     barrier()
     clocks = ClockSampler(local) if rank == 0 else None
     e0, e1 = ev(), ev()
@@ -214,7 +216,17 @@ def native_arm(args):
     e1.synchronize()
     barrier()
     ms = e0.elapsed_time(e1)
-    kern = solver.kernel_profile() if hasattr(solver, 'kernel_profile') else None
+    kern = None
+    if mode == 'extrinsics':
+        pr = solver.profile_read()
+        solver.profile(False)
+        # K4 (build) reads the mask of every slot-group, and for existing points the point and its kept observations
+        build_bytes = P * 1 + n_pts * 24 + n_obs * 16
+        back_bytes = build_bytes + n_pts * 24
+        kern = dict(name=f'schur_build_kernel<{C}>', ms_per_launch=pr['build_ms'], bytes_per_launch=build_bytes,
+                    launches_per_step=4 if world == 1 else 8, backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes,
+                    profiled_iterations=pr['iterations'])
+    fp64_peak = dense.fp64_peak_tflops()
     if world > 1:
         tms = torch.tensor([ms], device='cuda', dtype=torch.float64)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
@@ -323,7 +335,16 @@ def main():
         launches = ctx['kern']['launches_per_step'] * args.steps
     achieved = bytes_step / (kern_ms * 1e-3) / 1e9
     roofline = dict(bound='hbm', achieved=achieved, peak=peak, unit='GB/s', frac=achieved / peak, traffic=None,
-                    kernel=kern_name, algorithmic_bytes_per_launch=int(bytes_step), kernel_ms=kern_ms, peak_source=peak_src)
+                    kernel=kern_name, algorithmic_bytes_per_launch=int(bytes_step), kernel_ms=kern_ms, peak_source=peak_src,
+                    fp64_peak_tflops_measured=ctx['fp64_peak'],
+                    note='fp64-pipe bound, not HBM bound: see profiles/ for the ncu pipe utilisation')
+    if mode == 'extrinsics':
+        k6 = ctx['kern']
+        roofline['backsub_kernel'] = dict(kernel=f'schur_backsub_kernel<{C}>', kernel_ms=k6['backsub_ms'],
+                                          algorithmic_bytes_per_launch=int(k6['backsub_bytes']),
+                                          achieved=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9,
+                                          frac=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9 / peak)
+        roofline['step_share_of_kernels'] = (k6['ms_per_launch'] + k6['backsub_ms']) / ctx['ms_per_step']
     tri_gbs = tri_bytes(P, C) / (ctx['tri_ms'] * 1e-3) / 1e9
     cb = None
     if not args.no_cpu_baseline and world == 1:

@@ -88,7 +88,9 @@ typedef struct {
   double xtol;             /* stop when an accepted step has max|dx| <= xtol*(max|x|+xtol) */
   double lambda0;          /* initial Marquardt damping */
   double ftol;             /* points+extrinsics: stop when an accepted step reduces the cost by <= ftol*cost */
-  double reserved[3];
+  double hess_floor;       /* points+extrinsics: floor of the Gauss-Newton curvature weight relative to rho'
+                              (rho' + 2 rho'' f^2 = rho' (1-z)/(1+z) is negative beyond |f| > C): 1.0 = plain IRLS weights */
+  double reserved[2];
 } acino_sba_opts;
 
 typedef struct {
