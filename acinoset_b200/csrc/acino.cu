@@ -152,7 +152,7 @@ int acino_triangulate_pair(const double* uv1, const double* uv2, int64_t M, cons
 
 }  // extern "C"
 template <int C>
-static void launch_tri_ring(const double* uv, const double* lik, double thresh, int64_t P, const double* cams,
+static void launch_tri_ring(const double* uv, const double* lik, double thresh, int64_t P, const CamPack& cams,
                             double* xyz, uint8_t* mask, uint8_t* exists, cudaStream_t st) {
   tri_ring_kernel<C><<<grid_for(P, 128), 128, 0, st>>>((const double2*)uv, lik, thresh, P, cams, xyz, mask, exists);
 }
@@ -165,10 +165,9 @@ int acino_triangulate_ring_dev(const double* uv_dev, const double* lik_dev, doub
   if (P == 0) return ACINO_OK;
   ARG_CHECK(uv_dev && lik_dev && xyz_dev && obs_mask_dev && exists_dev, "triangulate_ring_dev null pointer");
   cudaStream_t st = (cudaStream_t)stream;
-  DevBuf cam;
-  ACINO_CUDA(cam.alloc(C * CAM_STRIDE * sizeof(double)));
-  ACINO_CUDA(cudaMemcpyAsync(cam.p, cams24_host, C * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice, st));
-  const double* dc = cam.as<double>();
+  CamPack dc;
+  memset(&dc, 0, sizeof(dc));
+  memcpy(dc.v, cams24_host, C * CAM_STRIDE * sizeof(double));
   switch (C) {
     case 2: launch_tri_ring<2>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;
     case 3: launch_tri_ring<3>(uv_dev, lik_dev, thresh, P, dc, xyz_dev, obs_mask_dev, exists_dev, st); break;

@@ -40,11 +40,14 @@ __device__ __forceinline__ void undistort_fisheye(const double* __restrict__ c, 
   }
 }
 
-// Smallest right singular vector of the 4x4 DLT system by one-sided (Hestenes) Jacobi in registers,
-// then dehomogenise. Rows: x*P[2]-P[0], y*P[2]-P[1] for both views, P = [R|t] (cv::triangulatePoints).
+// Null direction of the 4x4 DLT system (rows x*P[2]-P[0], y*P[2]-P[1] for both views, P = [R|t]) — what
+// cv::triangulatePoints takes from the SVD: the right singular vector of the smallest singular value, then
+// dehomogenised. Computed as the eigenvector of the smallest eigenvalue of B = A^T A by inverse iteration on a
+// Cholesky factor of B + mu I (mu = a few ulps of trace(B), so the factorisation exists even for noise-free input).
+// The iteration contracts by (sigma4/sigma3)^2 per step; it stops when the direction is stationary to 1e-15.
 __device__ __forceinline__ void dlt_pair(const double* __restrict__ ca, const double* __restrict__ cb,
                                          double xa, double ya, double xb, double yb, double* X) {
-  double A[4][4], V[4][4];
+  double A[4][4];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     A[0][k] = fma(xa, ca[15 + k], -ca[9 + k]);
@@ -56,56 +59,56 @@ __device__ __forceinline__ void dlt_pair(const double* __restrict__ ca, const do
   A[1][3] = fma(ya, ca[20], -ca[19]);
   A[2][3] = fma(xb, cb[20], -cb[18]);
   A[3][3] = fma(yb, cb[20], -cb[19]);
+  // B = A^T A (upper triangle)
+  double b00 = 0, b01 = 0, b02 = 0, b03 = 0, b11 = 0, b12 = 0, b13 = 0, b22 = 0, b23 = 0, b33 = 0;
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) V[i][j] = (i == j) ? 1.0 : 0.0;
-
+  for (int i = 0; i < 4; ++i) {
+    b00 = fma(A[i][0], A[i][0], b00); b01 = fma(A[i][0], A[i][1], b01); b02 = fma(A[i][0], A[i][2], b02);
+    b03 = fma(A[i][0], A[i][3], b03); b11 = fma(A[i][1], A[i][1], b11); b12 = fma(A[i][1], A[i][2], b12);
+    b13 = fma(A[i][1], A[i][3], b13); b22 = fma(A[i][2], A[i][2], b22); b23 = fma(A[i][2], A[i][3], b23);
+    b33 = fma(A[i][3], A[i][3], b33);
+  }
+  const double mu = 8.9e-16 * (b00 + b11 + b22 + b33) + 1e-300;
+  b00 += mu; b11 += mu; b22 += mu; b33 += mu;
+  // Cholesky B = L L^T, keeping the inverse diagonal
+  const double i0 = rsqrt_nr(b00);
+  const double l10 = b01 * i0, l20 = b02 * i0, l30 = b03 * i0;
+  const double i1 = rsqrt_nr(fmax(fma(-l10, l10, b11), 1e-300));
+  const double l21 = fma(-l20, l10, b12) * i1, l31 = fma(-l30, l10, b13) * i1;
+  const double i2 = rsqrt_nr(fmax(fma(-l21, l21, fma(-l20, l20, b22)), 1e-300));
+  const double l32 = fma(-l31, l21, fma(-l30, l20, b23)) * i2;
+  const double i3 = rsqrt_nr(fmax(fma(-l32, l32, fma(-l31, l31, fma(-l30, l30, b33))), 1e-300));
+  // inverse iteration; the start vector is the last column of L^-T (one free half-step)
+  double h3 = i3;
+  double h2 = -l32 * h3 * i2;
+  double h1 = -fma(l21, h2, l31 * h3) * i1;
+  double h0 = -fma(l10, h1, fma(l20, h2, l30 * h3)) * i0;
+  double nrm = rsqrt_nr(fma(h0, h0, fma(h1, h1, fma(h2, h2, h3 * h3))));
+  h0 *= nrm; h1 *= nrm; h2 *= nrm; h3 *= nrm;
 #pragma unroll 1
-  for (int sweep = 0; sweep < 30; ++sweep) {
-    bool rotated = false;
-#pragma unroll
-    for (int p = 0; p < 3; ++p) {
-#pragma unroll
-      for (int q = p + 1; q < 4; ++q) {
-        double al = 0, be = 0, ga = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          al = fma(A[i][p], A[i][p], al);
-          be = fma(A[i][q], A[i][q], be);
-          ga = fma(A[i][p], A[i][q], ga);
-        }
-        if (fabs(ga) > 1e-16 * sqrt(al * be) && ga != 0.0) {
-          rotated = true;
-          double zeta = (be - al) / (2.0 * ga);
-          double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(fma(zeta, zeta, 1.0)));
-          double cs = rsqrt(fma(t, t, 1.0));
-          double sn = cs * t;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            double ap = A[i][p], aq = A[i][q];
-            A[i][p] = fma(cs, ap, -sn * aq);
-            A[i][q] = fma(sn, ap, cs * aq);
-            double vp = V[i][p], vq = V[i][q];
-            V[i][p] = fma(cs, vp, -sn * vq);
-            V[i][q] = fma(sn, vp, cs * vq);
-          }
-        }
-      }
-    }
-    if (!rotated) break;
+  for (int it = 0; it < 40; ++it) {
+    // L y = h
+    const double y0 = h0 * i0;
+    const double y1 = fma(-l10, y0, h1) * i1;
+    const double y2 = fma(-l21, y1, fma(-l20, y0, h2)) * i2;
+    const double y3 = fma(-l32, y2, fma(-l31, y1, fma(-l30, y0, h3))) * i3;
+    // L^T z = y
+    double z3 = y3 * i3;
+    double z2 = fma(-l32, z3, y2) * i2;
+    double z1 = fma(-l21, z2, fma(-l31, z3, y1)) * i1;
+    double z0 = fma(-l10, z1, fma(-l20, z2, fma(-l30, z3, y0))) * i0;
+    // scale before squaring: z can be ~1/mu
+    const double big = fmax(fmax(fabs(z0), fabs(z1)), fmax(fabs(z2), fabs(z3)));
+    const double sc = rcp_nr(big);
+    z0 *= sc; z1 *= sc; z2 *= sc; z3 *= sc;
+    nrm = rsqrt_nr(fma(z0, z0, fma(z1, z1, fma(z2, z2, z3 * z3))));
+    z0 *= nrm; z1 *= nrm; z2 *= nrm; z3 *= nrm;
+    const double dot = fma(z0, h0, fma(z1, h1, fma(z2, h2, z3 * h3)));   // z is +/- h at convergence (B^-1 is SPD: +)
+    const double d0 = z0 - h0, d1 = z1 - h1, d2 = z2 - h2, d3 = z3 - h3;
+    h0 = z0; h1 = z1; h2 = z2; h3 = z3;
+    if (fmax(fmax(fabs(d0), fabs(d1)), fmax(fabs(d2), fabs(d3))) < 1e-15 && dot > 0.0) break;
   }
-  // column with the smallest norm
-  double best = 1e300;
-  double h0 = 0, h1 = 0, h2 = 0, h3 = 1;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    double n = 0;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) n = fma(A[i][j], A[i][j], n);
-    if (n < best) { best = n; h0 = V[0][j]; h1 = V[1][j]; h2 = V[2][j]; h3 = V[3][j]; }
-  }
-  double ih = 1.0 / h3;
+  const double ih = 1.0 / h3;
   X[0] = h0 * ih; X[1] = h1 * ih; X[2] = h2 * ih;
 }
 
@@ -127,13 +130,15 @@ __global__ void __launch_bounds__(128) tri_pair_kernel(const double2* __restrict
 
 // One thread per (frame, keypoint) point. C is a template parameter so the per-camera normalised
 // coordinates stay in registers.
+struct CamPack { double v[MAX_CAMS * CAM_STRIDE]; };   // cameras by value in the kernel parameters (1.5 KB)
+
 template <int C>
 __global__ void __launch_bounds__(128) tri_ring_kernel(const double2* __restrict__ uv, const double* __restrict__ lik,
-                                                       double thresh, int64_t P, const double* __restrict__ cams,
+                                                       double thresh, int64_t P, const __grid_constant__ CamPack cams,
                                                        double* __restrict__ xyz, uint8_t* __restrict__ obs_mask,
                                                        uint8_t* __restrict__ exists) {
   __shared__ double sc[C * CAM_STRIDE];
-  for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[i] = cams[i];
+  for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[i] = cams.v[i];
   __syncthreads();
   int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
