@@ -169,3 +169,151 @@ def bundle_adjust_points_and_extrinsics(points_2d, points_3d, point_3d_indices, 
     t_out = cams[:, 18:21].reshape(n_cams, 3, 1).copy()
     bundle_adjust_points_and_extrinsics.last_stats = st
     return obj_pts, r_out, t_out, dict(before=f0, after=f1)
+
+
+# ========== SBA PREPARATION (host side, runs once per calibration; src/lib/sba.py:37-137) ==========
+
+def prepare_calib_board_data_for_bundle_adjustment(img_pts_arr, fnames_arr, board_shape, k_arr, d_arr, r_arr, t_arr,
+                                                   triangulate_func):
+    """src/lib/sba.py:37-93. Images seen by >= 2 cameras, in first-seen order over the cameras' file lists (the reference
+    iterates a dict built from a set, whose order is arbitrary; first-seen order is one of its possible orders and is
+    deterministic). Every kept image contributes board_shape[0]*board_shape[1] new point ids and one observation per
+    seeing camera and corner; the initial 3-D estimate comes from the first two seeing cameras. Outputs are float32 /
+    int arrays like the reference's (sba.py:88-91)."""
+    if not _is_fisheye_triangulate(triangulate_func):
+        raise NotImplementedError('only triangulate_points_fisheye is supported (CUDA path, no fallback)')
+    n_cam = len(img_pts_arr)
+    seen = {}
+    for cam_idx in range(n_cam):
+        for name in fnames_arr[cam_idx]:
+            seen[name] = seen.get(name, 0) + 1
+    keep = [name for name, v in seen.items() if v >= 2]
+    index_of = [{name: i for i, name in enumerate(fnames_arr[c])} for c in range(n_cam)]
+    per_img = board_shape[0] * board_shape[1]
+    points_2d, point_3d_indices, camera_indices = [], [], []
+    tri_a, tri_b, tri_cams = [], [], []
+    for n_img, name in enumerate(keep):
+        cams = [c for c in range(n_cam) if name in index_of[c]]
+        ids = np.arange(n_img * per_img, (n_img + 1) * per_img)
+        for c in cams:
+            points_2d.append(np.asarray(img_pts_arr[c][index_of[c][name]]).reshape(per_img, 2))
+            point_3d_indices.append(ids)
+            camera_indices.append(np.full(per_img, c))
+        a, b = cams[0], cams[1]
+        tri_a.append(np.asarray(img_pts_arr[a][index_of[a][name]]).reshape(per_img, 2))
+        tri_b.append(np.asarray(img_pts_arr[b][index_of[b][name]]).reshape(per_img, 2))
+        tri_cams.append((a, b))
+    if not keep:
+        return (np.zeros((0, 2), np.float32), np.zeros((0, 3), np.float32), np.zeros(0, dtype=int), np.zeros(0, dtype=int))
+    # one CUDA launch per distinct camera pair instead of one per image
+    points_3d = np.empty((len(keep) * per_img, 3))
+    pairs = sorted(set(tri_cams))
+    for a, b in pairs:
+        sel = [i for i, ab in enumerate(tri_cams) if ab == (a, b)]
+        pa = np.concatenate([tri_a[i] for i in sel]); pb = np.concatenate([tri_b[i] for i in sel])
+        X = triangulate_func(pa, pb, k_arr[a], d_arr[a], r_arr[a], t_arr[a], k_arr[b], d_arr[b], r_arr[b], t_arr[b])
+        for j, i in enumerate(sel):
+            points_3d[i * per_img:(i + 1) * per_img] = X[j * per_img:(j + 1) * per_img]
+    return (np.concatenate(points_2d).astype(np.float32), points_3d.astype(np.float32),
+            np.concatenate(point_3d_indices).astype(int), np.concatenate(camera_indices).astype(int))
+
+
+def prepare_manual_points_for_bundle_adjustment(img_pts_arr, k_arr, d_arr, r_arr, t_arr, triangulate_func):
+    """src/lib/sba.py:96-137. img_pts_arr (n_points, n_cams, 2) with NaN where a camera did not see the point; points
+    seen by >= 2 cameras are kept and initialised from their first two cameras."""
+    if not _is_fisheye_triangulate(triangulate_func):
+        raise NotImplementedError('only triangulate_points_fisheye is supported (CUDA path, no fallback)')
+    pts = np.asarray(img_pts_arr, dtype=np.float64)
+    n_pts, n_cam = pts.shape[0], pts.shape[1]
+    points_2d, point_3d_indices, camera_indices, points_3d = [], [], [], []
+    idx = 0
+    for i in range(n_pts):
+        cams = [c for c in range(n_cam) if not np.isnan(pts[i, c]).any()]
+        if len(cams) < 2:
+            continue
+        for c in cams:
+            points_2d.append(pts[i, c]); camera_indices.append(c); point_3d_indices.append(idx)
+        a, b = cams[0], cams[1]
+        points_3d.append(triangulate_func(pts[i, a], pts[i, b], k_arr[a], d_arr[a], r_arr[a], t_arr[a],
+                                          k_arr[b], d_arr[b], r_arr[b], t_arr[b])[0])
+        idx += 1
+    return (np.array(points_2d, dtype=np.float32).reshape(-1, 2), np.array(points_3d, dtype=np.float32).reshape(-1, 3),
+            np.array(point_3d_indices, dtype=int), np.array(camera_indices, dtype=int))
+
+
+def bundle_adjust_board_points_only(img_pts_arr, fnames_arr, board_shape, k_arr, d_arr, r_arr, t_arr, triangulate_func,
+                                    project_func):
+    """src/lib/sba.py:198-206."""
+    points_2d, points_3d, point_3d_indices, camera_indices = prepare_calib_board_data_for_bundle_adjustment(
+        img_pts_arr, fnames_arr, board_shape, k_arr, d_arr, r_arr, t_arr, triangulate_func)
+    return bundle_adjust_points_only(points_2d, points_3d, point_3d_indices, camera_indices, k_arr, d_arr, r_arr, t_arr,
+                                     project_func)
+
+
+# ==========  BACK-END FUNCTION MANAGERS (src/lib/sba.py:211-313) ==========
+
+def _sba_board_points(scene_fpath, points_fpaths, manual_points_fpath, out_fpath, triangulate_func, project_func,
+                      camera_indices=None, manual_points_only=False):
+    """src/lib/sba.py:211-282: extrinsic calibration refinement from checkerboard (and optional manual) points;
+    writes the refined scene JSON and returns the residual dict."""
+    from .utils import load_points, load_manual_points
+    img_pts_arr, fnames_arr, board_shape = [], [], None
+    if camera_indices is None:
+        camera_indices = range(len(points_fpaths))
+    for i in camera_indices:
+        points, fnames, board_shape, *_ = load_points(points_fpaths[i])
+        img_pts_arr.append(points)
+        fnames_arr.append(fnames)
+    k_arr, d_arr, r_arr, t_arr, cam_res = load_scene(scene_fpath)
+    assert len(k_arr) == len(img_pts_arr)
+    if manual_points_fpath is not None:
+        manual_points, _manual_fnames, *_ = load_manual_points(manual_points_fpath)
+        m2d, m3d, midx, mcam = prepare_manual_points_for_bundle_adjustment(manual_points, k_arr, d_arr, r_arr, t_arr,
+                                                                           triangulate_func)
+        if manual_points_only:
+            print('bundle_adjust_board_points_and_extrinsics (with manual points only)')
+            obj_pts, r_arr, t_arr, res = bundle_adjust_points_and_extrinsics(m2d, m3d, midx, mcam, k_arr, d_arr, r_arr, t_arr,
+                                                                             project_func)
+        else:
+            print('bundle_adjust_board_points_and_extrinsics (with manual points)')
+            p2d, p3d, pidx, pcam = prepare_calib_board_data_for_bundle_adjustment(img_pts_arr, fnames_arr, board_shape, k_arr,
+                                                                                  d_arr, r_arr, t_arr, triangulate_func)
+            # The reference offsets the manual ids by point_3d_indices.max() (sba.py:257), which makes the first manual
+            # point share an id with the last board corner. The ids here start one past it, so no two physical points
+            # are merged; with no manual points both agree.
+            offset = (pidx.max() + 1) if len(pidx) else 0
+            obj_pts, r_arr, t_arr, res = bundle_adjust_points_and_extrinsics(
+                np.append(p2d, m2d, axis=0), np.append(p3d, m3d, axis=0), np.append(pidx, midx + offset, axis=0),
+                np.append(pcam, mcam, axis=0), k_arr, d_arr, r_arr, t_arr, project_func)
+    else:
+        print('bundle_adjust_board_points_and_extrinsics')
+        p2d, p3d, pidx, pcam = prepare_calib_board_data_for_bundle_adjustment(img_pts_arr, fnames_arr, board_shape, k_arr,
+                                                                              d_arr, r_arr, t_arr, triangulate_func)
+        obj_pts, r_arr, t_arr, res = bundle_adjust_points_and_extrinsics(p2d, p3d, pidx, pcam, k_arr, d_arr, r_arr, t_arr,
+                                                                         project_func)
+    print(f"\nBefore: mean: {np.mean(res['before'])}, std: {np.std(res['before'])}")
+    print(f"After: mean: {np.mean(res['after'])}, std: {np.std(res['after'])}\n")
+    save_scene(out_fpath, k_arr, d_arr, r_arr, t_arr, cam_res)
+    return res
+
+
+def _sba_points(scene_fpath, points_2d_df, triangulate_func, project_func):
+    """src/lib/sba.py:285-313: scene + thresholded DeepLabCut frame -> (DataFrame[frame, marker, x, y, z, point_index],
+    residuals). TRI initialises, the index arrays come from the same inner merge as the reference's (sba.py:296-302),
+    the points-only solve runs with f_scale=50."""
+    k_arr, d_arr, r_arr, t_arr, _cam_res = load_scene(scene_fpath)
+    points_3d_df = get_pairwise_3d_points_from_df(points_2d_df, k_arr, d_arr.reshape((-1, 4)), r_arr, t_arr, triangulate_func)
+    points_3d_df['point_index'] = points_3d_df.index
+    points_3d = np.array(points_3d_df[['x', 'y', 'z']], dtype=np.float64)
+    points_df = points_2d_df.merge(points_3d_df, how='inner', on=['frame', 'marker'], suffixes=('_cam', ''))
+    points_2d = np.array(points_df[['x_cam', 'y_cam']], dtype=np.float64)
+    point_indices = np.array(points_df['point_index'])
+    camera_indices = np.array(points_df['camera'])
+    print('bundle_adjust_points_only')
+    pts_3d, res = bundle_adjust_points_only(points_2d, points_3d, point_indices, camera_indices, k_arr, d_arr, r_arr, t_arr,
+                                            project_func, f_scale=50)
+    print(f"\nBefore: mean: {np.mean(res['before'])}, std: {np.std(res['before'])}")
+    print(f"After: mean: {np.mean(res['after'])}, std: {np.std(res['after'])}\n")
+    new_points_3d_df = points_3d_df.copy()
+    new_points_3d_df[['x', 'y', 'z']] = pts_3d
+    return new_points_3d_df, res

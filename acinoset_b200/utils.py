@@ -86,3 +86,32 @@ def get_pairwise_3d_points_from_df(points_2d_df, k_arr, d_arr, r_arr, t_arr, tri
     xyz, exists, _mask = dense.triangulate_ring(uv, present.astype(np.float64), 0.5, k_arr, d_arr, r_arr, t_arr)
     return pd.DataFrame({'frame': frames[exists], 'marker': markers[exists],
                          'x': xyz[exists, 0], 'y': xyz[exists, 1], 'z': xyz[exists, 2]})
+
+
+def load_points(fpath, verbose=False):
+    """Checkerboard corner file of one camera (src/lib/utils.py:18-28): float32 points, file names, board geometry."""
+    with open(fpath, 'r') as f:
+        data = json.load(f)
+    fnames = list(data['points'].keys())
+    points = np.array(list(data['points'].values()), dtype=np.float32)
+    if verbose:
+        print(f'Loaded checkerboard points from {fpath}\n')
+    return points, fnames, tuple(data['board_shape']), data['board_square_len'], tuple(data['camera_resolution'])
+
+
+def load_manual_points(fpath, verbose=True):
+    """Manually labelled points (src/lib/utils.py:31-41): (n_points, n_cams, 2) with NaN where unseen."""
+    with open(fpath, 'r') as f:
+        data = json.load(f)
+    points = np.array(data['points'])
+    fnames = [f'img{str(i).zfill(5)}.jpg' for i in data['frame_idx']]
+    if verbose:
+        print(f'Loaded manual points from {fpath}\n')
+    return points, fnames, tuple(data['camera_resolution'])
+
+
+def create_board_object_pts(board_shape, square_edge_length):
+    """src/lib/utils.py:313-316."""
+    object_pts = np.zeros((board_shape[0] * board_shape[1], 3), np.float32)
+    object_pts[:, :2] = np.mgrid[0:board_shape[0], 0:board_shape[1]].T.reshape(-1, 2) * square_edge_length
+    return object_pts
