@@ -186,41 +186,60 @@ def nccl_unique_id() -> bytes:
     return buf.raw
 
 
+class ScenePipeline:
+    """core.tri + core.sba on host buffers with the device allocations (and the NCCL communicator) kept across calls:
+    upload observations and likelihoods, threshold + ring triangulation (K2), SBA solve, download the points
+    (src/core/tri.py:41-47, src/core/sba.py:41-43). With ``comm=(unique_id, rank, world)`` every rank holds a frame shard
+    and ``run`` is collective."""
+
+    def __init__(self, n_points, n_cams, k_arr, d_arr, r_arr, t_arr, mode=MODE_POINTS_ONLY, comm=None):
+        _capi.require_gpu()
+        self.P, self.C, self.mode = int(n_points), int(n_cams), mode
+        self.cam_args = (k_arr, d_arr, r_arr, t_arr)
+        self.cams = _capi.pack_cams(k_arr, d_arr, r_arr, t_arr)
+        self.uv_d = DeviceArray((self.P, self.C, 2), np.float64)
+        self.lik_d = DeviceArray((self.P, self.C), np.float64)
+        self.xyz_d = DeviceArray((self.P, 3), np.float64)
+        self.mask_d = DeviceArray((self.P,), np.uint8)
+        self.ex_d = DeviceArray((self.P,), np.uint8)
+        self.solver = SbaSolver(self.C, self.P)
+        self.solver.set_observations_dev(self.uv_d, self.mask_d)
+        if comm is not None and comm[2] > 1:
+            self.solver.comm_init(*comm)
+
+    def run(self, uv, lik, thresh, out_points=None, rvec_t0=None, **solver_opts):
+        L = _capi.lib()
+        self.uv_d.upload(uv)
+        self.lik_d.upload(lik)
+        _capi.check(L.acino_triangulate_ring_dev(self.uv_d.ptr, self.lik_d.ptr, float(thresh), self.P, self.C,
+                                                 _capi.ptr(self.cams), self.xyz_d.ptr, self.mask_d.ptr, self.ex_d.ptr,
+                                                 ct.c_void_p(self.solver.stream)))
+        self.solver.set_cameras(*self.cam_args)
+        if self.mode == MODE_POINTS_AND_EXTRINSICS and rvec_t0 is not None and rvec_t0[0] is not None:
+            self.solver.set_rvec_t(rvec_t0[0], rvec_t0[1])
+        self.solver.set_points_dev(self.xyz_d)
+        st = self.solver.solve(default_opts(self.mode, **solver_opts))
+        if out_points is None:
+            out_points = np.empty((self.P, 3))
+        _capi.check(L.acino_sba_get_points(self.solver._h, _capi.ptr(out_points)))
+        st['points'] = out_points
+        return st
+
+    def close(self):
+        self.solver.close()
+        for a in (self.uv_d, self.lik_d, self.xyz_d, self.mask_d, self.ex_d):
+            a.free()
+
+
 def solve_scene_host(uv, lik, thresh, k_arr, d_arr, r_arr, t_arr, mode=MODE_POINTS_ONLY, out_points=None, rvec_t0=None,
                      **solver_opts):
-    """Whole pipeline on host buffers (what core.tri + core.sba do, src/core/tri.py:41-47, src/core/sba.py:41-43):
-    upload observations and likelihoods, threshold + ring triangulation (K2), SBA solve, download the points.
-    Returns the solver statistics; absent points are NaN rows of ``out_points``."""
-    _capi.require_gpu()
+    """One-shot ScenePipeline: returns the solver statistics; absent points are NaN rows of ``st['points']``."""
     uv = _capi.f64(uv)
-    P, C = uv.shape[0], uv.shape[1]
-    lik = _capi.f64(lik).reshape(P, C)
-    cams = _capi.pack_cams(k_arr, d_arr, r_arr, t_arr)
-    L = _capi.lib()
-    uv_d = DeviceArray.from_host(uv)
-    lik_d = DeviceArray.from_host(lik)
-    xyz_d = DeviceArray((P, 3), np.float64)
-    mask_d = DeviceArray((P,), np.uint8)
-    ex_d = DeviceArray((P,), np.uint8)
-    solver = SbaSolver(C, P)
+    pipe = ScenePipeline(uv.shape[0], uv.shape[1], k_arr, d_arr, r_arr, t_arr, mode)
     try:
-        _capi.check(L.acino_triangulate_ring_dev(uv_d.ptr, lik_d.ptr, float(thresh), P, C, _capi.ptr(cams), xyz_d.ptr,
-                                                 mask_d.ptr, ex_d.ptr, ct.c_void_p(solver.stream)))
-        solver.set_cameras(k_arr, d_arr, r_arr, t_arr)
-        if mode == MODE_POINTS_AND_EXTRINSICS and rvec_t0 is not None and rvec_t0[0] is not None:
-            solver.set_rvec_t(rvec_t0[0], rvec_t0[1])
-        solver.set_observations_dev(uv_d, mask_d)
-        solver.set_points_dev(xyz_d)
-        st = solver.solve(default_opts(mode, **solver_opts))
-        if out_points is None:
-            out_points = np.empty((P, 3))
-        _capi.check(L.acino_sba_get_points(solver._h, _capi.ptr(out_points)))
-        st['points'] = out_points
+        return pipe.run(uv, lik, thresh, out_points, rvec_t0, **solver_opts)
     finally:
-        solver.close()
-        for a in (uv_d, lik_d, xyz_d, mask_d, ex_d):
-            a.free()
-    return st
+        pipe.close()
 
 
 def fp64_peak_tflops():
@@ -229,3 +248,12 @@ def fp64_peak_tflops():
     v = ct.c_double()
     _capi.check(_capi.lib().acino_fp64_peak(ct.byref(v)))
     return v.value
+
+
+def frame_shard(n_frames, rank, world):
+    """Contiguous, balanced frame range [start, stop) of ``rank`` (observations shard by frame)."""
+    if not (0 <= rank < world):
+        raise ValueError('rank outside the world')
+    base, extra = divmod(int(n_frames), int(world))
+    start = rank * base + min(rank, extra)
+    return start, start + base + (1 if rank < extra else 0)

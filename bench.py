@@ -38,8 +38,8 @@ UNIT = 'LM iterations/s (119,490-frame scene equivalents)'
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=50)
-    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--impl', default='native', choices=['native', 'reference'])
     ap.add_argument('--mode', default='auto', choices=['auto', 'points', 'extrinsics'])
     ap.add_argument('--frames', type=int, default=C4_FRAMES, help='frames per GPU shard')
@@ -67,7 +67,7 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
         self.p = None
         try:
-            self.p = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits', '-lms', '100',
+            self.p = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits', '-lms', '50',
                                        '-i', str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
@@ -192,7 +192,7 @@ def native_arm(args):
 
     m = _capi.MODE_POINTS_AND_EXTRINSICS if mode == 'extrinsics' else _capi.MODE_POINTS_ONLY
     # full solve from the TRI initialisation (solve ms, iterations to converge)
-    st_solve = solver.solve(dense.default_opts(m))
+    st_solve = solver.solve(dense.default_opts(m, **(dict(ftol=1e-10) if mode == 'extrinsics' else {})))
     # fixed-work LM iterations for the throughput number: every point does a full iteration each step
     solver.reset_state()
     opts = dense.default_opts(m, inner_iters=1, force_iters=1)
@@ -202,12 +202,12 @@ def native_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    clocks = ClockSampler(local) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
         solver.iterate(opts)
     if mode == 'extrinsics':
         solver.profile(True)          # CUDA events around K4 / K6 on the solver's stream, inside the timed region
     barrier()
-    clocks = ClockSampler(local) if rank == 0 else None
     e0, e1 = ev(), ev()
     e0.record(stream)
     for _ in range(args.steps):
@@ -244,49 +244,79 @@ def HAVE_SCHUR():
 
 
 def e2e_arm(args, ctx):
-    """Full solves through the host-buffer API: pinned host observations -> HBM -> TRI -> solve -> host points.
-    Every solve uploads its inputs and downloads its result inside the timed region."""
+    """Full solves through the host-buffer API (dense.ScenePipeline): pinned host observations -> HBM -> TRI -> solve ->
+    host points. Every solve uploads its inputs and downloads its result inside the timed region; at N > 1 every rank
+    feeds its own frame shard and the solve is collective (NCCL allreduce of the reduced camera system)."""
     import torch
-    from acinoset_b200 import _capi, dense
-    sc, P, C = ctx['sc'], ctx['P'], ctx['C']
+    import torch.distributed as dist
+    from acinoset_b200 import dense
+    sc, P, C, world, rank = ctx['sc'], ctx['P'], ctx['C'], ctx['world'], ctx['rank']
     k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
     uv_h = torch.from_numpy(sc['uv']).pin_memory()
     lik_h = torch.from_numpy(sc['lik']).pin_memory()
     out_h = torch.empty((P, 3), dtype=torch.float64).pin_memory()
-    m = ctx['m']
-    iters = 0
-    times = []
+    comm = None
+    if world > 1 and ctx['mode'] == 'extrinsics':
+        uid = [dense.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        comm = (uid[0], rank, world)
+    pipe = dense.ScenePipeline(P, C, k, d, r, t, ctx['m'], comm)
+    rv0 = (ctx.get('rv'), ctx.get('tv')) if ctx['mode'] == 'extrinsics' else None
+    # the reference's own stopping literal for this mode (src/lib/sba.py:170-173 ftol=1e-10); points-only keeps its defaults
+    opts = dict(ftol=1e-10) if ctx['mode'] == 'extrinsics' else {}
+    iters, times, last = 0, [], None
     for i in range(args.e2e_solves + 1):
+        if world > 1:
+            dist.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        st = dense.solve_scene_host(uv_h.numpy(), lik_h.numpy(), THRESH, k, d, r, t, mode=m, out_points=out_h.numpy(),
-                                    rvec_t0=(ctx.get('rv'), ctx.get('tv')) if ctx['mode'] == 'extrinsics' else None)
+        last = pipe.run(uv_h.numpy(), lik_h.numpy(), THRESH, out_h.numpy(), rv0, **opts)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         if i > 0:                     # first solve is the warm-up
             times.append(dt)
-            iters += st['iterations']
+            iters += last['iterations']
+    pipe.close()
+    total = float(np.sum(times))
+    if world > 1:
+        tt = torch.tensor([total], device='cuda', dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total = float(tt.item())
     h2d = uv_h.numel() * 8 + lik_h.numel() * 8
     d2h = out_h.numel() * 8
-    total = float(np.sum(times))
-    return dict(value=iters / total, unit=UNIT, step='one full solve: H2D observations+likelihoods, TRI, LM to convergence, D2H points',
-                solve_ms=1e3 * total / len(times), lm_iters_per_solve=iters / len(times),
+    return dict(value=world * iters / total, unit=UNIT,
+                step='one full solve per GPU shard: H2D observations+likelihoods, TRI, LM until the stopping rule, D2H points',
+                solve_ms=1e3 * total / len(times), lm_iters_per_solve=iters / len(times), exit_status=last.get('status'),
+                cost_initial=last['cost_initial'], cost_final=last['cost_final'],
                 h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h))
 
 
 def cpu_baseline(frames, mode, full_obs):
-    """The reference's CPU algorithm (oracle/ref_port.py) on a bounded sample; scaled linearly in observations to
-    the bench workload (the per-observation Python/OpenCV loop is exactly linear)."""
+    """The reference's CPU algorithm (oracle/ref_port.py) on a bounded sample; scaled linearly in observations to the
+    bench workload (the per-observation Python/OpenCV loop is exactly linear, SURVEY.md §6, and the number of finite-
+    difference column groups per Jacobian does not depend on the scene size)."""
     from oracle import ref_port
-    sc = make_shard(frames, seed=4)
     t0 = time.perf_counter()
-    out = ref_port.sba_points_scene(sc['uv'], sc['lik'], THRESH, sc['k'], sc['d'], sc['r'], sc['t'], f_scale=50.0)
+    if mode == 'extrinsics':
+        frames = max(2, min(frames, 10))
+        sc = make_shard(frames, seed=4)
+        rng = np.random.default_rng(100)
+        from acinoset_b200 import synth
+        r0 = np.array([sc['r'][c] @ synth._rot_from_axis_angle(rng.normal(0, 8e-4, 3)) for c in range(N_CAMS)])
+        t0_ = sc['t'] + rng.normal(0, 3e-3, sc['t'].shape)
+        out = ref_port.sba_extrinsics_scene(sc['uv'], sc['lik'], THRESH, sc['k'], sc['d'], r0, t0_)
+        what = ('points+extrinsics SBA (reference algorithm with the layout-consistent sparsity pattern, SURVEY.md F6; '
+                'bounded at 25 nfev)')
+    else:
+        sc = make_shard(frames, seed=4)
+        out = ref_port.sba_points_scene(sc['uv'], sc['lik'], THRESH, sc['k'], sc['d'], sc['r'], sc['t'], f_scale=50.0)
+        what = 'points-only SBA'
     dt = time.perf_counter() - t0
-    its_per_s_sample = out['iterations'] / out['sba_seconds']
+    its_per_s_sample = max(out['iterations'], 1) / out['sba_seconds']
     scale = out['n_obs'] / float(full_obs)
     return dict(value=its_per_s_sample * scale, unit=UNIT, cores=1, kind='port',
                 sample=(f'{frames} frames x 20 kpts x 6 cams ({out["n_obs"]} observations, {out["n_points"]} points): '
-                        f'TRI {out["tri_seconds"]:.2f} s, points-only SBA {out["sba_seconds"]:.2f} s, {out["iterations"]} TRF iterations, '
+                        f'{what} {out["sba_seconds"]:.2f} s, {out["iterations"]} TRF iterations, '
                         f'{out["nfev"]} nfev, {out["cost_calls"]} cost-function sweeps; iterations/s scaled by observations '
                         f'({out["n_obs"]}/{int(full_obs)}) to the bench workload'),
                 host_cpus=os.cpu_count(), sample_seconds=dt, sample_iters_per_s=its_per_s_sample,
@@ -302,15 +332,17 @@ def main():
         full_obs = args.frames * N_KPTS * N_CAMS * 0.42     # kept observations of existing points at thresh 0.5 (measured ratio)
         vals = []
         cb = None
-        for i in range(max(1, min(args.steps, 3))):
-            cb = cpu_baseline(args.cpu_frames, 'points', full_obs)
+        mode = 'points' if args.mode == 'points' else 'extrinsics'
+        for i in range(max(1, min(args.steps, 2))):
+            cb = cpu_baseline(args.cpu_frames, mode, full_obs)
             vals.append(cb['value'])
         v = float(np.median(vals))
         cb['value'] = v
         line = dict(impl='reference', metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=len(vals), warmup=0,
                     ms_per_step=1e3 / v, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f64',
-                    data='synthetic', config=dict(workload=f'C4 points-only SBA: {args.frames} frames x 20 keypoints x 6 cameras, dlc_thresh 0.5',
-                                                  note='reference CPU algorithm, single-threaded as in the reference'),
+                    data='synthetic', config=dict(workload=f'C4 {"points+extrinsics (Schur)" if mode == "extrinsics" else "points-only"} SBA: '
+                                                           f'{args.frames} frames x 20 keypoints x 6 cameras per GPU, dlc_thresh 0.5, 1 px noise',
+                                                  mode=mode, note='reference CPU algorithm, single-threaded as in the reference'),
                     cpu_baseline=cb, e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
         print(json.dumps(line))
         return
@@ -321,6 +353,8 @@ def main():
     mode, P, C = ctx['mode'], ctx['P'], ctx['C']
     e2e = e2e_arm(args, ctx)
     if rank != 0:
+        import torch.distributed as dist
+        dist.destroy_process_group()
         return
     n_obs, n_pts = ctx['n_obs'], ctx['n_pts']
     if mode == 'points':
@@ -363,6 +397,9 @@ def main():
                 tri=dict(ms=ctx['tri_ms'], points_per_s=P / (ctx['tri_ms'] * 1e-3), gbs=tri_gbs, frac_hbm=tri_gbs / peak,
                          algorithmic_bytes=tri_bytes(P, C)))
     print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
 
 
 if __name__ == '__main__':

@@ -181,3 +181,21 @@ def sba_points_scene(uv, lik, thresh, k_arr, d_arr, r_arr, t_arr, f_scale=50.0, 
     return dict(points=X, frame=p3['frame'].to_numpy(), marker=p3['marker'].to_numpy(), residuals=res, n_obs=len(pidx),
                 n_points=len(X0), tri_seconds=t_tri, sba_seconds=info['seconds'], iterations=info['njev'], nfev=info['nfev'],
                 cost_calls=info['cost_calls'], cost=info['cost'], pidx=pidx, cidx=cidx, obs=obs, X0=X0)
+
+
+def sba_extrinsics_scene(uv, lik, thresh, k_arr, d_arr, r0, t0, n_kpts=20, layout='consistent', max_nfev=25):
+    """bundle_adjust_points_and_extrinsics (src/lib/sba.py:158-178) fed with DLC-derived arrays: threshold,
+    TRI, index merge, then the points+extrinsics solve. ``layout='consistent'`` uses the sparsity pattern that matches the
+    parameter layout (the as-shipped pattern stalls at once); ``max_nfev`` bounds the sample — the rate
+    (TRF iterations per second) is what the caller wants, not convergence."""
+    from acinoset_b200 import synth
+    df = synth.dense_to_df(uv, lik, n_kpts)
+    df = df[df['likelihood'] > thresh]
+    p3 = ring_triangulate_df(df, k_arr, d_arr, r0, t0)
+    obs, X0, pidx, cidx = observation_lists(df, p3)
+    n = len(k_arr)
+    X, R, T, res, info = bundle_adjust_points_and_extrinsics(obs, X0, pidx, cidx, k_arr, np.asarray(d_arr).reshape(n, 4, 1),
+                                                             np.asarray(r0), np.asarray(t0).reshape(n, 3, 1), layout=layout,
+                                                             max_nfev=max_nfev)
+    return dict(points=X, r=R, t=T, residuals=res, n_obs=len(pidx), n_points=len(X0), sba_seconds=info['seconds'],
+                iterations=info['njev'], nfev=info['nfev'], cost_calls=info['cost_calls'], cost=info['cost'])
