@@ -143,8 +143,9 @@ struct SchurSmem {
   static constexpr int NU = rcs_units(C);
   static constexpr int NW = BT / 32;
   static constexpr int LEN = rcs_len(C);
-  static constexpr size_t n_doubles = (size_t)C * CAM_STRIDE + (size_t)C * 8 * BT + 12 * BT + LEN;
-  static constexpr size_t bytes = n_doubles * 8 + (size_t)NU * BT * 2 + (size_t)NU * NW * 4 + NU * 4 + 16 + NU * 2;
+  static constexpr int BS = BT + 1;       // row stride of the staged arrays (odd: spreads the per-observation writes over banks)
+  static constexpr size_t n_doubles = (size_t)C * CAM_STRIDE + (size_t)C * 8 * BS + 12 * BS + LEN;
+  static constexpr size_t bytes = n_doubles * 8 + (size_t)NU * BT * 2 + (size_t)C * BT * 2 + NW * 4 + 16 + NU * 2 + BT + 16;
 };
 
 template <int C>
@@ -155,26 +156,28 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
                    const SchurLm* __restrict__ lm, SchurParams prm,
                    double* __restrict__ rcs_partial, double* __restrict__ max_partial) {
   using L = SchurSmem<C>;
-  constexpr int BT = L::BT, NU = L::NU, NW = L::NW, LEN = L::LEN;
+  constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sc = reinterpret_cast<double*>(smem_raw);
-  double* sN = sc + C * CAM_STRIDE;          // [(c*6+k)*BT + q]
-  double* sE = sN + (size_t)C * 6 * BT;      // [(c*2+k)*BT + q]
-  double* sX = sE + (size_t)C * 2 * BT;      // [k*BT + q], k<3
-  double* sVi = sX + 3 * BT;                 // [k*BT + q], k<6: 00 01 02 11 12 22
-  double* sH = sVi + 6 * BT;                 // [k*BT + q], k<3
-  double* sS = sH + 3 * BT;                  // [LEN]
-  unsigned short* list = reinterpret_cast<unsigned short*>(sS + LEN);   // [u*BT + i]
-  int* cnt = reinterpret_cast<int*>(list + (size_t)NU * BT);            // [u*NW + w]
-  int* unit_n = cnt + NU * NW;                                          // [u]
-  int* next_unit = unit_n + NU;                                         // [1] (+3 pad)
+  double* sN = sc + C * CAM_STRIDE;          // [(c*6+k)*BS + q]
+  double* sE = sN + (size_t)C * 6 * BS;      // [(c*2+k)*BS + q]
+  double* sX = sE + (size_t)C * 2 * BS;      // [k*BS + q], k<3
+  double* sVi = sX + 3 * BS;                 // [k*BS + q], k<6: 00 01 02 11 12 22
+  double* sH = sVi + 6 * BS;                 // [k*BS + q], k<3
+  double* sS = sH + 3 * BS;                  // [LEN]
+  unsigned short* list = reinterpret_cast<unsigned short*>(sS + LEN);   // [u*BT + i] points of unit u
+  unsigned short* olist = list + (size_t)NU * BT;                       // [i] observations of the tile: q*8 + c
+  int* wtot = reinterpret_cast<int*>(olist + (size_t)C * BT);           // [w] observations per warp
+  int* next_unit = wtot + NW;                                           // [0] unit counter, [1] observations in the tile
   unsigned char* u_c = reinterpret_cast<unsigned char*>(next_unit + 4); // [u] first camera
   unsigned char* u_cp = u_c + NU;                                       // [u] second camera
+  unsigned char* sM = u_cp + NU;                                        // [q] observation masks of the tile
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
   const int cur = lm->cur;
   const double lam = lm->lambda;
+  const bool need_cost = (lm->iter == 0);   // later iterations inherit the cost from the accepted trial evaluation (K6/K7)
   const double* __restrict__ cams = cur ? cams1 : cams0;
   const double* __restrict__ Xp = cur ? X1 : X0;
 
@@ -191,63 +194,82 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0;
   const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    // ---------------- phase 1
+    // ---------------- phase 1a: stage the points, compact the tile's observations (point-major, camera-minor)
     const int64_t p = tile * BT + tid;
     unsigned m = (p < P) ? obs_mask[p] : 0u;
+    sM[tid] = (unsigned char)m;
+    {
+      if (m) {
+        double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
+        sX[tid] = X; sX[BS + tid] = Y; sX[2 * BS + tid] = Z;
+        xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
+      }
+      int k = __popc(m), incl = k;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (lane == 31) wtot[warp] = incl;
+      __syncthreads();
+      int base = incl - k;
+      for (int w = 0; w < warp; ++w) base += wtot[w];
+      unsigned mm = m;
+      while (mm) {
+        int c = __ffs(mm) - 1;
+        mm &= mm - 1;
+        olist[base++] = (unsigned short)(tid * 8 + c);
+      }
+      if (tid == BT - 1) next_unit[1] = base;
+      __syncthreads();
+    }
+    // ---------------- phase 1b: one thread per observation: residual, Jacobian rows, robust weights
+    {
+      const int n_obs = next_unit[1];
+      for (int i = tid; i < n_obs; i += BT) {
+        const int e = olist[i], q = e >> 3, c = e & 7;
+        const int64_t pq = tile * BT + q;
+        double2 ob = uv[pq * C + c];
+        double pm1 = 0.0;
+        ObsLin o = linearise_obs(sc + c * CAM_STRIDE, sX[q], sX[BS + q], sX[2 * BS + q], ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
+        double* n = sN + (size_t)(c * 6) * BS + q;
+        n[0] = o.n0[0]; n[BS] = o.n0[1]; n[2 * BS] = o.n0[2];
+        n[3 * BS] = o.n1[0]; n[4 * BS] = o.n1[1]; n[5 * BS] = o.n1[2];
+        sE[(size_t)(c * 2) * BS + q] = o.e0;
+        sE[(size_t)(c * 2 + 1) * BS + q] = o.e1;
+        if (need_cost) cost_acc += prm.half_c2 * log1p(pm1);
+      }
+      __syncthreads();
+    }
+    // ---------------- phase 1c: one thread per point: V, g from the staged rows, damped inverse
     if (m) {
-      double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
-      double pm1 = 0.0;
       double g0 = 0, g1 = 0, g2 = 0, v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0;
-#pragma unroll 1
+#pragma unroll
       for (int c = 0; c < C; ++c) {
         if (m >> c & 1) {
-          double2 ob = uv[p * C + c];
-          ObsLin o = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
-          double* n = sN + (size_t)(c * 6) * BT + tid;
-          n[0] = o.n0[0]; n[BT] = o.n0[1]; n[2 * BT] = o.n0[2];
-          n[3 * BT] = o.n1[0]; n[4 * BT] = o.n1[1]; n[5 * BT] = o.n1[2];
-          sE[(size_t)(c * 2) * BT + tid] = o.e0;
-          sE[(size_t)(c * 2 + 1) * BT + tid] = o.e1;
-          g0 = fma(o.n0[0], o.e0, fma(o.n1[0], o.e1, g0));
-          g1 = fma(o.n0[1], o.e0, fma(o.n1[1], o.e1, g1));
-          g2 = fma(o.n0[2], o.e0, fma(o.n1[2], o.e1, g2));
-          v00 = fma(o.n0[0], o.n0[0], fma(o.n1[0], o.n1[0], v00));
-          v01 = fma(o.n0[0], o.n0[1], fma(o.n1[0], o.n1[1], v01));
-          v02 = fma(o.n0[0], o.n0[2], fma(o.n1[0], o.n1[2], v02));
-          v11 = fma(o.n0[1], o.n0[1], fma(o.n1[1], o.n1[1], v11));
-          v12 = fma(o.n0[1], o.n0[2], fma(o.n1[1], o.n1[2], v12));
-          v22 = fma(o.n0[2], o.n0[2], fma(o.n1[2], o.n1[2], v22));
+          const double* n = sN + (size_t)(c * 6) * BS + tid;
+          const double a0 = n[0], a1 = n[BS], a2 = n[2 * BS], b0 = n[3 * BS], b1 = n[4 * BS], b2 = n[5 * BS];
+          const double e0 = sE[(size_t)(c * 2) * BS + tid], e1 = sE[(size_t)(c * 2 + 1) * BS + tid];
+          g0 = fma(a0, e0, fma(b0, e1, g0));
+          g1 = fma(a1, e0, fma(b1, e1, g1));
+          g2 = fma(a2, e0, fma(b2, e1, g2));
+          v00 = fma(a0, a0, fma(b0, b0, v00));
+          v01 = fma(a0, a1, fma(b0, b1, v01));
+          v02 = fma(a0, a2, fma(b0, b2, v02));
+          v11 = fma(a1, a1, fma(b1, b1, v11));
+          v12 = fma(a1, a2, fma(b1, b2, v12));
+          v22 = fma(a2, a2, fma(b2, b2, v22));
         }
       }
       Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
-      sX[tid] = X; sX[BT + tid] = Y; sX[2 * BT + tid] = Z;
-      sVi[tid] = iv.i00; sVi[BT + tid] = iv.i01; sVi[2 * BT + tid] = iv.i02;
-      sVi[3 * BT + tid] = iv.i11; sVi[4 * BT + tid] = iv.i12; sVi[5 * BT + tid] = iv.i22;
+      sVi[tid] = iv.i00; sVi[BS + tid] = iv.i01; sVi[2 * BS + tid] = iv.i02;
+      sVi[3 * BS + tid] = iv.i11; sVi[4 * BS + tid] = iv.i12; sVi[5 * BS + tid] = iv.i22;
       sH[tid] = fma(iv.i00, g0, fma(iv.i01, g1, iv.i02 * g2));
-      sH[BT + tid] = fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
-      sH[2 * BT + tid] = fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
-      cost_acc += prm.half_c2 * log1p(pm1);
+      sH[BS + tid] = fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
+      sH[2 * BS + tid] = fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
       gmax_acc = fmax(gmax_acc, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
-      xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
     }
-    // unit membership counts per warp
-#pragma unroll 1
-    for (int u = 0; u < NU; ++u) {
-      bool in = (m >> u_c[u] & 1) && (m >> u_cp[u] & 1);
-      unsigned b = __ballot_sync(0xffffffffu, in);
-      if (lane == 0) cnt[u * NW + warp] = __popc(b);
-    }
-    if (tid == 0) *next_unit = 0;
-    __syncthreads();
-#pragma unroll 1
-    for (int u = 0; u < NU; ++u) {
-      bool in = (m >> u_c[u] & 1) && (m >> u_cp[u] & 1);
-      unsigned b = __ballot_sync(0xffffffffu, in);
-      int base = 0;
-      for (int w = 0; w < warp; ++w) base += cnt[u * NW + w];
-      if (in) list[(size_t)u * BT + base + __popc(b & ((1u << lane) - 1u))] = (unsigned short)tid;
-      if (tid == BT - 1) unit_n[u] = base + __popc(b);     // last warp, last lane: total
-    }
+    if (tid == 0) next_unit[0] = 0;
     __syncthreads();
     // ---------------- phase 2: warps take units (longest first: diagonal units lead) until none is left
     for (;;) {
@@ -255,25 +277,36 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       if (lane == 0) u = atomicAdd(next_unit, 1);
       u = __shfl_sync(0xffffffffu, u, 0);
       if (u >= NU) break;
-      const int n = unit_n[u];
-      if (n == 0) continue;
       const int c = u_c[u], cp = u_cp[u];
       const bool diag = (c == cp);
+      // the unit's point list: tile points observed by both cameras, in point order (built by this warp alone)
+      unsigned short* lst = list + (size_t)u * BT;
+      int n = 0;
+#pragma unroll 1
+      for (int b0 = 0; b0 < BT; b0 += 32) {
+        const unsigned mq = sM[b0 + lane];
+        const bool in = (mq >> c & 1) && (mq >> cp & 1);
+        const unsigned b = __ballot_sync(0xffffffffu, in);
+        if (in) lst[n + __popc(b & ((1u << lane) - 1u))] = (unsigned short)(b0 + lane);
+        n += __popc(b);
+      }
+      __syncwarp();
+      if (n == 0) continue;
       double acc[RCS_UNIT];
 #pragma unroll
       for (int i = 0; i < RCS_UNIT; ++i) acc[i] = 0.0;
-      const double* nc = sN + (size_t)(c * 6) * BT;
-      const double* ncp = sN + (size_t)(cp * 6) * BT;
-      const double* ec = sE + (size_t)(c * 2) * BT;
+      const double* nc = sN + (size_t)(c * 6) * BS;
+      const double* ncp = sN + (size_t)(cp * 6) * BS;
+      const double* ec = sE + (size_t)(c * 2) * BS;
 #pragma unroll 1
       for (int base = 0; base < n; base += 32) {
         if (base + lane < n) {
-          const int q = list[(size_t)u * BT + base + lane];
-          const double X = sX[q], Y = sX[BT + q], Z = sX[2 * BT + q];
-          const double n0x = nc[q], n0y = nc[BT + q], n0z = nc[2 * BT + q];
-          const double n1x = nc[3 * BT + q], n1y = nc[4 * BT + q], n1z = nc[5 * BT + q];
-          const double i00 = sVi[q], i01 = sVi[BT + q], i02 = sVi[2 * BT + q];
-          const double i11 = sVi[3 * BT + q], i12 = sVi[4 * BT + q], i22 = sVi[5 * BT + q];
+          const int q = lst[base + lane];
+          const double X = sX[q], Y = sX[BS + q], Z = sX[2 * BS + q];
+          const double n0x = nc[q], n0y = nc[BS + q], n0z = nc[2 * BS + q];
+          const double n1x = nc[3 * BS + q], n1y = nc[4 * BS + q], n1z = nc[5 * BS + q];
+          const double i00 = sVi[q], i01 = sVi[BS + q], i02 = sVi[2 * BS + q];
+          const double i11 = sVi[3 * BS + q], i12 = sVi[4 * BS + q], i22 = sVi[5 * BS + q];
           double a0[6], a1[6];
           a0[0] = fma(Y, n0z, -Z * n0y); a0[1] = fma(Z, n0x, -X * n0z); a0[2] = fma(X, n0y, -Y * n0x);
           a0[3] = n0x; a0[4] = n0y; a0[5] = n0z;
@@ -301,8 +334,8 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
             for (int i = 0; i < 6; ++i)
 #pragma unroll
               for (int j = i; j < 6; ++j) { acc[k] = fma(a0[i], t0[j], fma(a1[i], t1[j], acc[k])); ++k; }
-            const double e0 = ec[q], e1 = ec[BT + q];
-            const double hx = sH[q], hy = sH[BT + q], hz = sH[2 * BT + q];
+            const double e0 = ec[q], e1 = ec[BS + q];
+            const double hx = sH[q], hy = sH[BS + q], hz = sH[2 * BS + q];
             const double b0 = e0 - fma(n0x, hx, fma(n0y, hy, n0z * hz));
             const double b1 = e1 - fma(n1x, hx, fma(n1y, hy, n1z * hz));
 #pragma unroll
@@ -312,8 +345,8 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
               acc[33 + i] = fma(a0[i], a0[i], fma(a1[i], a1[i], acc[33 + i]));
             }
           } else {
-            const double p0x = ncp[q], p0y = ncp[BT + q], p0z = ncp[2 * BT + q];
-            const double p1x = ncp[3 * BT + q], p1y = ncp[4 * BT + q], p1z = ncp[5 * BT + q];
+            const double p0x = ncp[q], p0y = ncp[BS + q], p0z = ncp[2 * BS + q];
+            const double p1x = ncp[3 * BS + q], p1y = ncp[4 * BS + q], p1z = ncp[5 * BS + q];
             double b0[6], b1[6];
             b0[0] = fma(Y, p0z, -Z * p0y); b0[1] = fma(Z, p0x, -X * p0z); b0[2] = fma(X, p0y, -Y * p0x);
             b0[3] = p0x; b0[4] = p0y; b0[5] = p0z;
@@ -421,8 +454,7 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
     for (int i = 0; i < n; ++i) { dmax = fmax(dmax, D[i]); gm = fmax(gm, fabs(gbar[i])); }
     double flo = fmax(1e-12 * dmax, 1e-300);
     for (int i = 0; i < n; ++i) D[i] = fmax(D[i], flo);
-    lm->F = r[NU * RCS_UNIT];
-    if (lm->iter == 0) lm->F0 = r[NU * RCS_UNIT];
+    if (lm->iter == 0) { lm->F = r[NU * RCS_UNIT]; lm->F0 = r[NU * RCS_UNIT]; }   // K4 evaluates the cost only then
     lm->gmax = gm;
     lm->xmax = smax[1];
     lm->skip = 0;
