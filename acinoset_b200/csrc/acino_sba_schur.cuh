@@ -50,14 +50,14 @@ __device__ __forceinline__ Sym3Inv damped_inverse3(double v00, double v01, doubl
   double flo = fmax(1e-9 * dmax, 1e-300);
   r.D0 = fmax(v00, flo); r.D1 = fmax(v11, flo); r.D2 = fmax(v22, flo);
   double a = fma(lam, r.D0, v00), d = fma(lam, r.D1, v11), f = fma(lam, r.D2, v22);
-  double ia = 1.0 / a;
+  double ia = rcp_nr(a);
   double l10 = v01 * ia, l20 = v02 * ia;
   double d1 = fma(-l10, v01, d);
   double e1 = fma(-l20, v01, v12);
-  double id1 = 1.0 / d1;
+  double id1 = rcp_nr(d1);
   double l21 = e1 * id1;
   double f2 = fma(-l21, e1, fma(-l20, v02, f));
-  double if2 = 1.0 / f2;
+  double if2 = rcp_nr(f2);
   double m20 = fma(l10, l21, -l20);
   r.i22 = if2;
   r.i12 = -l21 * if2;
@@ -80,12 +80,13 @@ __device__ __forceinline__ ObsLin linearise_obs(const double* __restrict__ cam, 
   mul_R(cam, Jv, jv);
   double fu = u - ou, fv = v - ov;
   Robust w = cauchy_weights(fu, fv, inv_c2, prod_m1, hfloor);
-  double su = sqrt(w.hu), sv = sqrt(w.hv);
+  const double isu = rsqrt_nr(w.hu), isv = rsqrt_nr(w.hv);      // hu, hv > 0 (floored)
+  const double su = w.hu * isu, sv = w.hv * isv;
   ObsLin o;
   o.n0[0] = su * ju[0]; o.n0[1] = su * ju[1]; o.n0[2] = su * ju[2];
   o.n1[0] = sv * jv[0]; o.n1[1] = sv * jv[1]; o.n1[2] = sv * jv[2];
-  o.e0 = w.gu * fu / su;
-  o.e1 = w.gv * fv / sv;
+  o.e0 = w.gu * fu * isu;
+  o.e1 = w.gv * fv * isv;
   return o;
 }
 
@@ -526,21 +527,27 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
 }
 
 // ---- K6: back-substitution + trial evaluation --------------------------------------------------------------
-// One thread per point (grid-stride): re-linearise at the current parameters (V, g and s = sum_c N_c^T N_c d_c with
-// d_c = w_c x X + tau_c, in one pass, nothing is stored per observation), dX = -(V + lam D)^-1 (g + s), write the
-// trial point, evaluate the robust cost at the trial parameters. Per-block partials: [trial cost, predicted
-// reduction of the point blocks, max |dX|, 0].
+// Warp-synchronous, no block barrier in the loop: a warp owns 32 consecutive points at a time and cuts them into
+// batches of whole points whose observations fill its 32 lanes (one lane per observation):
+//   re-linearise at the current parameters (N, e) and y = e + N d_c with d_c = w_c x X + tau_c;
+//   segmented shuffle scan over each point's lanes: V = sum N^T N, g + s = sum N^T y;
+//   the segment's last lane solves dX = -(V + lam D)^-1 (g + s), writes the trial point, and hands dX back to the
+//   segment; every lane adds its share of the predicted reduction (-0.5 e^T N dX; the tail adds 0.5 lam dX^T D dX),
+//   projects the trial point with the trial cameras and adds its robust cost 0.5 C^2 log1p((1+z_u)(1+z_v) - 1).
+// Per-block partials: [trial cost, predicted reduction of the point blocks, max |dX|, 0].
 template <int C>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
 schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
                      const double* __restrict__ cams0, const double* __restrict__ cams1,
                      const double* __restrict__ X0, const double* __restrict__ X1, double* __restrict__ Xt0,
                      double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
                      const double* __restrict__ delta_c, double* __restrict__ scal_partial) {
+  constexpr int NW = 8;
   __shared__ double sc[C * CAM_STRIDE];
   __shared__ double st[C * CAM_STRIDE];
   __shared__ double sd[6 * C];
-  __shared__ double red[3][4];
+  __shared__ double red[3][NW];
+  __shared__ unsigned char smap[NW][32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
   const int cur = lm->cur;
@@ -553,74 +560,127 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
   if (tid < 6 * C) sd[tid] = delta_c[tid];
   __syncthreads();
   double f_acc = 0.0, pred_acc = 0.0, dx_acc = 0.0;
-  if (!skip) {
-    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + tid; p < P; p += (int64_t)gridDim.x * blockDim.x) {
-      unsigned m = obs_mask[p];
-      if (!m) continue;
-      double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
-      double pm1 = 0.0;
-      double g0 = 0, g1 = 0, g2 = 0, v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0;
-      double h0 = 0, h1 = 0, h2 = 0;     // pure point gradient N^T e (for the predicted reduction)
-#pragma unroll 1
-      for (int c = 0; c < C; ++c) {
-        if (m >> c & 1) {
-          double2 ob = uv[p * C + c];
-          ObsLin o = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
-          h0 = fma(o.n0[0], o.e0, fma(o.n1[0], o.e1, h0));
-          h1 = fma(o.n0[1], o.e0, fma(o.n1[1], o.e1, h1));
-          h2 = fma(o.n0[2], o.e0, fma(o.n1[2], o.e1, h2));
+  double prod = 1.0;       // running product of (1+z_u)(1+z_v) over this lane's observations; logged when it grows large
+  const int64_t n_groups = skip ? 0 : (P + 31) / 32;
+  const unsigned FULL = 0xffffffffu;
+  for (int64_t grp = (int64_t)blockIdx.x * NW + warp; grp < n_groups; grp += (int64_t)gridDim.x * NW) {
+    const int64_t p = grp * 32 + lane;
+    const unsigned m = (p < P) ? obs_mask[p] : 0u;
+    const int k = __popc(m);
+    double X = 0.0, Y = 0.0, Z = 0.0;
+    if (m) { X = Xp[3 * p]; Y = Xp[3 * p + 1]; Z = Xp[3 * p + 2]; }
+    int s = k;                                  // exclusive prefix of the observation counts
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int v = __shfl_up_sync(FULL, s, o);
+      if (lane >= o) s += v;
+    }
+    const int total = __shfl_sync(FULL, s, 31);
+    s -= k;
+    int start = 0;
+    while (start < 32) {
+      // batch = points [start, end): as many whole points as fit in 32 lanes (a point has <= 8 observations)
+      const int base = __shfl_sync(FULL, s, start);
+      const unsigned fit = __ballot_sync(FULL, lane >= start && s + k - base <= 32);
+      const unsigned nofit = ~fit & (FULL << start);
+      const int end = nofit ? (__ffs(nofit) - 1) : 32;
+      const int s_end = (end < 32) ? __shfl_sync(FULL, s, end & 31) : total;
+      const int nb = s_end - base;
+      if (nb > 0) {
+        if (lane >= start && lane < end) {
+          int off = s - base;
+          unsigned mm = m;
+          while (mm) {
+            int c = __ffs(mm) - 1;
+            mm &= mm - 1;
+            smap[warp][off++] = (unsigned char)(lane << 3 | c);
+          }
+        }
+        __syncwarp();
+        const bool valid = lane < nb;
+        const int e = valid ? smap[warp][lane] : (start << 3);
+        const int j = e >> 3, c = e & 7;
+        const double Xj = __shfl_sync(FULL, X, j), Yj = __shfl_sync(FULL, Y, j), Zj = __shfl_sync(FULL, Z, j);
+        const int tail_idx = __shfl_sync(FULL, s, j) - base + __shfl_sync(FULL, k, j) - 1;
+        double v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0, g0 = 0, g1 = 0, g2 = 0;
+        ObsLin o;
+        o.n0[0] = o.n0[1] = o.n0[2] = o.n1[0] = o.n1[1] = o.n1[2] = o.e0 = o.e1 = 0.0;
+        double2 ob = make_double2(0.0, 0.0);
+        if (valid) {
+          ob = uv[(grp * 32 + j) * C + c];
+          double pm1 = 0.0;
+          o = linearise_obs(sc + c * CAM_STRIDE, Xj, Yj, Zj, ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
           const double* d = sd + 6 * c;
-          double dx = fma(d[1], Z, -d[2] * Y) + d[3];
-          double dy = fma(d[2], X, -d[0] * Z) + d[4];
-          double dz = fma(d[0], Y, -d[1] * X) + d[5];
-          double y0 = o.e0 + fma(o.n0[0], dx, fma(o.n0[1], dy, o.n0[2] * dz));   // e + N d: g + s in one go
-          double y1 = o.e1 + fma(o.n1[0], dx, fma(o.n1[1], dy, o.n1[2] * dz));
-          g0 = fma(o.n0[0], y0, fma(o.n1[0], y1, g0));
-          g1 = fma(o.n0[1], y0, fma(o.n1[1], y1, g1));
-          g2 = fma(o.n0[2], y0, fma(o.n1[2], y1, g2));
-          v00 = fma(o.n0[0], o.n0[0], fma(o.n1[0], o.n1[0], v00));
-          v01 = fma(o.n0[0], o.n0[1], fma(o.n1[0], o.n1[1], v01));
-          v02 = fma(o.n0[0], o.n0[2], fma(o.n1[0], o.n1[2], v02));
-          v11 = fma(o.n0[1], o.n0[1], fma(o.n1[1], o.n1[1], v11));
-          v12 = fma(o.n0[1], o.n0[2], fma(o.n1[1], o.n1[2], v12));
-          v22 = fma(o.n0[2], o.n0[2], fma(o.n1[2], o.n1[2], v22));
+          const double dx = fma(d[1], Zj, -d[2] * Yj) + d[3];
+          const double dy = fma(d[2], Xj, -d[0] * Zj) + d[4];
+          const double dz = fma(d[0], Yj, -d[1] * Xj) + d[5];
+          const double y0 = o.e0 + fma(o.n0[0], dx, fma(o.n0[1], dy, o.n0[2] * dz));
+          const double y1 = o.e1 + fma(o.n1[0], dx, fma(o.n1[1], dy, o.n1[2] * dz));
+          g0 = fma(o.n0[0], y0, o.n1[0] * y1); g1 = fma(o.n0[1], y0, o.n1[1] * y1); g2 = fma(o.n0[2], y0, o.n1[2] * y1);
+          v00 = fma(o.n0[0], o.n0[0], o.n1[0] * o.n1[0]); v01 = fma(o.n0[0], o.n0[1], o.n1[0] * o.n1[1]);
+          v02 = fma(o.n0[0], o.n0[2], o.n1[0] * o.n1[2]); v11 = fma(o.n0[1], o.n0[1], o.n1[1] * o.n1[1]);
+          v12 = fma(o.n0[1], o.n0[2], o.n1[1] * o.n1[2]); v22 = fma(o.n0[2], o.n0[2], o.n1[2] * o.n1[2]);
         }
-      }
-      Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
-      double d0 = -fma(iv.i00, g0, fma(iv.i01, g1, iv.i02 * g2));
-      double d1 = -fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
-      double d2 = -fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
-      // predicted reduction: over all parameters m(0) - m(delta) = 0.5 (lam delta^T D delta - g^T delta) with the
-      // undamped gradient g; this is the point part (the solve kernel adds the camera part).
-      pred_acc += 0.5 * (lam * (iv.D0 * d0 * d0 + iv.D1 * d1 * d1 + iv.D2 * d2 * d2) - (h0 * d0 + h1 * d1 + h2 * d2));
-      double Xn = X + d0, Yn = Y + d1, Zn = Z + d2;
-      Xt[3 * p] = Xn; Xt[3 * p + 1] = Yn; Xt[3 * p + 2] = Zn;
-      dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
-      double pt = 0.0;
-#pragma unroll 1
-      for (int c = 0; c < C; ++c) {
-        if (m >> c & 1) {
+        // segmented inclusive scan over the point's lanes (segments are <= 8 lanes: offsets 1, 2, 4)
+#pragma unroll
+        for (int off = 1; off <= 4; off <<= 1) {
+          const int jo = __shfl_up_sync(FULL, j, off);
+          const bool same = valid && lane >= off && jo == j;
+          double t;
+          t = __shfl_up_sync(FULL, v00, off); if (same) v00 += t;
+          t = __shfl_up_sync(FULL, v01, off); if (same) v01 += t;
+          t = __shfl_up_sync(FULL, v02, off); if (same) v02 += t;
+          t = __shfl_up_sync(FULL, v11, off); if (same) v11 += t;
+          t = __shfl_up_sync(FULL, v12, off); if (same) v12 += t;
+          t = __shfl_up_sync(FULL, v22, off); if (same) v22 += t;
+          t = __shfl_up_sync(FULL, g0, off); if (same) g0 += t;
+          t = __shfl_up_sync(FULL, g1, off); if (same) g1 += t;
+          t = __shfl_up_sync(FULL, g2, off); if (same) g2 += t;
+        }
+        double d0 = 0.0, d1 = 0.0, d2 = 0.0;
+        if (valid && lane == tail_idx) {
+          Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
+          d0 = -fma(iv.i00, g0, fma(iv.i01, g1, iv.i02 * g2));
+          d1 = -fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
+          d2 = -fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
+          // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta), undamped gradient g;
+          // this is the damping term of the point, the gradient term is added observation by observation below
+          pred_acc += 0.5 * lam * (iv.D0 * d0 * d0 + iv.D1 * d1 * d1 + iv.D2 * d2 * d2);
+          const int64_t pj = grp * 32 + j;
+          Xt[3 * pj] = Xj + d0; Xt[3 * pj + 1] = Yj + d1; Xt[3 * pj + 2] = Zj + d2;
+          dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
+        }
+        d0 = __shfl_sync(FULL, d0, tail_idx & 31);
+        d1 = __shfl_sync(FULL, d1, tail_idx & 31);
+        d2 = __shfl_sync(FULL, d2, tail_idx & 31);
+        if (valid) {
+          const double nd0 = fma(o.n0[0], d0, fma(o.n0[1], d1, o.n0[2] * d2));
+          const double nd1 = fma(o.n1[0], d0, fma(o.n1[1], d1, o.n1[2] * d2));
+          pred_acc -= 0.5 * fma(o.e0, nd0, o.e1 * nd1);
           double x, y, z, u, v;
-          to_camera(st + c * CAM_STRIDE, Xn, Yn, Zn, x, y, z);
+          to_camera(st + c * CAM_STRIDE, Xj + d0, Yj + d1, Zj + d2, x, y, z);
           fisheye_uv(st + c * CAM_STRIDE, x, y, z, u, v);
-          double2 ob = uv[p * C + c];
-          cauchy_accum(u - ob.x, v - ob.y, prm.inv_c2, pt);
+          const double fu = u - ob.x, fv = v - ob.y;
+          prod *= fma(fu * fu, prm.inv_c2, 1.0) * fma(fv * fv, prm.inv_c2, 1.0);
+          if (prod > 1e200) { f_acc += log(prod); prod = 1.0; }      // sum of log1p(z) = log of the product; rare
         }
+        __syncwarp();
       }
-      f_acc += prm.half_c2 * log1p(pt);
+      start = end;
     }
   }
+  f_acc = prm.half_c2 * (f_acc + log(prod));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    f_acc += __shfl_xor_sync(0xffffffffu, f_acc, o);
-    pred_acc += __shfl_xor_sync(0xffffffffu, pred_acc, o);
-    dx_acc = fmax(dx_acc, __shfl_xor_sync(0xffffffffu, dx_acc, o));
+    f_acc += __shfl_xor_sync(FULL, f_acc, o);
+    pred_acc += __shfl_xor_sync(FULL, pred_acc, o);
+    dx_acc = fmax(dx_acc, __shfl_xor_sync(FULL, dx_acc, o));
   }
   if (lane == 0) { red[0][warp] = f_acc; red[1][warp] = pred_acc; red[2][warp] = dx_acc; }
   __syncthreads();
   if (tid == 0) {
     double a = 0, b = 0, c = 0;
-    for (int w = 0; w < 4; ++w) { a += red[0][w]; b += red[1][w]; c = fmax(c, red[2][w]); }
+    for (int w = 0; w < NW; ++w) { a += red[0][w]; b += red[1][w]; c = fmax(c, red[2][w]); }
     scal_partial[4 * blockIdx.x] = a;
     scal_partial[4 * blockIdx.x + 1] = b;
     scal_partial[4 * blockIdx.x + 2] = c;

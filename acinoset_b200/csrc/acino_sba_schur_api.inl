@@ -69,8 +69,11 @@ static int schur_ensure(acino_sba* h) {
   const int bt = schur_bt(C), len = rcs_len(C);
   int64_t tiles = (h->P + bt - 1) / bt;
   s.grid_build = (int)(tiles < 1 ? 1 : (tiles < sms ? tiles : sms));
-  int64_t bb = (h->P + 127) / 128;
-  s.grid_back = (int)(bb < 1 ? 1 : (bb < (int64_t)sms * 8 ? bb : (int64_t)sms * 8));
+  int64_t bb = (h->P + 255) / 256;
+  int occ = 1;     // resident CTAs per SM of the persistent back-substitution kernel
+  DISPATCH_C(C, (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, schur_backsub_kernel<CC>, 256, 0)));
+  if (occ < 1) occ = 1;
+  s.grid_back = (int)(bb < 1 ? 1 : (bb < (int64_t)sms * occ ? bb : (int64_t)sms * occ));
   size_t P = h->P ? (size_t)h->P : 1;
   ACINO_CUDA(cudaMalloc(&s.cams_alt, MAX_CAMS * CAM_STRIDE * sizeof(double)));
   ACINO_CUDA(cudaMalloc(&s.X_alt, P * 3 * sizeof(double)));
@@ -153,7 +156,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   }
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 2], st));
-  DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, 128, 0, st>>>(h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X,
+  DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, 256, 0, st>>>(h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X,
                                                                        s.X_alt, h->X, s.X_alt, s.lm, prm, s.delta_c,
                                                                        s.scal_partial)));
   ACINO_CUDA(cudaGetLastError());
