@@ -403,7 +403,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
 // One CTA. partial = [n_partial][LEN] (the build kernel's per-CTA partials, or the single all-reduced vector);
 // maxp = [n_max][2] maxima (|g_p|, |X|).
 template <int C>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 schur_solve_kernel(const double* __restrict__ partial, int n_partial, const double* __restrict__ maxp, int n_max,
                    const double* __restrict__ cams0, const double* __restrict__ cams1, double* __restrict__ cams_trial0,
                    double* __restrict__ cams_trial1, SchurLm* __restrict__ lm, SchurParams prm,
@@ -413,13 +413,23 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   __shared__ double A[n][n + 1];
   __shared__ double rhs[n], gbar[n], D[n], dl[n];
   __shared__ double smax[2];
+  __shared__ double col[n];
+  __shared__ double rhs_diag;
   __shared__ int fail;
   const int tid = threadIdx.x;
   if (lm->status != 0 && !prm.force) return;
   for (int i = tid; i < LEN; i += blockDim.x) {
-    double s = 0.0;
-    for (int b = 0; b < n_partial; ++b) s += partial[(size_t)b * LEN + i];
-    r[i] = s;
+    // fixed summation order (four interleaved chains, then a fixed combine): deterministic, and the loads overlap
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int b = 0;
+    for (; b + 4 <= n_partial; b += 4) {
+      s0 += partial[(size_t)b * LEN + i];
+      s1 += partial[(size_t)(b + 1) * LEN + i];
+      s2 += partial[(size_t)(b + 2) * LEN + i];
+      s3 += partial[(size_t)(b + 3) * LEN + i];
+    }
+    for (; b < n_partial; ++b) s0 += partial[(size_t)b * LEN + i];
+    r[i] = (s0 + s1) + (s2 + s3);
   }
   if (tid < 2) {
     double mx = 0.0;
@@ -465,47 +475,85 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   const double lam = lm->lambda;
   if (tid < n) A[tid][tid] = fma(lam, D[tid], A[tid][tid]);
   __syncthreads();
-  // in-place Cholesky (lower), right-looking; n <= 48
-  for (int k = 0; k < n; ++k) {
-    if (tid == 0) {
-      double d = A[k][k];
-      if (!(d > 0.0)) { fail = 1; d = 1.0; }
-      A[k][k] = sqrt(d);
+  // Cholesky (lower): one matrix element per thread, in a register; per column one sqrt by the diagonal's owner, one
+  // scaling by the column's owners and a rank-1 update by everybody else: two barriers per column, no serial loop
+  {
+    constexpr int NE = n * (n + 1) / 2;
+    constexpr int EPT = (NE + 1023) / 1024;
+    double a[EPT];
+    int ei[EPT], ej[EPT];
+#pragma unroll
+    for (int t = 0; t < EPT; ++t) {
+      const int e = tid + t * 1024;
+      int ii = 0;
+      while ((ii + 1) * (ii + 2) / 2 <= e) ++ii;       // row of packed lower-triangular index e
+      ei[t] = e < NE ? ii : -1;
+      ej[t] = e - ii * (ii + 1) / 2;
+      a[t] = e < NE ? A[ii][ej[t]] : 0.0;
     }
-    __syncthreads();
-    if (tid > k && tid < n) A[tid][k] /= A[k][k];
-    __syncthreads();
-    for (int e = tid; e < (n - k - 1) * (n - k - 1); e += blockDim.x) {
-      int i = k + 1 + e / (n - k - 1), j = k + 1 + e % (n - k - 1);
-      if (j <= i) A[i][j] = fma(-A[i][k], A[j][k], A[i][j]);
+    for (int k = 0; k < n; ++k) {
+#pragma unroll
+      for (int t = 0; t < EPT; ++t)
+        if (ei[t] == k && ej[t] == k) {
+          double d = a[t];
+          if (!(d > 0.0)) { fail = 1; d = 1.0; }
+          a[t] = sqrt(d);
+          rhs_diag = a[t];
+        }
+      __syncthreads();
+#pragma unroll
+      for (int t = 0; t < EPT; ++t)
+        if (ej[t] == k && ei[t] > k) { a[t] /= rhs_diag; col[ei[t]] = a[t]; }
+      __syncthreads();
+#pragma unroll
+      for (int t = 0; t < EPT; ++t)
+        if (ej[t] > k && ei[t] >= 0) a[t] = fma(-col[ei[t]], col[ej[t]], a[t]);
     }
-    __syncthreads();
+#pragma unroll
+    for (int t = 0; t < EPT; ++t)
+      if (ei[t] >= 0) A[ei[t]][ej[t]] = a[t];
   }
-  if (tid == 0) {
-    // L y = -rhs ; L^T d = y
+  __syncthreads();
+  // the two triangular solves by one warp (dot products over lanes, shuffle reduction)
+  if (tid < 32) {
+    const int lane = tid;
+    // L y = -rhs
     for (int i = 0; i < n; ++i) {
-      double s = -rhs[i];
-      for (int j = 0; j < i; ++j) s = fma(-A[i][j], dl[j], s);
-      dl[i] = s / A[i][i];
+      double part = 0.0;
+      for (int j2 = lane; j2 < i; j2 += 32) part = fma(A[i][j2], dl[j2], part);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      if (lane == 0) dl[i] = (-rhs[i] - part) / A[i][i];
+      __syncwarp();
     }
+    // L^T d = y
     for (int i = n - 1; i >= 0; --i) {
-      double s = dl[i];
-      for (int j = i + 1; j < n; ++j) s = fma(-A[j][i], dl[j], s);
-      dl[i] = s / A[i][i];
+      double part = 0.0;
+      for (int j2 = i + 1 + lane; j2 < n; j2 += 32) part = fma(A[j2][i], dl[j2], part);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      if (lane == 0) dl[i] = (dl[i] - part) / A[i][i];
+      __syncwarp();
     }
     double pc = 0.0;
-    bool bad = fail != 0;
-    for (int i = 0; i < n; ++i) {
-      if (!isfinite(dl[i])) bad = true;
+    int bad = 0;
+    for (int i = lane; i < n; i += 32) {
+      if (!isfinite(dl[i])) bad = 1;
       pc += 0.5 * (lam * D[i] * dl[i] * dl[i] - gbar[i] * dl[i]);
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { pc += __shfl_xor_sync(0xffffffffu, pc, o); bad |= __shfl_xor_sync(0xffffffffu, bad, o); }
+    __syncwarp();
+    bad |= fail;
     if (bad) {
-      for (int i = 0; i < n; ++i) dl[i] = 0.0;
+      for (int i = lane; i < n; i += 32) dl[i] = 0.0;
       pc = 0.0;
-      lm->chol_fail += 1;
     }
-    lm->pred_cam = pc;
-    fail = bad;
+    if (lane == 0) {
+      if (bad) lm->chol_fail += 1;
+      lm->pred_cam = pc;
+      fail = bad;
+    }
   }
   __syncthreads();
   if (tid < n) delta_c[tid] = dl[tid];
@@ -745,21 +793,42 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
   }
 }
 
-// multi-GPU: fold the per-CTA partials before the NCCL allreduce (sum rows, max rows)
+// fold the per-CTA partials (fixed order: deterministic): block = 8 warps x 32 entries; warp w sums the partials
+// b = w, w+8, ... of its 32 entries with two chains in flight, warp 0 combines the eight sums. One pass over
+// [n_partial][len] with len/32 CTAs instead of one CTA chasing n_partial dependent loads per entry. Block 0 also
+// folds the maxima rows (max_w columns at stride max_stride, offset max_off).
 __global__ void __launch_bounds__(256)
 fold_partials_kernel(const double* __restrict__ partial, int n_partial, int len, double* __restrict__ out_sum,
                      const double* __restrict__ maxp, int n_max, int max_w, int max_stride, int max_off,
                      double* __restrict__ out_max) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ double sm[8][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + lane;
+  double s0 = 0.0, s1 = 0.0;
   if (i < len) {
-    double s = 0.0;
-    for (int b = 0; b < n_partial; ++b) s += partial[(size_t)b * len + i];
-    out_sum[i] = s;
+    int b = warp;
+    for (; b + 8 < n_partial; b += 16) {
+      s0 += partial[(size_t)b * len + i];
+      s1 += partial[(size_t)(b + 8) * len + i];
+    }
+    if (b < n_partial) s0 += partial[(size_t)b * len + i];
   }
-  if (i < max_w) {
-    double m = 0.0;
-    for (int b = 0; b < n_max; ++b) m = fmax(m, maxp[(size_t)b * max_stride + max_off + i]);
-    out_max[i] = m;
+  sm[warp][lane] = s0 + s1;
+  __syncthreads();
+  if (warp == 0 && i < len) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sm[w][lane];
+    out_sum[i] = t;
+  }
+  if (blockIdx.x == 0 && warp == 1) {
+    for (int c = 0; c < max_w; ++c) {
+      double m = 0.0;
+      for (int b = lane; b < n_max; b += 32) m = fmax(m, maxp[(size_t)b * max_stride + max_off + c]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+      if (lane == 0) out_max[c] = m;
+    }
   }
 }
 

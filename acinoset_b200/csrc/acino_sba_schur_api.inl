@@ -138,22 +138,20 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 1], st));
   ++s.launches;
+  fold_partials_kernel<<<(len + 31) / 32, 256, 0, st>>>(s.rcs_partial, s.grid_build, len, s.rcs, s.max_partial, s.grid_build,
+                                                        2, 2, 0, s.mx);
+  ACINO_CUDA(cudaGetLastError());
+  ++s.launches;
   if (h->nranks > 1) {
-    fold_partials_kernel<<<(len + 255) / 256, 256, 0, st>>>(s.rcs_partial, s.grid_build, len, s.rcs, s.max_partial,
-                                                           s.grid_build, 2, 2, 0, s.mx);
-    ACINO_CUDA(cudaGetLastError());
     ACINO_NCCL(g_nccl.GroupStart());
     ACINO_NCCL(g_nccl.AllReduce(s.rcs, s.rcs, (size_t)len, kNcclDouble, kNcclSum, h->nccl_comm, st));
     ACINO_NCCL(g_nccl.AllReduce(s.mx, s.mx, 2, kNcclDouble, kNcclMax, h->nccl_comm, st));
     ACINO_NCCL(g_nccl.GroupEnd());
-    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, 256, 0, st>>>(s.rcs, 1, s.mx, 1, h->cams, s.cams_alt, h->cams, s.cams_alt,
-                                                            s.lm, prm, s.delta_c)));
-    s.launches += 3;
-  } else {
-    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, 256, 0, st>>>(s.rcs_partial, s.grid_build, s.max_partial, s.grid_build,
-                                                            h->cams, s.cams_alt, h->cams, s.cams_alt, s.lm, prm, s.delta_c)));
     ++s.launches;
   }
+  DISPATCH_C(C, (schur_solve_kernel<CC><<<1, 1024, 0, st>>>(s.rcs, 1, s.mx, 1, h->cams, s.cams_alt, h->cams, s.cams_alt, s.lm, prm,
+                                                          s.delta_c)));
+  ++s.launches;
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 2], st));
   DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, 256, 0, st>>>(h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X,

@@ -224,7 +224,7 @@ def native_arm(args):
         build_bytes = P * 1 + n_pts * 24 + n_obs * 16
         back_bytes = build_bytes + n_pts * 24
         kern = dict(name=f'schur_build_kernel<{C}>', ms_per_launch=pr['build_ms'], bytes_per_launch=build_bytes,
-                    launches_per_step=4 if world == 1 else 8, backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes,
+                    launches_per_step=5 if world == 1 else 8, backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes,
                     profiled_iterations=pr['iterations'])
     fp64_peak = dense.fp64_peak_tflops()
     if world > 1:
