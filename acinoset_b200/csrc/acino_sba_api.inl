@@ -56,12 +56,13 @@ static LmParams make_lm_params(const acino_sba_opts* o, int inner) {
   p.lambda0 = o->lambda0;
   p.inner_iters = inner;
   p.force = o->force_iters;
+  p.ignore_status = 0;
   return p;
 }
 
 static int launch_lm_points(acino_sba* h, const LmParams& prm) {
   DISPATCH_C(h->C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, h->stream>>>(
-                       h->uv, h->mask, h->P, h->cams, h->X, h->lam, h->cost_p, h->status, prm, h->counters)));
+                       h->uv, h->mask, h->P, h->cams, h->X, h->lam, h->cost_p, h->status, prm, h->counters, LmPointsCtl{nullptr, nullptr, nullptr, nullptr})));
   ACINO_CUDA(cudaGetLastError());
   return ACINO_OK;
 }
@@ -155,6 +156,7 @@ void acino_sba_default_opts(acino_sba_opts* o, int mode) {
     o->xtol = 1e-14;
     o->ftol = 1e-14;
     o->hess_floor = 0.3;
+    o->point_refine_iters = 2;
     o->lambda0 = 1e-4;
   } else {
     o->max_iter = 200;

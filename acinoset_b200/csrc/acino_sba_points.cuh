@@ -88,6 +88,16 @@ __device__ __forceinline__ double lm_step3(const NormalEq& ne, double lam, doubl
 struct LmParams {
   double inv_c2, half_c2, gtol, xtol, lambda0;
   int inner_iters, force;
+  int ignore_status;   // 1: every observed point restarts as active (the cameras moved since its status was written)
+};
+
+// optional device-side control of a launch (the points+extrinsics solver refines points between camera steps):
+// run only when *go != 0; use the alternate point / camera buffers when *cur != 0
+struct LmPointsCtl {
+  const int* go;
+  const int* cur;
+  const double* cams_alt;
+  double* X_alt;
 };
 
 // One launch = up to inner_iters LM iterations of every active point. cost_p[p] = robust cost of the
@@ -97,9 +107,11 @@ __global__ void __launch_bounds__(128)
 lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
                  const double* __restrict__ cams, double* __restrict__ Xp, double* __restrict__ lam_p,
                  double* __restrict__ cost_p, uint8_t* __restrict__ status, LmParams prm,
-                 unsigned long long* __restrict__ counters) {
+                 unsigned long long* __restrict__ counters, LmPointsCtl ctl) {
   __shared__ double sc[C * CAM_STRIDE];
   __shared__ double2 s_uv[C * 128];
+  if (ctl.go && *ctl.go == 0) return;
+  if (ctl.cur && *ctl.cur) { cams = ctl.cams_alt; Xp = ctl.X_alt; }
   for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[i] = cams[i];
   __syncthreads();
   int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -108,7 +120,7 @@ lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs
   if (p < P) {
     unsigned m = obs_mask[p];
     uint8_t st = status[p];
-    if (m != 0 && (st == ST_ACTIVE || prm.force)) {
+    if (m != 0 && (st == ST_ACTIVE || prm.force || prm.ignore_status)) {
 #pragma unroll
       for (int c = 0; c < C; ++c)
         if (m >> c & 1) uvr[c * 128] = uv[p * C + c];

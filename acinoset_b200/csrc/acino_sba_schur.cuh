@@ -30,15 +30,18 @@ struct SchurLm {
   double gmax, dxmax, xmax;
   double F0;         // cost at the first linearisation
   double pred_cam;
+  double last_rel_dec;   // relative cost decrease of the latest accepted step
   int cur;           // which of the two parameter buffers is current
   int status;        // 0 running, 1 gtol, 2 ftol, 3 xtol, 4 stalled (damping exhausted), 6 step failed (kept running)
   int iter, n_accept, n_reject, chol_fail, skip;
+  int last_accept;   // 1 when the latest decision accepted the step
+  int need_cost;     // 1: the next linearisation must re-evaluate the cost (points were refined after the accepted step)
   int pad;
 };
 
 struct SchurParams {
   double inv_c2, half_c2, gtol, ftol, xtol, hfloor;
-  int force;
+  int force, refine;
 };
 
 // ---- symmetric 3x3: V + lam*D -> inverse (via LDL^T), D = floored diag(V) --------------------------------
@@ -178,7 +181,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   const int skip = (lm->status != 0 && !prm.force);
   const int cur = lm->cur;
   const double lam = lm->lambda;
-  const bool need_cost = (lm->iter == 0);   // later iterations inherit the cost from the accepted trial evaluation (K6/K7)
+  const bool need_cost = (lm->iter == 0) || lm->need_cost;   // later iterations inherit the cost from the accepted trial evaluation (K6/K7)
   const double* __restrict__ cams = cur ? cams1 : cams0;
   const double* __restrict__ Xp = cur ? X1 : X0;
 
@@ -193,6 +196,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   __syncthreads();
 
   double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0;
+  double cprod = 1.0;     // running product of (1+z_u)(1+z_v): sum of log1p(z) = log of the product
   const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     // ---------------- phase 1a: stage the points, compact the tile's observations (point-major, camera-minor)
@@ -238,7 +242,10 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
         n[3 * BS] = o.n1[0]; n[4 * BS] = o.n1[1]; n[5 * BS] = o.n1[2];
         sE[(size_t)(c * 2) * BS + q] = o.e0;
         sE[(size_t)(c * 2 + 1) * BS + q] = o.e1;
-        if (need_cost) cost_acc += prm.half_c2 * log1p(pm1);
+        if (need_cost) {
+          cprod *= 1.0 + pm1;
+          if (cprod > 1e200) { cost_acc += prm.half_c2 * log(cprod); cprod = 1.0; }
+        }
       }
       __syncthreads();
     }
@@ -379,6 +386,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   }
 
   // ---------------- CTA totals: cost (sum) and gradient / coordinate maxima
+  cost_acc += prm.half_c2 * log(cprod);
   __shared__ double red[3][32];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -465,7 +473,11 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
     for (int i = 0; i < n; ++i) { dmax = fmax(dmax, D[i]); gm = fmax(gm, fabs(gbar[i])); }
     double flo = fmax(1e-12 * dmax, 1e-300);
     for (int i = 0; i < n; ++i) D[i] = fmax(D[i], flo);
-    if (lm->iter == 0) { lm->F = r[NU * RCS_UNIT]; lm->F0 = r[NU * RCS_UNIT]; }   // K4 evaluates the cost only then
+    if (lm->iter == 0 || lm->need_cost) {      // K4 evaluates the cost only then
+      lm->F = r[NU * RCS_UNIT];
+      if (lm->iter == 0) lm->F0 = r[NU * RCS_UNIT];
+      lm->need_cost = 0;
+    }
     lm->gmax = gm;
     lm->xmax = smax[1];
     lm->skip = 0;
@@ -776,6 +788,9 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
     lm->cur ^= 1;
     lm->F = Ft;
     lm->n_accept += 1;
+    lm->last_accept = 1;
+    lm->need_cost = prm.refine > 0;
+    lm->last_rel_dec = act / F;
     if (!prm.force) {
       if (act <= prm.ftol * F) lm->status = 2;
       else if (c <= prm.xtol * (lm->xmax + prm.xtol)) lm->status = 3;
@@ -783,11 +798,14 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
   } else {
     lm->rho = 0.0;
     lm->n_reject += 1;
+    lm->last_accept = 0;
     double l = lm->lambda * lm->nu;
     lm->nu = fmin(lm->nu * 2.0, 1e8);
     if (l > 1e16) {
       l = 1e16;
-      if (!prm.force) lm->status = 4;
+      // damping exhausted: no descent left at fp64 resolution. If the last accepted step was already tiny this is
+      // convergence (the cost differences have sunk below the rounding of the cost sums), otherwise a stall.
+      if (!prm.force) lm->status = (lm->n_accept > 0 && lm->last_rel_dec <= 1e-8) ? 2 : 4;
     }
     lm->lambda = l;
   }
@@ -830,6 +848,13 @@ fold_partials_kernel(const double* __restrict__ partial, int n_partial, int len,
       if (lane == 0) out_max[c] = m;
     }
   }
+}
+
+// after the last accepted step was followed by a point refinement: take the cost of the final parameters from a fresh
+// linearisation (rcs scalar slot), so that the reported cost_final is the cost of what get_points / get_cameras return
+__global__ void schur_refresh_cost_kernel(SchurLm* lm, const double* __restrict__ rcs, int cost_slot) {
+  lm->F = rcs[cost_slot];
+  lm->need_cost = 0;
 }
 
 __global__ void schur_init_kernel(SchurLm* lm, double lambda0) {

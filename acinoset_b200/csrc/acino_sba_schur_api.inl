@@ -113,6 +113,7 @@ static SchurParams make_schur_params(const acino_sba_opts* o) {
   p.xtol = o->xtol;
   p.hfloor = o->hess_floor > 0 ? o->hess_floor : 0.3;
   p.force = o->force_iters;
+  p.refine = o->point_refine_iters > 0 ? (int)o->point_refine_iters : 0;
   return p;
 }
 
@@ -175,6 +176,18 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
     ++s.launches;
   }
   ACINO_CUDA(cudaGetLastError());
+  if (prm.refine > 0) {
+    // per-point refinement with the (just accepted) cameras fixed: K3 on the current buffers, skipped on the device
+    // when the step was rejected. Every point keeps its own damping (h->lam) across calls.
+    LmParams lp;
+    lp.inv_c2 = prm.inv_c2; lp.half_c2 = prm.half_c2; lp.gtol = prm.gtol; lp.xtol = prm.xtol; lp.lambda0 = 1e-4;
+    lp.inner_iters = prm.refine; lp.force = 0; lp.ignore_status = 1;
+    LmPointsCtl ctl{&s.lm->last_accept, &s.lm->cur, s.cams_alt, s.X_alt};
+    DISPATCH_C(C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, st>>>(h->uv, h->mask, h->P, h->cams, h->X, h->lam, h->cost_p,
+                                                                          h->status, lp, h->counters, ctl)));
+    ACINO_CUDA(cudaGetLastError());
+    ++s.launches;
+  }
   return ACINO_OK;
 }
 
@@ -224,6 +237,22 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     ACINO_CUDA(cudaMemcpyAsync(s.h_lm, s.lm, sizeof(SchurLm), cudaMemcpyDeviceToHost, h->stream));
     ACINO_CUDA(cudaStreamSynchronize(h->stream));
     if (s.h_lm->status != 0 && !o->force_iters) break;
+  }
+  if (s.h_lm->need_cost) {
+    // the last accepted step was refined: one more linearisation for the cost of the final parameters
+    SchurParams pf = prm;
+    pf.force = 1;
+    const int len = rcs_len(h->C);
+    DISPATCH_C(h->C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, h->stream>>>(
+                         h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, pf, s.rcs_partial, s.max_partial)));
+    ACINO_CUDA(cudaGetLastError());
+    fold_partials_kernel<<<(len + 31) / 32, 256, 0, h->stream>>>(s.rcs_partial, s.grid_build, len, s.rcs, s.max_partial,
+                                                                 s.grid_build, 2, 2, 0, s.mx);
+    ACINO_CUDA(cudaGetLastError());
+    if (h->nranks > 1) ACINO_NCCL(g_nccl.AllReduce(s.rcs, s.rcs, (size_t)len, kNcclDouble, kNcclSum, h->nccl_comm, h->stream));
+    schur_refresh_cost_kernel<<<1, 1, 0, h->stream>>>(s.lm, s.rcs, rcs_units(h->C) * RCS_UNIT);
+    ACINO_CUDA(cudaGetLastError());
+    s.launches += 3;
   }
   rc = schur_sync_current(h);
   if (rc) return rc;

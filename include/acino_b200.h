@@ -90,7 +90,9 @@ typedef struct {
   double ftol;             /* points+extrinsics: stop when an accepted step reduces the cost by <= ftol*cost */
   double hess_floor;       /* points+extrinsics: floor of the Gauss-Newton curvature weight relative to rho'
                               (rho' + 2 rho'' f^2 = rho' (1-z)/(1+z) is negative beyond |f| > C): 1.0 = plain IRLS weights */
-  double reserved[2];
+  double point_refine_iters; /* points+extrinsics: after every accepted step, this many per-point LM iterations with
+                                the cameras fixed (K3 on the current buffers; each point has its own damping) */
+  double reserved[1];
 } acino_sba_opts;
 
 typedef struct {

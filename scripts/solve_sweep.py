@@ -1,0 +1,21 @@
+"""Solve-time sweep of the points+extrinsics solver at a given size for several point-refinement settings (needs a GPU)."""
+import sys, os, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+from acinoset_b200 import synth, dense, sba, _capi
+frames = int(sys.argv[1]) if len(sys.argv) > 1 else 119490
+sc = synth.make_rig_scene(frames, 20, seed=4)
+k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
+xyz, exists, mask = dense.triangulate_ring(sc['uv'], sc['lik'], 0.5, k, d, r, t)
+P, C = sc['lik'].shape
+rng = np.random.default_rng(100)
+rv = np.array([sba.rotation_matrix_to_rvec(m) for m in r]) + rng.normal(0, 8e-4, (C, 3))
+tv = t.reshape(C, 3) + rng.normal(0, 3e-3, (C, 3))
+s = dense.SbaSolver(C, P)
+s.set_observations(sc['uv'], mask)
+for refine in (0, 1, 2, 3):
+    for ftol in (1e-10, 1e-6):
+        s.set_cameras(k, d, r, t); s.set_rvec_t(rv, tv); s.set_points(np.nan_to_num(xyz))
+        st = s.solve(dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, point_refine_iters=refine, ftol=ftol, max_iter=300))
+        print(f"refine {refine} ftol {ftol:g}: {st['solve_ms']:.1f} ms, {st['iterations']} it, status {st['status']}, "
+              f"cost {st['cost_initial']:.6e} -> {st['cost_final']:.9e}, gmax {st['gmax']:.2e}")

@@ -154,7 +154,7 @@ def test_full_size_schur_properties():
         s = dense.SbaSolver(C, P)
         s.set_cameras(k, d, r, t); s.set_rvec_t(rv, tv)
         s.set_observations(sc['uv'], mask); s.set_points(np.nan_to_num(xyz))
-        o = dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, force_iters=1)
+        o = dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, force_iters=1, point_refine_iters=0)   # pure LM iterations
         costs = []
         for it in range(12):
             s.iterate(o)
