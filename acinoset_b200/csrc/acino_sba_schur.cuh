@@ -21,6 +21,7 @@ namespace acino {
 __host__ __device__ constexpr int rcs_units(int C) { return C * (C + 1) / 2; }
 __host__ __device__ constexpr int rcs_len(int C) { return rcs_units(C) * RCS_UNIT + 8; }
 __host__ __device__ constexpr int schur_bt(int C) { return C <= 6 ? 384 : 256; }
+__host__ __device__ constexpr int schur_ctas_per_sm(int) { return 1; }   // 2 x 192 threads measured slower (0.74 vs 0.66 ms)
 
 // device-resident LM state: every decision is taken on the device from (all-reduced) sums, identically on all ranks
 struct SchurLm {
@@ -153,7 +154,7 @@ struct SchurSmem {
 };
 
 template <int C>
-__global__ void __launch_bounds__(schur_bt(C), 1)
+__global__ void __launch_bounds__(schur_bt(C), schur_ctas_per_sm(C))
 schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
                    const double* __restrict__ cams0, const double* __restrict__ cams1,
                    const double* __restrict__ X0, const double* __restrict__ X1,

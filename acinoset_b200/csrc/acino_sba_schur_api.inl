@@ -68,7 +68,7 @@ static int schur_ensure(acino_sba* h) {
   const int C = h->C;
   const int bt = schur_bt(C), len = rcs_len(C);
   int64_t tiles = (h->P + bt - 1) / bt;
-  s.grid_build = (int)(tiles < 1 ? 1 : (tiles < sms ? tiles : sms));
+  { const int64_t cap = (int64_t)sms * schur_ctas_per_sm(C); s.grid_build = (int)(tiles < 1 ? 1 : (tiles < cap ? tiles : cap)); }
   int64_t bb = (h->P + 255) / 256;
   int occ = 1;     // resident CTAs per SM of the persistent back-substitution kernel
   DISPATCH_C(C, (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, schur_backsub_kernel<CC>, 256, 0)));

@@ -112,6 +112,32 @@ def gen_c1():
     print(f'c1: {len(points_3d)} points, {len(pidx)} obs, tri {t_tri:.2f}s sba {t_sba:.2f}s')
 
 
+def gen_metric():
+    """a12: the reference's own metric.residual_error (src/lib/metric.py:36-101) on config C1 (thresholded 2-D frame vs the
+    reference's triangulated points)."""
+    calib, utils, sba = ref_shim.load()
+    from lib import metric
+    sc, df = c1_inputs()
+    g = np.load(os.path.join(GOLD, 'golden_c1.npz'))
+    import pandas as pd
+    df_t = df.query('likelihood > 0.5')
+    p3 = pd.DataFrame({'frame': g['frame'], 'marker': g['marker'], 'x': g['points_3d'][:, 0], 'y': g['points_3d'][:, 1],
+                       'z': g['points_3d'][:, 2]})
+    from acinoset_b200 import synth
+    markers = synth.MARKERS[:20]
+    cam = (sc['k'], sc['d'], sc['r'], sc['t'], None, None)
+    with ref_shim.quiet():
+        err = metric.residual_error(df_t, p3, markers, cam)
+    out = {}
+    for c, e in err.items():
+        out[f'cam{c}_frame'] = e['frame'].to_numpy().astype(np.float64)
+        out[f'cam{c}_marker'] = e['marker'].to_numpy().astype(str)
+        for col in ('camera_distance', 'pixel_residual', 'pck_threshold', 'error_u', 'error_v'):
+            out[f'cam{c}_{col}'] = e[col].to_numpy().astype(np.float64)
+    np.savez_compressed(os.path.join(GOLD, 'golden_metric.npz'), versions=_versions(), **out)
+    print('metric:', {c: len(e) for c, e in err.items()})
+
+
 def main():
     what = sys.argv[1] if len(sys.argv) > 1 else 'all'
     os.makedirs(GOLD, exist_ok=True)
@@ -125,6 +151,8 @@ def main():
     if what in ('calib', 'all'):
         from .make_golden_calib import gen_calib
         gen_calib()
+    if what in ('metric', 'all'):
+        gen_metric()
 
 
 if __name__ == '__main__':
