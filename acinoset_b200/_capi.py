@@ -52,6 +52,7 @@ SIGNATURES = {
     'acino_sync': (_I, []),
     'acino_project': (_I, [_P, _I64, _P, _P]),
     'acino_project_dev': (_I, [_P, _I64, _P, _P, _P]),
+    'acino_project_all': (_I, [_P, _I64, _P, _I, _D, _D, _P]),
     'acino_residuals_list': (_I, [_P, _I64, _P, _P, _P, _I64, _P, _I, _P]),
     'acino_rodrigues': (_I, [_P, _I, _P]),
     'acino_triangulate_pair': (_I, [_P, _P, _I64, _P, _P, _P]),

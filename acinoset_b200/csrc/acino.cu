@@ -83,6 +83,22 @@ int acino_project(const double* X, int64_t N, const double* cam24, double* uv) {
   return ACINO_OK;
 }
 
+int acino_project_all(const double* X, int64_t N, const double* cams24, int n_cams, double width, double height, double* uv) {
+  ARG_CHECK(N >= 0 && cams24 && n_cams > 0 && n_cams <= 64 && (N == 0 || (X && uv)), "project_all");
+  if (N == 0) return ACINO_OK;
+  DevBuf dX, dUV, dCam;
+  ACINO_CUDA(dX.alloc(N * 3 * sizeof(double)));
+  ACINO_CUDA(dUV.alloc((size_t)n_cams * N * 2 * sizeof(double)));
+  ACINO_CUDA(dCam.alloc(n_cams * CAM_STRIDE * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(dX.p, X, N * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dCam.p, cams24, n_cams * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  project_all_kernel<<<grid_for(N, 256), 256, n_cams * CAM_STRIDE * sizeof(double)>>>(dX.as<double>(), N, dCam.as<double>(), n_cams,
+                                                                                       width, height, dUV.as<double2>());
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaMemcpy(uv, dUV.p, (size_t)n_cams * N * 2 * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
 int acino_residuals_list(const double* X, int64_t n_points, const int32_t* point_idx, const int32_t* cam_idx,
                          const double* points_2d, int64_t n_obs, const double* cams24, int n_cams, double* f) {
   ARG_CHECK(n_points >= 0 && n_obs >= 0 && n_cams > 0 && n_cams <= 64 && cams24, "residuals_list");

@@ -246,4 +246,27 @@ project_kernel(const double* __restrict__ Xp, int64_t N, const double* __restric
   uv[i] = make_double2(u, v);
 }
 
+// K1 for every camera at once (save_3d_cheetah_as_2d, src/lib/utils.py:255-263): thread per point reads X once and writes one
+// pixel per camera into uv[c][i]. With width > 0 the reference's range rule applies: a row with u or v outside
+// [0, width] x [0, height] becomes NaN (utils.py:262-263); NaN positions stay NaN.
+__global__ void __launch_bounds__(256)
+project_all_kernel(const double* __restrict__ Xp, int64_t N, const double* __restrict__ cams, int n_cams, double width,
+                   double height, double2* __restrict__ uv) {
+  extern __shared__ double sc[];
+  for (int i = threadIdx.x; i < n_cams * CAM_STRIDE; i += blockDim.x) sc[i] = cams[i];
+  __syncthreads();
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const double X = Xp[3 * i], Y = Xp[3 * i + 1], Z = Xp[3 * i + 2];
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int c = 0; c < n_cams; ++c) {
+    const double* cam = sc + c * CAM_STRIDE;
+    double x, y, z, u, v;
+    to_camera(cam, X, Y, Z, x, y, z);
+    fisheye_uv(cam, x, y, z, u, v);
+    if (width > 0.0 && (u > width || v > height || u < 0.0 || v < 0.0)) u = v = qnan;
+    uv[(int64_t)c * N + i] = make_double2(u, v);
+  }
+}
+
 }  // namespace acino

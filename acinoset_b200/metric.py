@@ -59,3 +59,13 @@ def residual_error(points_2d_df, points_3d_dfs, markers, camera_params):
         table = np.vstack((frames, m['marker'].to_numpy().astype(str), cam_dist, np.sqrt(np.sum(err ** 2, axis=1)), thr, err.T)).T
         error[str(i)] = pd.DataFrame(table, columns=COLUMNS)
     return error
+
+
+def pck(pix_errors, ratio=0.5):
+    """Percentage of correct keypoints over all cameras, as save_error_dists computes it (src/core/metrics.py:36-45): share of
+    rows whose pixel residual is <= ratio * nose-to-eye distance; rows without a threshold (NaN) count as incorrect."""
+    dist = np.concatenate([np.asarray(df['pixel_residual'], dtype=np.float64) for df in pix_errors.values()] or [np.zeros(0)])
+    thr = np.concatenate([np.asarray(df['pck_threshold'], dtype=np.float64) for df in pix_errors.values()] or [np.zeros(0)])
+    if len(dist) == 0:
+        return float('nan')
+    return float(100.0 * (np.sum(dist <= (ratio * thr)) / len(dist)))

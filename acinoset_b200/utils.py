@@ -2,6 +2,8 @@
 plus the scene IO helpers the hot path's callers use (same JSON format, src/lib/utils.py:55-74,186-203).
 """
 import json
+import os
+from glob import glob
 from datetime import datetime
 import numpy as np
 import pandas as pd
@@ -115,3 +117,67 @@ def create_board_object_pts(board_shape, square_edge_length):
     object_pts = np.zeros((board_shape[0] * board_shape[1], 3), np.float32)
     object_pts[:, :2] = np.mgrid[0:board_shape[0], 0:board_shape[1]].T.reshape(-1, 2) * square_edge_length
     return object_pts
+
+
+def project_3d_cheetah_to_2d(position3d_arr, k_arr, d_arr, r_arr, t_arr, cam_res, bodyparts, start_frame):
+    """The numeric core of save_3d_cheetah_as_2d (src/lib/utils.py:248-268): per camera a DLC-shaped DataFrame (columns
+    MultiIndex bodyparts x [x, y, likelihood], index start_frame..) of the reprojected positions, pixels outside the image
+    set to NaN, likelihood NaN. A single positions array is projected into all cameras by ONE kernel launch; a per-camera
+    list (the reference accepts one, utils.py:249-250) takes one launch per entry."""
+    from . import calib
+    n_cams = len(k_arr)
+    pdindex = pd.MultiIndex.from_product([bodyparts, ['x', 'y', 'likelihood']], names=['bodyparts', 'coords'])
+    if isinstance(position3d_arr, list):
+        pos = [np.asarray(p, dtype=np.float64) for p in position3d_arr]
+        prj = [calib.project_points_fisheye_all(pos[i], k_arr[i:i + 1], np.asarray(d_arr)[i:i + 1], r_arr[i:i + 1], t_arr[i:i + 1],
+                                                cam_res)[0] for i in range(n_cams)]
+    else:
+        pos = [np.asarray(position3d_arr, dtype=np.float64)] * n_cams
+        prj = calib.project_points_fisheye_all(pos[0], k_arr, d_arr, r_arr, t_arr, cam_res)
+    out = []
+    for i in range(n_cams):
+        n_frames = len(pos[i])
+        data = np.full(pos[i].shape, np.nan)
+        data[:, :, 0:2] = prj[i].reshape((n_frames, -1, 2))
+        out.append(pd.DataFrame(data.reshape((n_frames, -1)), columns=pdindex, index=range(start_frame, start_frame + n_frames)))
+    return out
+
+
+def save_3d_cheetah_as_2d(position3d_arr, out_dir, scene_fpath, bodyparts, project_func, start_frame, save_as_csv=True,
+                          out_fname=None):
+    """src/lib/utils.py:237-283, same arguments, files and return value. `project_func` selects the camera model as in the
+    reference; only the fisheye model is implemented here. The .h5 copy needs PyTables, like the reference; when it is not
+    importable the .csv is still written and the .h5 skipped with a message."""
+    assert os.path.dirname(os.path.dirname(scene_fpath)) in out_dir, 'scene_fpath does not belong to the same parent folder as out_dir'
+    if getattr(project_func, '__name__', '') != 'project_points_fisheye':
+        raise NotImplementedError('only the fisheye camera model is implemented')
+    video_fpaths = sorted(glob(os.path.join(out_dir, 'cam[1-9].mp4')))
+    if not video_fpaths:
+        video_fpaths = sorted(glob(os.path.join(os.path.dirname(out_dir), 'cam[1-9].mp4')))
+    if not video_fpaths:
+        print('Could not save 3D cheetah to 2D - No videos were found in', out_dir, 'or', os.path.dirname(out_dir))
+        return []
+    k_arr, d_arr, r_arr, t_arr, cam_res = load_scene(scene_fpath, verbose=False)
+    assert len(k_arr) == len(video_fpaths)
+    out_fname = os.path.basename(out_dir) if out_fname is None else out_fname
+    result_dfs = project_3d_cheetah_to_2d(position3d_arr, k_arr, d_arr, r_arr, t_arr, cam_res, bodyparts, start_frame)
+    try:
+        import tables  # noqa: F401
+        have_h5 = True
+    except ImportError:
+        have_h5 = False
+        print('PyTables is not installed: .h5 output skipped')
+    for i, df in enumerate(result_dfs):
+        cam_name = os.path.splitext(os.path.basename(video_fpaths[i]))[0]
+        fpath = os.path.join(out_dir, cam_name + '_' + out_fname + '.h5')
+        if have_h5:
+            df.to_hdf(fpath, key=f'{out_fname}_df', format='table', mode='w')
+        if save_as_csv:
+            df.to_csv(os.path.splitext(fpath)[0] + '.csv')
+    fpath = fpath.replace(cam_name, 'cam*')
+    if have_h5:
+        print('Saved', fpath)
+    if save_as_csv:
+        print('Saved', os.path.splitext(fpath)[0] + '.csv')
+    print()
+    return result_dfs

@@ -46,6 +46,10 @@ int acino_sync(void);
  * X double[N][3] -> uv double[N][2]. Host pointers. */
 int acino_project(const double* X, int64_t N, const double* cam24, double* uv);
 int acino_project_dev(const double* X_dev, int64_t N, const double* cam24_host, double* uv_dev, void* stream);
+/* K1 for all cameras in one launch — the projection loop of save_3d_cheetah_as_2d, src/lib/utils.py:255-263.
+ * X double[N][3] -> uv double[n_cams][N][2]. width > 0 applies the reference's range rule (a pixel outside
+ * [0,width] x [0,height] becomes NaN, utils.py:262-263); width <= 0 leaves pixels as projected. Host pointers. */
+int acino_project_all(const double* X, int64_t N, const double* cams24, int n_cams, double width, double height, double* uv);
 
 /* K1 — cost_func_points_only / cost_func_points_extrinsics, src/lib/sba.py:142-153, on observation
  * lists: f[2*o], f[2*o+1] = proj(X[point_idx[o]], cam cam_idx[o]) - points_2d[o]. Host pointers. */

@@ -138,6 +138,44 @@ def gen_metric():
     print('metric:', {c: len(e) for c, e in err.items()})
 
 
+def gen_project2d():
+    """N2: the reference's save_3d_cheetah_as_2d (src/lib/utils.py:237-283) on the C1 positions array. PyTables is not in the
+    image, so DataFrame.to_hdf is stubbed for the call (harness shim, like np.int): the projection, range rule and table
+    layout are the reference's own code."""
+    import tempfile
+    import pandas as pd
+    calib, utils, sba = ref_shim.load()
+    g = np.load(os.path.join(GOLD, 'golden_c1.npz'))
+    from acinoset_b200 import synth
+    markers = synth.MARKERS[:20]
+    pos = np.full((102, 20, 3), np.nan)
+    rank = {m: i for i, m in enumerate(markers)}
+    for f, m, p in zip(g['frame'], g['marker'], g['obj_pts']):
+        pos[int(f) - 69, rank[str(m)]] = p
+    # some rows well outside every image, to exercise the range rule
+    pos[3, 4] = [40.0, 6.0, 0.5]
+    pos[7, 2] = [-30.0, 7.0, 0.2]
+    saved = pd.DataFrame.to_hdf
+    pd.DataFrame.to_hdf = lambda self, *a, **k: None
+    try:
+        with tempfile.TemporaryDirectory() as td:
+            data_dir = os.path.join(td, 'run'); out_dir = os.path.join(data_dir, 'sba')
+            os.makedirs(os.path.join(data_dir, 'extrinsic_calib')); os.makedirs(out_dir)
+            scene = os.path.join(data_dir, 'extrinsic_calib', '6_cam_scene_sba.json')
+            with open(os.path.join(GOLD, 'scene_6cam.json')) as fi, open(scene, 'w') as fo:
+                fo.write(fi.read())
+            for c in range(6):
+                open(os.path.join(data_dir, f'cam{c + 1}.mp4'), 'w').close()
+            with ref_shim.quiet():
+                dfs = utils.save_3d_cheetah_as_2d(pos, out_dir, scene, markers, calib.project_points_fisheye, 69, save_as_csv=False)
+    finally:
+        pd.DataFrame.to_hdf = saved
+    assert len(dfs) == 6
+    np.savez_compressed(os.path.join(GOLD, 'golden_project2d.npz'), positions=pos, tables=np.stack([d.to_numpy() for d in dfs]),
+                        index=np.array(dfs[0].index), versions=_versions())
+    print('project2d:', np.stack([d.to_numpy() for d in dfs]).shape, 'nan rows', int(np.isnan(dfs[0].to_numpy()[:, 0::3]).sum()))
+
+
 def main():
     what = sys.argv[1] if len(sys.argv) > 1 else 'all'
     os.makedirs(GOLD, exist_ok=True)
@@ -153,6 +191,8 @@ def main():
         gen_calib()
     if what in ('metric', 'all'):
         gen_metric()
+    if what in ('project2d', 'all'):
+        gen_project2d()
 
 
 if __name__ == '__main__':

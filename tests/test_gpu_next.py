@@ -74,3 +74,54 @@ def test_dense_pipeline_equals_dataframe_pipeline(golden_dir):
     assert np.array_equal(np.isnan(pos), np.isnan(want2))
     assert np.array_equal(pos[~np.isnan(pos)], want2[~np.isnan(want2)])
     assert st['n_unconverged'] == 0
+
+
+def test_project_all_cameras_vs_reference_golden(golden_dir, tmp_path):
+    """N2: save_3d_cheetah_as_2d (src/lib/utils.py:237-283) — all cameras in one launch, reference range rule on the device."""
+    g = np.load(os.path.join(golden_dir, 'golden_project2d.npz'))
+    sc = synth.make_rig_scene(2, 2, seed=0)
+    markers = synth.MARKERS[:20]
+    k, d, r, t, res = utils.load_scene(os.path.join(golden_dir, 'scene_6cam.json'), verbose=False)
+    dfs = utils.project_3d_cheetah_to_2d(g['positions'], k, d, r, t, res, markers, 69)
+    assert len(dfs) == 6
+    for c in range(6):
+        a, b = dfs[c].to_numpy(), g['tables'][c]
+        assert np.array_equal(np.isnan(a), np.isnan(b)), c
+        m = ~np.isnan(b)
+        assert np.abs(a[m] - b[m]).max() < 1e-9 * 2704
+        assert list(dfs[c].index) == list(g['index'])
+        assert list(dfs[c].columns.get_level_values(0)[::3]) == markers
+    # a per-camera list of position arrays (utils.py:249-250) gives the same tables
+    dfs2 = utils.project_3d_cheetah_to_2d([g['positions']] * 6, k, d, r, t, res, markers, 69)
+    for c in range(6):
+        assert np.array_equal(dfs2[c].to_numpy(), dfs[c].to_numpy(), equal_nan=True)
+    # file-level drop-in: same directory contract, csv written
+    data_dir = tmp_path / 'run'; out_dir = data_dir / 'sba'
+    (data_dir / 'extrinsic_calib').mkdir(parents=True); out_dir.mkdir()
+    scene = data_dir / 'extrinsic_calib' / '6_cam_scene_sba.json'
+    scene.write_text(open(os.path.join(golden_dir, 'scene_6cam.json')).read())
+    for c in range(6):
+        (data_dir / f'cam{c + 1}.mp4').write_text('')
+    out = utils.save_3d_cheetah_as_2d(g['positions'], str(out_dir), str(scene), markers, calib.project_points_fisheye, 69)
+    assert len(out) == 6 and (out_dir / 'cam3_sba.csv').exists()
+    back = pd.read_csv(out_dir / 'cam3_sba.csv', header=[0, 1], index_col=0)
+    assert np.allclose(back.to_numpy(), g['tables'][2], rtol=0, atol=1e-6, equal_nan=True)
+    # no videos -> empty list, as the reference
+    assert utils.save_3d_cheetah_as_2d(g['positions'], str(tmp_path / 'run2' / 'sba'), str(tmp_path / 'run2' / 'x' / 's.json'), markers,
+                                       calib.project_points_fisheye, 69) == []
+    # plain projection of every camera equals the per-camera call bit for bit
+    X = np.nan_to_num(g['positions']).reshape(-1, 3)
+    all_ = calib.project_points_fisheye_all(X, k, d, r, t)
+    for c in range(6):
+        assert np.array_equal(all_[c], calib.project_points_fisheye(X, k[c], d[c], r[c], t[c]), equal_nan=True)
+
+
+def test_pck_matches_reference_formula(golden_dir):
+    g = np.load(os.path.join(golden_dir, 'golden_metric.npz'))
+    errs = {str(c): pd.DataFrame({'pixel_residual': g[f'cam{c}_pixel_residual'].astype(str), 'pck_threshold': g[f'cam{c}_pck_threshold'].astype(str)})
+            for c in range(6)}
+    dist = np.concatenate([g[f'cam{c}_pixel_residual'] for c in range(6)])
+    thr = np.concatenate([g[f'cam{c}_pck_threshold'] for c in range(6)])
+    want = 100.0 * (np.sum(dist <= 0.5 * thr) / len(dist))           # src/core/metrics.py:45
+    assert metric.pck(errs) == want
+    assert np.isnan(metric.pck({}))

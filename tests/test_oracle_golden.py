@@ -108,3 +108,24 @@ def test_sparsity_pattern_shapes():
     # shipped: obs 0 (camera 0) marks columns 0..5; consistent: rvec 0..2 and tvec 9..11
     assert S[0, :6].all() and not S[0, 6:18].any()
     assert Cn[0, [0, 1, 2, 9, 10, 11]].all() and Cn[0, :18].sum() == 6
+
+
+def test_oracle_projection_vs_reference_project2d_golden(golden_dir):
+    """N2 oracle pin: numpy projection + the range rule of save_3d_cheetah_as_2d (src/lib/utils.py:261-266) against the
+    tables the reference function itself produced."""
+    import os
+    import numpy as np
+    from oracle import fisheye_np as fe
+    from acinoset_b200 import synth
+    g = np.load(os.path.join(golden_dir, 'golden_project2d.npz'))
+    k, d, r, t, res = synth.load_rig(os.path.join(golden_dir, 'scene_6cam.json'))
+    pos = g['positions']
+    for c in range(6):
+        prj = fe.project_points_fisheye(pos.reshape(-1, 3), k[c], d[c], r[c], t[c])
+        bad = np.where((prj > np.array(res)) | (prj < 0))[0]
+        prj[bad] = np.nan
+        want = g['tables'][c].reshape(102, 20, 3)[:, :, :2].reshape(-1, 2)
+        assert np.array_equal(np.isnan(prj), np.isnan(want))
+        m = ~np.isnan(want)
+        assert np.abs(prj[m] - want[m]).max() < 1e-8
+        assert np.isnan(g['tables'][c].reshape(102, 20, 3)[:, :, 2]).all()
