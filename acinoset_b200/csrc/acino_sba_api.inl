@@ -57,6 +57,7 @@ static LmParams make_lm_params(const acino_sba_opts* o, int inner) {
   p.inner_iters = inner;
   p.force = o->force_iters;
   p.ignore_status = 0;
+  p.skip_pred = 0.0;
   return p;
 }
 
@@ -157,6 +158,7 @@ void acino_sba_default_opts(acino_sba_opts* o, int mode) {
     o->ftol = 1e-14;
     o->hess_floor = 0.3;
     o->point_refine_iters = 2;
+    o->point_refine_skip = 1e-11;
     o->lambda0 = 1e-4;
   } else {
     o->max_iter = 200;

@@ -54,6 +54,25 @@ __device__ __forceinline__ void eval_point(const double* __restrict__ sc, const 
   ne.V[0] = v0; ne.V[1] = v1; ne.V[2] = v2; ne.V[3] = v3; ne.V[4] = v4; ne.V[5] = v5;
 }
 
+// robust cost of one point (no derivatives): the trial evaluation of the last LM iteration of a launch
+template <int C>
+__device__ __forceinline__ double eval_point_cost(const double* __restrict__ sc, const double2* uvr, int stride, unsigned m,
+                                                  double X, double Y, double Z, double inv_c2, double half_c2) {
+  double pm1 = 0.0;
+#pragma unroll 1
+  for (int c = 0; c < C; ++c) {
+    if (m >> c & 1) {
+      const double* cam = sc + c * CAM_STRIDE;
+      double x, y, z, u, v;
+      to_camera(cam, X, Y, Z, x, y, z);
+      fisheye_uv(cam, x, y, z, u, v);
+      double2 ob = uvr[c * stride];
+      cauchy_accum(u - ob.x, v - ob.y, inv_c2, pm1);
+    }
+  }
+  return half_c2 * log1p(pm1);
+}
+
 // solve (V + lam*D) d = -g by LDL^T, D = diag(V) floored; returns predicted reduction of the model
 __device__ __forceinline__ double lm_step3(const NormalEq& ne, double lam, double* d) {
   double dmax = fmax(ne.V[0], fmax(ne.V[3], ne.V[5]));
@@ -61,14 +80,14 @@ __device__ __forceinline__ double lm_step3(const NormalEq& ne, double lam, doubl
   double D0 = fmax(ne.V[0], flo), D1 = fmax(ne.V[3], flo), D2 = fmax(ne.V[5], flo);
   double a = fma(lam, D0, ne.V[0]), b = ne.V[1], c = ne.V[2];
   double dd = fma(lam, D1, ne.V[3]), e = ne.V[4], f = fma(lam, D2, ne.V[5]);
-  double ia = 1.0 / a;
+  double ia = rcp_nr(a);
   double l10 = b * ia, l20 = c * ia;
   double d1 = fma(-l10, b, dd);
   double e1 = fma(-l20, b, e);
-  double id1 = 1.0 / d1;
+  double id1 = rcp_nr(d1);
   double l21 = e1 * id1;
   double f2 = fma(-l21, e1, fma(-l20, c, f));
-  double if2 = 1.0 / f2;
+  double if2 = rcp_nr(f2);
   double y0 = -ne.g[0];
   double y1 = fma(-l10, y0, -ne.g[1]);
   double y2 = fma(-l21, y1, fma(-l20, y0, -ne.g[2]));
@@ -89,6 +108,7 @@ struct LmParams {
   double inv_c2, half_c2, gtol, xtol, lambda0;
   int inner_iters, force;
   int ignore_status;   // 1: every observed point restarts as active (the cameras moved since its status was written)
+  double skip_pred;    // > 0: leave a point alone when the model predicts a decrease <= skip_pred * max(cost_p, C^2/2)
 };
 
 // optional device-side control of a launch (the points+extrinsics solver refines points between camera steps):
@@ -137,8 +157,11 @@ lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs
         if (!prm.force && !(gmax > prm.gtol)) { st = ST_CONVERGED; break; }
         double d[3];
         double pred = lm_step3(ne, lam, d);
+        if (prm.skip_pred > 0.0 && pred <= prm.skip_pred * fmax(ne.F, prm.half_c2)) break;     // nothing to gain (refinement between camera steps)
         NormalEq nt;
-        eval_point<C>(sc, uvr, 128, m, X + d[0], Y + d[1], Z + d[2], prm.inv_c2, prm.half_c2, nt);
+        const bool last = (it + 1 == prm.inner_iters);      // no further linearisation in this launch: cost only
+        if (last) nt.F = eval_point_cost<C>(sc, uvr, 128, m, X + d[0], Y + d[1], Z + d[2], prm.inv_c2, prm.half_c2);
+        else eval_point<C>(sc, uvr, 128, m, X + d[0], Y + d[1], Z + d[2], prm.inv_c2, prm.half_c2, nt);
         double act = ne.F - nt.F;
         if (act > 0.0 && pred > 0.0) {          // NaN-safe: comparisons fail on a non-finite trial cost
           double rho = act / pred;
@@ -149,7 +172,7 @@ lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs
           double dmax = fmax(fabs(d[0]), fmax(fabs(d[1]), fabs(d[2])));
           double xmax = fmax(fabs(X), fmax(fabs(Y), fabs(Z)));
           X += d[0]; Y += d[1]; Z += d[2];
-          ne = nt;
+          if (last) ne.F = nt.F; else ne = nt;
           if (!prm.force && dmax <= prm.xtol * (xmax + prm.xtol)) { st = ST_CONVERGED; break; }
         } else {
           lam *= nu;

@@ -41,7 +41,7 @@ struct SchurLm {
 };
 
 struct SchurParams {
-  double inv_c2, half_c2, gtol, ftol, xtol, hfloor;
+  double inv_c2, half_c2, gtol, ftol, xtol, hfloor, refine_skip;
   int force, refine;
 };
 
@@ -793,7 +793,7 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
     lm->need_cost = prm.refine > 0;
     lm->last_rel_dec = act / F;
     if (!prm.force) {
-      if (act <= prm.ftol * F) lm->status = 2;
+      if (act <= prm.ftol * F && rho > 0.25) lm->status = 2;      // scipy trf check_termination: dF < ftol*F and ratio > 0.25
       else if (c <= prm.xtol * (lm->xmax + prm.xtol)) lm->status = 3;
     }
   } else {

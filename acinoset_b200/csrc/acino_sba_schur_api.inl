@@ -114,6 +114,7 @@ static SchurParams make_schur_params(const acino_sba_opts* o) {
   p.hfloor = o->hess_floor > 0 ? o->hess_floor : 0.3;
   p.force = o->force_iters;
   p.refine = o->point_refine_iters > 0 ? (int)o->point_refine_iters : 0;
+  p.refine_skip = o->point_refine_skip > 0 ? o->point_refine_skip : 0.0;
   return p;
 }
 
@@ -182,6 +183,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
     LmParams lp;
     lp.inv_c2 = prm.inv_c2; lp.half_c2 = prm.half_c2; lp.gtol = prm.gtol; lp.xtol = prm.xtol; lp.lambda0 = 1e-4;
     lp.inner_iters = prm.refine; lp.force = 0; lp.ignore_status = 1;
+    lp.skip_pred = prm.refine_skip;
     LmPointsCtl ctl{&s.lm->last_accept, &s.lm->cur, s.cams_alt, s.X_alt};
     DISPATCH_C(C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, st>>>(h->uv, h->mask, h->P, h->cams, h->X, h->lam, h->cost_p,
                                                                           h->status, lp, h->counters, ctl)));
@@ -375,7 +377,7 @@ int acino_sba_profile_read(acino_sba_t* h, double* build_ms, double* backsub_ms,
   return ACINO_OK;
 }
 
-int acino_sba_lm_state(acino_sba_t* h, double* out6) {
+int acino_sba_lm_state(acino_sba_t* h, double* out6) {   // 16 doubles
   H_CHECK(h);
   ARG_CHECK(out6, "lm_state");
   SchurState& s = h->schur;
@@ -384,6 +386,9 @@ int acino_sba_lm_state(acino_sba_t* h, double* out6) {
   ACINO_CUDA(cudaStreamSynchronize(h->stream));
   out6[0] = s.h_lm->F; out6[1] = s.h_lm->lambda; out6[2] = s.h_lm->gmax; out6[3] = s.h_lm->iter;
   out6[4] = s.h_lm->n_accept; out6[5] = s.h_lm->status;
+  out6[6] = s.h_lm->F_trial; out6[7] = s.h_lm->pred; out6[8] = s.h_lm->rho; out6[9] = s.h_lm->dxmax; out6[10] = s.h_lm->xmax;
+  out6[11] = s.h_lm->nu; out6[12] = s.h_lm->last_rel_dec; out6[13] = s.h_lm->n_reject; out6[14] = s.h_lm->chol_fail;
+  out6[15] = s.h_lm->F0;
   return ACINO_OK;
 }
 

@@ -167,9 +167,11 @@ class SbaSolver:
         return dict(build_ms=b.value, backsub_ms=k.value, iterations=n.value)
 
     def lm_state(self):
-        out = np.empty(6)
+        out = np.empty(16)
         _capi.check(_capi.lib().acino_sba_lm_state(self._h, _capi.ptr(out)))
-        return dict(cost=out[0], lam=out[1], gmax=out[2], iterations=int(out[3]), accepted=int(out[4]), status=int(out[5]))
+        return dict(cost=out[0], lam=out[1], gmax=out[2], iterations=int(out[3]), accepted=int(out[4]), status=int(out[5]),
+                    cost_trial=out[6], pred=out[7], rho=out[8], dxmax=out[9], xmax=out[10], nu=out[11], last_rel_dec=out[12],
+                    rejected=int(out[13]), chol_fail=int(out[14]), cost_first=out[15])
 
     @property
     def stream(self):

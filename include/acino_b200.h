@@ -96,7 +96,8 @@ typedef struct {
                               (rho' + 2 rho'' f^2 = rho' (1-z)/(1+z) is negative beyond |f| > C): 1.0 = plain IRLS weights */
   double point_refine_iters; /* points+extrinsics: after every accepted step, this many per-point LM iterations with
                                 the cameras fixed (K3 on the current buffers; each point has its own damping) */
-  double reserved[1];
+  double point_refine_skip;  /* the refinement leaves a point alone when its model predicts a cost decrease
+                              * <= point_refine_skip * max(cost of the point, f_scale^2/2); 0 = refine every point */
 } acino_sba_opts;
 
 typedef struct {
@@ -136,8 +137,10 @@ void* acino_sba_stream(acino_sba_t* h);
  * enable, run <=256 iterations, read the averages in ms (build = K4 residual+Jacobian+Schur, backsub = K6). */
 int acino_sba_profile(acino_sba_t* h, int enable);
 int acino_sba_profile_read(acino_sba_t* h, double* build_ms, double* backsub_ms, int* n_iterations);
-/* LM state after iterate / solve: out[0]=cost, [1]=lambda, [2]=gmax, [3]=iterations, [4]=accepted, [5]=status */
-int acino_sba_lm_state(acino_sba_t* h, double* out6);
+/* LM state after iterate / solve: out[0]=cost, [1]=lambda, [2]=gmax, [3]=iterations, [4]=accepted, [5]=status,
+ * [6]=trial cost, [7]=predicted reduction, [8]=gain ratio, [9]=max |dx|, [10]=max |x|, [11]=nu, [12]=relative decrease of
+ * the last accepted step, [13]=rejected, [14]=Cholesky failures, [15]=cost at the first linearisation */
+int acino_sba_lm_state(acino_sba_t* h, double* out16);
 
 /* multi-GPU (frame-sharded) — one handle per rank; NCCL is dlopen'ed from the process (libnccl.so.2). Every rank
  * calls solve / iterate collectively; the reduced camera system (6C x 6C + gradient + cost) is all-reduced once per LM

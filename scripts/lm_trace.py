@@ -8,7 +8,7 @@ frames = int(sys.argv[1]) if len(sys.argv) > 1 else 2000
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 60
 fscale = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0
 hfloor = float(sys.argv[4]) if len(sys.argv) > 4 else 0.3
-refine = float(sys.argv[5]) if len(sys.argv) > 5 else 0
+refine = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 sc = synth.make_rig_scene(frames, 20, seed=4)
 k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
 xyz, exists, mask = dense.triangulate_ring(sc['uv'], sc['lik'], 0.5, k, d, r, t)
@@ -23,6 +23,6 @@ o = dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, f_scale=fscale, hess_fl
 for i in range(iters):
     s.iterate(o)
     st = s.lm_state()
-    if i % 5 == 0 or st['status']: print(i, f"cost {st['cost']:.10e} lam {st['lam']:.3e} gmax {st['gmax']:.3e} acc {st['accepted']} status {st['status']}")
+    if True: print(i, f"cost {st['cost']:.10e} lam {st['lam']:.3e} gmax {st['gmax']:.3e} acc {st['accepted']} status {st['status']} Ftrial {st['cost_trial']:.10e} pred {st['pred']:.3e} rho {st['rho']:.3f} dx {st['dxmax']:.2e} chol {st['chol_fail']}")
     if st['status']:
         break
