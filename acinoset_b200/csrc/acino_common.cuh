@@ -72,6 +72,13 @@ __device__ __forceinline__ double atan_ratio(double rho, double irho, double az,
   return inv ? 1.5707963267948966 - th : th;
 }
 
+// ---- 8-byte asynchronous global -> shared copy (LDGSTS) and its completion wait
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gmem_src) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // ---- camera in shared memory ----------------------------------------------------------------
 // c points at 24 doubles: fx fy cx cy alpha k1 k2 k3 k4 R[9] t[3] pad[3]
 __device__ __forceinline__ void to_camera(const double* __restrict__ c, double X, double Y, double Z,

@@ -149,7 +149,7 @@ struct SchurSmem {
   static constexpr int NW = BT / 32;
   static constexpr int LEN = rcs_len(C);
   static constexpr int BS = BT + 1;       // row stride of the staged arrays (odd: spreads the per-observation writes over banks)
-  static constexpr size_t n_doubles = (size_t)C * CAM_STRIDE + (size_t)C * 8 * BS + 12 * BS + LEN;
+  static constexpr size_t n_doubles = (size_t)C * CAM_STRIDE + (size_t)C * 8 * BS + 15 * BS + LEN;   // sX is double-buffered
   static constexpr size_t bytes = n_doubles * 8 + (size_t)NU * BT * 2 + (size_t)C * BT * 2 + NW * 4 + 16 + NU * 2 + BT + 16;
 };
 
@@ -166,8 +166,8 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   double* sc = reinterpret_cast<double*>(smem_raw);
   double* sN = sc + C * CAM_STRIDE;          // [(c*6+k)*BS + q]
   double* sE = sN + (size_t)C * 6 * BS;      // [(c*2+k)*BS + q]
-  double* sX = sE + (size_t)C * 2 * BS;      // [k*BS + q], k<3
-  double* sVi = sX + 3 * BS;                 // [k*BS + q], k<6: 00 01 02 11 12 22
+  double* sXbuf = sE + (size_t)C * 2 * BS;   // two buffers of [k*BS + q], k<3: the next tile's points arrive by cp.async
+  double* sVi = sXbuf + 6 * BS;              // [k*BS + q], k<6: 00 01 02 11 12 22
   double* sH = sVi + 6 * BS;                 // [k*BS + q], k<3
   double* sS = sH + 3 * BS;                  // [LEN]
   unsigned short* list = reinterpret_cast<unsigned short*>(sS + LEN);   // [u*BT + i] points of unit u
@@ -199,15 +199,25 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0;
   double cprod = 1.0;     // running product of (1+z_u)(1+z_v): sum of log1p(z) = log of the product
   const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
+  // the first tile's points and mask; later tiles are fetched while the previous tile is in phase 2
+  unsigned m_next = 0u;
+  int buf = 0;
+  if ((int64_t)blockIdx.x < n_tiles) {
+    const int64_t p0 = (int64_t)blockIdx.x * BT + tid;
+    if (p0 < P) {
+      m_next = obs_mask[p0];
+      cp_async8(sXbuf + tid, Xp + 3 * p0); cp_async8(sXbuf + BS + tid, Xp + 3 * p0 + 1); cp_async8(sXbuf + 2 * BS + tid, Xp + 3 * p0 + 2);
+    }
+  }
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     // ---------------- phase 1a: stage the points, compact the tile's observations (point-major, camera-minor)
-    const int64_t p = tile * BT + tid;
-    unsigned m = (p < P) ? obs_mask[p] : 0u;
+    double* sX = sXbuf + buf * 3 * BS;
+    const unsigned m = m_next;
     sM[tid] = (unsigned char)m;
+    cp_async_wait_all();
     {
       if (m) {
-        double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
-        sX[tid] = X; sX[BS + tid] = Y; sX[2 * BS + tid] = Z;
+        double X = sX[tid], Y = sX[BS + tid], Z = sX[2 * BS + tid];
         xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
       }
       int k = __popc(m), incl = k;
@@ -279,6 +289,16 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       gmax_acc = fmax(gmax_acc, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
     }
     if (tid == 0) next_unit[0] = 0;
+    {   // fetch the next tile's points (other buffer) and mask: the latency hides behind phase 2
+      const int64_t pn = (tile + gridDim.x) * BT + tid;
+      m_next = 0u;
+      if (pn < P) {
+        double* sXn = sXbuf + (buf ^ 1) * 3 * BS;
+        m_next = obs_mask[pn];
+        cp_async8(sXn + tid, Xp + 3 * pn); cp_async8(sXn + BS + tid, Xp + 3 * pn + 1); cp_async8(sXn + 2 * BS + tid, Xp + 3 * pn + 2);
+      }
+      buf ^= 1;
+    }
     __syncthreads();
     // ---------------- phase 2: warps take units (longest first: diagonal units lead) until none is left
     for (;;) {
