@@ -8,6 +8,7 @@
 #include "acino_tri.cuh"
 #include "acino_sba_points.cuh"
 #include "acino_sba_schur.cuh"
+#include "acino_calib.cuh"
 
 namespace acino {
 static thread_local char g_err[512] = "";
@@ -221,5 +222,55 @@ int acino_triangulate_ring(const double* uv, const double* lik, double thresh, i
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------- N3: calibration-loop callers of K1/K2
+int acino_manual_residuals(const double* img_pts, int n_points, const double* cams24, int n_cams, const int32_t* correct_cams,
+                           int n_correct, const int32_t* cam_pairs, int n_pairs, const double* params, int n_batch,
+                           double loss_a, double loss_b, double loss_c, double* f) {
+  ARG_CHECK(n_points >= 0 && n_cams > 0 && n_cams <= 32 && n_pairs >= 0 && n_batch >= 0 && n_correct >= 0, "manual_residuals sizes");
+  if (n_points == 0 || n_pairs == 0 || n_batch == 0) return ACINO_OK;
+  ARG_CHECK(img_pts && cams24 && cam_pairs && params && f && (n_correct == 0 || correct_cams), "manual_residuals null pointer");
+  ARG_CHECK(loss_a < loss_b && loss_b < loss_c, "manual_residuals: loss needs a < b < c");
+  unsigned mask = 0;
+  for (int i = 0; i < n_correct; ++i) {
+    ARG_CHECK(correct_cams[i] >= 0 && correct_cams[i] < n_cams, "manual_residuals: camera index out of range");
+    mask |= 1u << correct_cams[i];
+  }
+  for (int i = 0; i < 2 * n_pairs; ++i) ARG_CHECK(cam_pairs[i] >= 0 && cam_pairs[i] < n_cams, "manual_residuals: pair index out of range");
+  const size_t smem = (size_t)n_batch * n_cams * CAM_STRIDE * sizeof(double);
+  ARG_CHECK(smem <= 200 * 1024, "manual_residuals: batch too large");
+  const size_t n_out = (size_t)n_batch * n_cams * n_pairs * n_points;
+  DevBuf dI, dC, dP, dX, dF;
+  ACINO_CUDA(dI.alloc((size_t)n_points * n_cams * 2 * sizeof(double)));
+  ACINO_CUDA(dC.alloc((size_t)n_cams * CAM_STRIDE * sizeof(double)));
+  ACINO_CUDA(dP.alloc((size_t)n_pairs * 2 * sizeof(int32_t)));
+  ACINO_CUDA(dX.alloc((size_t)n_batch * 6 * sizeof(double)));
+  ACINO_CUDA(dF.alloc(n_out * 2 * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(dI.p, img_pts, (size_t)n_points * n_cams * 2 * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dC.p, cams24, (size_t)n_cams * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dP.p, cam_pairs, (size_t)n_pairs * 2 * sizeof(int32_t), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dX.p, params, (size_t)n_batch * 6 * sizeof(double), cudaMemcpyHostToDevice));
+  if (smem > 48 * 1024)
+    ACINO_CUDA(cudaFuncSetAttribute(manual_residuals_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int total = n_batch * n_pairs * n_points;
+  manual_residuals_kernel<<<(total + 127) / 128, 128, smem>>>(dI.as<double2>(), n_points, dC.as<double>(), n_cams, mask, dP.as<int>(),
+                                                             n_pairs, dX.as<double>(), n_batch, loss_a, loss_b, loss_c, dF.as<double2>());
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaMemcpy(f, dF.p, n_out * 2 * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
+int acino_ring_critical(const double* lik, int64_t P, int n_cams, double* crit) {
+  ARG_CHECK(P >= 0 && n_cams > 0 && n_cams <= 64 && (P == 0 || (lik && crit)), "ring_critical");
+  if (P == 0) return ACINO_OK;
+  DevBuf dL, dO;
+  ACINO_CUDA(dL.alloc((size_t)P * n_cams * sizeof(double)));
+  ACINO_CUDA(dO.alloc((size_t)P * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(dL.p, lik, (size_t)P * n_cams * sizeof(double), cudaMemcpyHostToDevice));
+  ring_critical_kernel<<<grid_for(P, 256), 256>>>(dL.as<double>(), P, n_cams, dO.as<double>());
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaMemcpy(crit, dO.p, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
 
 #include "acino_sba_api.inl"

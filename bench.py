@@ -388,6 +388,25 @@ def main():
                                           achieved=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9,
                                           frac=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9 / peak)
         roofline['step_share_of_kernels'] = (k6['ms_per_launch'] + k6['backsub_ms']) / ctx['ms_per_step']
+    # DRAM traffic and executed fp64 flops per launch come from the committed ncu capture of the same workload
+    # (profiles/r01_ncu_counts.json); they are attached only when this run IS that workload
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r01_ncu_counts.json')) as f:
+            ncu = json.load(f)
+        w = ncu['workload']
+        if (args.frames, args.masked_frac, args.outlier_frac) == (w['frames'], w['masked_frac'], w['outlier_frac']) and mode == 'extrinsics':
+            def fp64_block(name, ms):
+                k = ncu['kernels'][name]
+                tf = k['fp64_flops'] / (ms * 1e-3) / 1e12
+                return dict(flops_per_launch=k['fp64_flops'], achieved_tflops=tf, peak_tflops=ctx['fp64_peak'], frac=tf / ctx['fp64_peak'],
+                            pipe_active_pct_ncu=k['fp64_pipe_pct'], source='executed DFMA x2 + DMUL + DADD, ncu SASS page (profiles/r01_ncu_counts.json)')
+            roofline['traffic'] = ncu['kernels'][kern_name]['dram_bytes']
+            roofline['traffic_source'] = 'ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r01_ncu_counts.json)'
+            roofline['fp64'] = fp64_block(kern_name, kern_ms)
+            roofline['backsub_kernel']['traffic'] = ncu['kernels'][f'schur_backsub_kernel<{C}>']['dram_bytes']
+            roofline['backsub_kernel']['fp64'] = fp64_block(f'schur_backsub_kernel<{C}>', ctx['kern']['backsub_ms'])
+    except (OSError, KeyError, ValueError):
+        pass
     tri_gbs = tri_bytes(P, C) / (ctx['tri_ms'] * 1e-3) / 1e9
     cb = None
     if not args.no_cpu_baseline and world == 1:

@@ -56,6 +56,20 @@ int acino_project_all(const double* X, int64_t N, const double* cams24, int n_ca
 int acino_residuals_list(const double* X, int64_t n_points, const int32_t* point_idx, const int32_t* cam_idx,
                          const double* points_2d, int64_t n_obs, const double* cams24, int n_cams, double* f);
 
+/* N3 — the residual vector of adjust_extrinsics_manual_points, src/lib/calib.py:224-256, for n_batch candidate
+ * corrections at once (the current (rvec, t) and scipy's forward differences). img_pts double[n_points][n_cams][2];
+ * cameras in correct_cams take (r R^T, t - r t_corr); every pair (a, b) of cam_pairs triangulates all points (K2), every
+ * camera reprojects them (K1), errors pass the reference's redescending loss (src/lib/misc.py:329-343, a<b<c)
+ * elementwise. f double[n_batch][n_cams][n_pairs][n_points][2] = the reference's flatten order. Host pointers. */
+int acino_manual_residuals(const double* img_pts, int n_points, const double* cams24, int n_cams, const int32_t* correct_cams,
+                           int n_correct, const int32_t* cam_pairs, int n_pairs, const double* params, int n_batch,
+                           double loss_a, double loss_b, double loss_c, double* f);
+
+/* N3 — threshold search of initialize_marker_3d, src/lib/app.py:44-57: crit[p] = max over ring pairs of
+ * min(lik[p][c], lik[p][c+1]) = the supremum of thresholds t for which `likelihood > t` still triangulates point p
+ * (-inf when no pair exists; NaN likelihoods never pass). lik double[P][n_cams]. Host pointers. */
+int acino_ring_critical(const double* lik, int64_t P, int n_cams, double* crit);
+
 /* cv::Rodrigues(rvec)->R for n vectors (src/lib/sba.py:29), the device routine the extrinsics solver uses. */
 int acino_rodrigues(const double* rvecs, int n, double* R_out);
 

@@ -1,4 +1,4 @@
-"""Small fixed workload for ncu: C4-sized scene (119,490 frames), TRI x2, 3 Schur LM iterations, 2 points-only LM
+"""Small fixed workload for ncu: C4-sized scene (119,490 frames), TRI x2, 8 Schur LM iterations, 2 points-only LM
 iterations. Usage: python scripts/profile_target.py [frames]"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -25,7 +25,7 @@ s.set_cameras(k, d, r, t); s.set_rvec_t(rv, tv)
 s.set_observations_dev(uv_d, mask_d)
 s.set_points(np.nan_to_num(xyz_d.download()))
 o = dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, force_iters=1)
-for _ in range(3):
+for _ in range(8):      # the first five steps are rejected while the damping grows; 6-8 are accepted (point refinement runs)
     s.iterate(o)
 print('schur', s.lm_state())
 s.reset_state()
