@@ -76,6 +76,47 @@ def make_rig_scene(n_frames, n_kpts=20, seed=0, noise_px=1.0, masked_frac=0.5, o
     return dict(uv=uv, lik=lik, gt=gt, k=k, d=d, r=r, t=t, n_frames=n_frames, n_kpts=n_kpts)
 
 
+def make_track_scene(n_frames, n_kpts=20, seed=0, noise_px=1.0, rig=None):
+    """Like make_rig_scene but the keypoints ride a smooth cubic trajectory through the view volume (a running animal)
+    instead of being redrawn every frame; likelihood ~ U(0,1). For the trajectory-fit callers (initialize_marker_3d)."""
+    k, d, r, t, _ = rig if rig is not None else load_rig()
+    C = len(k)
+    rng = np.random.default_rng(seed)
+    tt = np.linspace(0.0, 1.0, n_frames)
+    base = np.stack([-0.5 + 4.5 * tt + 0.6 * tt ** 2 - 0.8 * tt ** 3, 6.0 + 1.2 * tt - 0.9 * tt ** 2, 0.4 + 0.3 * tt ** 2], axis=1)
+    off = rng.uniform(-0.25, 0.25, (n_kpts, 3))
+    gt = (base[:, None, :] + off[None, :, :]).reshape(-1, 3)
+    uv = np.empty((len(gt), C, 2))
+    for c in range(C):
+        uv[:, c, :] = _project_np(gt, k[c], d[c], r[c], t[c])
+    uv += rng.normal(0.0, noise_px, uv.shape)
+    lik = rng.uniform(size=(len(gt), C))
+    return dict(uv=uv, lik=lik, gt=gt, k=k, d=d, r=r, t=t, n_frames=n_frames, n_kpts=n_kpts)
+
+
+def make_manual_points_case(n_points=14, seed=0, noise_px=0.3, bad_cams=(3, 4, 5), rig=None):
+    """Manually-labelled points seen by every camera, and a rig whose cameras `bad_cams` are off by one common rigid
+    transform (what adjust_extrinsics_manual_points corrects, src/lib/calib.py:216-297).
+    Returns dict(img_pts (N, C, 2), k, d, r_true, t_true, r_bad, t_bad (C,3,1), bad_cams)."""
+    k, d, r, t, _ = rig if rig is not None else load_rig()
+    C = len(k)
+    rng = np.random.default_rng(seed)
+    X = np.stack([rng.uniform(-1, 5, n_points), rng.uniform(5, 8, n_points), rng.uniform(0, 1, n_points)], axis=1)
+    img = np.empty((n_points, C, 2))
+    for c in range(C):
+        img[:, c, :] = _project_np(X, k[c], d[c], r[c], t[c])
+    img += rng.normal(0.0, noise_px, img.shape)
+    Rg = _rot_from_axis_angle(rng.normal(0, 0.01, 3))
+    tg = rng.normal(0, 0.02, (3, 1))
+    r_bad = np.array(r, dtype=np.float64).copy()
+    t_bad = np.array(t, dtype=np.float64).reshape(C, 3, 1).copy()
+    for c in bad_cams:                          # inverse of the reference's update r_f = r_i R^T, t_f = t_i - r_i t
+        r_bad[c] = r[c] @ Rg
+        t_bad[c] = t_bad[c] + r_bad[c] @ tg
+    return dict(img_pts=img, k=k, d=d, r_true=np.array(r), t_true=np.array(t).reshape(C, 3, 1), r_bad=r_bad, t_bad=t_bad,
+                bad_cams=list(bad_cams), gt=X)
+
+
 def dense_to_df(uv, lik, n_kpts, first_frame=0, markers=None):
     """Dense slots -> DataFrame[frame, camera, marker, x, y, likelihood], rows camera-major then
     frame then marker, like load_dlc_points_as_df (src/lib/utils.py:139-147)."""

@@ -1,0 +1,85 @@
+"""TEST INFRASTRUCTURE ONLY — golden vectors for the SURVEY.md §8(f) N3 callers, produced by the REAL reference functions:
+
+  adjust_extrinsics_manual_points (/root/reference/src/lib/calib.py:216-297): run unmodified; scipy's least_squares is
+      wrapped for the duration of the call only to record the closure's residual vector at two parameter points;
+  initialize_marker_3d (/root/reference/src/lib/app.py:39-84): lib/app.py cannot be imported here (it pulls in the
+      OpenGL viewer and video modules), so the function's source text is cut out of the file at generation time and
+      executed unmodified in a namespace holding the reference's own utils / calib / points modules.
+
+    python -m oracle.make_golden_n3
+"""
+import ast
+import os
+import numpy as np
+
+from . import ref_shim
+from .make_golden import GOLD, _versions
+
+
+def gen_adjust():
+    calib, utils, sba = ref_shim.load()
+    from acinoset_b200 import synth
+    rig = synth.load_rig(os.path.join(GOLD, 'scene_6cam.json'))
+    case = synth.make_manual_points_case(14, seed=3, rig=rig)
+    probe = np.array([0.01, -0.02, 0.005, 0.03, -0.01, 0.02])
+    rec = {}
+    real = calib.least_squares
+
+    def spy(fun, x0, *a, **kw):
+        rec['f0'] = np.array(fun(np.asarray(x0, dtype=np.float64)))
+        rec['f_probe'] = np.array(fun(probe))
+        res = real(fun, x0, *a, **kw)
+        rec['x'] = res.x.copy(); rec['cost'] = res.cost; rec['nfev'] = res.nfev; rec['fun'] = res.fun.copy()
+        return res
+
+    calib.least_squares = spy
+    try:
+        r_in = case['r_bad'].copy(); t_in = case['t_bad'].copy()
+        with ref_shim.quiet():
+            r_out, t_out = calib.adjust_extrinsics_manual_points(calib.calibrate_pair_extrinsics_fisheye, case['img_pts'],
+                                                                 case['bad_cams'], case['k'], case['d'], r_in, t_in)
+    finally:
+        calib.least_squares = real
+    np.savez_compressed(os.path.join(GOLD, 'golden_manual_adjust.npz'), probe=probe, f0=rec['f0'], f_probe=rec['f_probe'],
+                        x=rec['x'], cost=rec['cost'], nfev=rec['nfev'], fun=rec['fun'], r_out=np.array(r_out), t_out=np.array(t_out),
+                        versions=_versions())
+    err_before = np.abs(case['r_bad'] - case['r_true']).max()
+    err_after = np.abs(np.array(r_out) - case['r_true']).max()
+    print(f"manual adjust: {len(rec['f0'])} residuals, cost {rec['cost']:.6e}, nfev {rec['nfev']}, |dR| {err_before:.2e} -> {err_after:.2e}")
+
+
+def _cut_function(path, name):
+    src = open(path).read()
+    for node in ast.parse(src).body:
+        if isinstance(node, ast.FunctionDef) and node.name == name:
+            return '\n'.join(src.splitlines()[node.lineno - 1:node.end_lineno])
+    raise KeyError(name)
+
+
+def gen_init_marker():
+    calib, utils, sba = ref_shim.load()
+    from lib import points
+    from acinoset_b200 import synth
+    rig = synth.load_rig(os.path.join(GOLD, 'scene_6cam.json'))
+    sc = synth.make_track_scene(60, 20, seed=2, rig=rig)
+    df = synth.dense_to_df(sc['uv'], sc['lik'], 20, first_frame=10)
+    ns = dict(np=np, utils=utils, triangulate_points_fisheye=calib.triangulate_points_fisheye, EOM_curve_fit=points.EOM_curve_fit,
+              plot_marker_3d=None)
+    exec(compile(_cut_function(os.path.join(ref_shim.REF_SRC, 'lib', 'app.py'), 'initialize_marker_3d'), 'reference:lib/app.py', 'exec'), ns)
+    out = {}
+    import io, contextlib
+    for marker in ('nose', 'spine'):
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            fit, fit_deriv = ns['initialize_marker_3d'](df, marker, sc['k'], sc['d'].reshape((-1, 4)), sc['r'], sc['t'])
+        line = [l for l in buf.getvalue().splitlines() if l.startswith('Initializing')][0]
+        out[f'{marker}_fit'] = fit; out[f'{marker}_fit_deriv'] = fit_deriv; out[f'{marker}_thresh_line'] = line
+        print(line)
+    np.savez_compressed(os.path.join(GOLD, 'golden_init_marker.npz'), versions=_versions(), **out)
+
+
+if __name__ == '__main__':
+    if not ref_shim.available():
+        raise SystemExit('reference tree not present; fixtures can only be generated in the build container')
+    gen_adjust()
+    gen_init_marker()

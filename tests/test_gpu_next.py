@@ -125,3 +125,58 @@ def test_pck_matches_reference_formula(golden_dir):
     want = 100.0 * (np.sum(dist <= 0.5 * thr) / len(dist))           # src/core/metrics.py:45
     assert metric.pck(errs) == want
     assert np.isnan(metric.pck({}))
+
+
+def test_manual_points_residuals_and_adjust_vs_reference_golden(golden_dir):
+    """N3: adjust_extrinsics_manual_points (src/lib/calib.py:216-297): residual vector 1e-9 against the reference's closure,
+    batch == single evaluations, and the corrected extrinsics against the reference's own scipy run."""
+    from oracle import calib_np
+    g = np.load(os.path.join(golden_dir, 'golden_manual_adjust.npz'))
+    case = synth.make_manual_points_case(14, seed=3, rig=synth.load_rig(os.path.join(golden_dir, 'scene_6cam.json')))
+    pairs = [[0, 5], [2, 3], [3, 4], [4, 5]]
+    args = (case['img_pts'], case['bad_cams'], pairs, case['k'], case['d'], case['r_bad'], case['t_bad'])
+    f0 = calib.manual_points_residuals(*args, np.zeros(6))
+    fp = calib.manual_points_residuals(*args, g['probe'])
+    assert np.abs(f0 - g['f0']).max() <= 1e-9 * np.abs(g['f0']).max()
+    assert np.abs(fp - g['f_probe']).max() <= 1e-9 * np.abs(g['f_probe']).max()
+    fo = calib_np.manual_points_residuals(g['probe'], case['img_pts'], case['bad_cams'], pairs, case['k'], case['d'], case['r_bad'], case['t_bad'])
+    assert np.abs(fp - fo).max() <= 1e-9 * np.abs(fo).max()
+    batch = calib.manual_points_residuals(*args, np.stack([np.zeros(6), g['probe'], 0.5 * g['probe']]))
+    assert batch.shape == (3, len(f0)) and np.array_equal(batch[0], f0) and np.array_equal(batch[1], fp)
+    # full drop-in call, in place on copies like the reference
+    r_in, t_in = case['r_bad'].copy(), case['t_bad'].copy()
+    r_out, t_out = calib.adjust_extrinsics_manual_points(calib.calibrate_pair_extrinsics_fisheye, case['img_pts'], case['bad_cams'],
+                                                         case['k'], case['d'], r_in, t_in)
+    assert r_out is r_in and t_out is t_in
+    res = calib.adjust_extrinsics_manual_points.last_result
+    assert abs(res.cost - float(g['cost'])) <= 1e-8 * float(g['cost'])
+    assert np.abs(res.x - g['x']).max() < 1e-6
+    assert np.abs(r_out - g['r_out']).max() < 1e-6 and np.abs(t_out - g['t_out']).max() < 1e-6
+    assert np.abs(r_out - case['r_true']).max() < np.abs(case['r_bad'] - case['r_true']).max() / 5
+    for c in (0, 1, 2):
+        assert np.array_equal(r_out[c], case['r_bad'][c]) and np.array_equal(t_out[c], case['t_bad'][c])
+    with pytest.raises(NotImplementedError):
+        calib.adjust_extrinsics_manual_points(lambda: None, case['img_pts'], 3, case['k'], case['d'], r_in, t_in)
+    # a single integer index is accepted like a list of one
+    r2, t2 = calib.adjust_extrinsics_manual_points(calib.calibrate_pair_extrinsics_fisheye, case['img_pts'], 3, case['k'], case['d'],
+                                                   case['r_bad'].copy(), case['t_bad'].copy())
+    assert r2.shape == (6, 3, 3)
+
+
+def test_initialize_marker_3d_vs_reference_golden(golden_dir, capsys):
+    """N3: initialize_marker_3d (src/lib/app.py:39-84): same interim threshold (one kernel instead of ~20 re-triangulations
+    of the whole table) and the same fitted trajectory as the reference function."""
+    from oracle import calib_np
+    g = np.load(os.path.join(golden_dir, 'golden_init_marker.npz'))
+    sc = synth.make_track_scene(60, 20, seed=2, rig=synth.load_rig(os.path.join(golden_dir, 'scene_6cam.json')))
+    df = synth.dense_to_df(sc['uv'], sc['lik'], 20, first_frame=10)
+    assert np.array_equal(app.ring_critical_likelihood(sc['lik']), calib_np.ring_critical(sc['lik']))
+    lik = sc['lik'][:50].copy(); lik[3, 1] = np.nan; lik[4] = 0.0
+    assert np.array_equal(app.ring_critical_likelihood(lik), calib_np.ring_critical(lik))
+    for marker in ('nose', 'spine'):
+        fit, fit_deriv = app.initialize_marker_3d(df, marker, sc['k'], sc['d'].reshape((-1, 4)), sc['r'], sc['t'])
+        line = [l for l in capsys.readouterr().out.splitlines() if l.startswith('Initializing')][0]
+        assert line == str(g[f'{marker}_thresh_line'])
+        assert fit.shape == (60, 3) and fit_deriv.shape == (60, 3)
+        assert np.abs(fit - g[f'{marker}_fit']).max() < 1e-6
+        assert np.abs(fit_deriv - g[f'{marker}_fit_deriv']).max() < 1e-6

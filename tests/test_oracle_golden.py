@@ -129,3 +129,33 @@ def test_oracle_projection_vs_reference_project2d_golden(golden_dir):
         m = ~np.isnan(want)
         assert np.abs(prj[m] - want[m]).max() < 1e-8
         assert np.isnan(g['tables'][c].reshape(102, 20, 3)[:, :, 2]).all()
+
+
+def test_oracle_manual_adjust_residuals_vs_reference_golden(golden_dir):
+    """N3 oracle pin: residual_arr of adjust_extrinsics_manual_points at two parameter points."""
+    import os
+    import numpy as np
+    from oracle import calib_np
+    from acinoset_b200 import synth
+    g = np.load(os.path.join(golden_dir, 'golden_manual_adjust.npz'))
+    case = synth.make_manual_points_case(14, seed=3, rig=synth.load_rig(os.path.join(golden_dir, 'scene_6cam.json')))
+    pairs = [[2, 3], [3, 4], [4, 5], [0, 5]]
+    pairs = np.unique(pairs, axis=0).tolist()
+    for x, want in ((np.zeros(6), g['f0']), (g['probe'], g['f_probe'])):
+        f = calib_np.manual_points_residuals(x, case['img_pts'], case['bad_cams'], pairs, case['k'], case['d'], case['r_bad'], case['t_bad'])
+        assert f.shape == want.shape
+        assert np.abs(f - want).max() <= 1e-9 * max(1.0, np.abs(want).max())
+
+
+def test_oracle_ring_critical_is_the_threshold_loop():
+    """The closed form equals what the reference's loop observes: a point is triangulated at threshold t iff crit > t."""
+    import numpy as np
+    from oracle import calib_np
+    rng = np.random.default_rng(0)
+    lik = rng.uniform(size=(200, 6))
+    lik[5, 2] = np.nan
+    crit = calib_np.ring_critical(lik)
+    for t in (0.01, 0.2, 0.5, 0.77):
+        m = lik > t
+        has_pair = (m & np.roll(m, -1, axis=1)).any(axis=1)
+        assert np.array_equal(has_pair, crit > t)
