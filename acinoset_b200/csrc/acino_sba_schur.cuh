@@ -132,6 +132,43 @@ __device__ __forceinline__ void warp_reduce_scatter40(double (&a)[RCS_UNIT], int
   }
 }
 
+// ---- unit lists: for every tile of BT points and every camera pair (unit), the tile-local indices of the points both
+// cameras observe, in point order. They depend on the masks only, so they are built once per solve and K4 streams
+// them in (cp.async) instead of compacting them again in every LM iteration. lists [tile][unit][BT] u16,
+// counts [tile][NUP] u16.
+template <int C>
+__global__ void __launch_bounds__(schur_bt(C))
+schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned short* __restrict__ lists,
+                   unsigned short* __restrict__ counts) {
+  constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (NU + 7) & ~7;
+  __shared__ unsigned char sM[BT];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t tile = blockIdx.x;
+  const int64_t p = tile * BT + tid;
+  sM[tid] = (p < P) ? obs_mask[p] : (unsigned char)0;
+  __syncthreads();
+  for (int u = warp; u < NUP; u += NW) {
+    if (u >= NU) { if (lane == 0) counts[tile * NUP + u] = 0; continue; }
+    int c, cp;
+    if (u < C) { c = u; cp = u; }
+    else {
+      int k = u - C; c = 0;
+      while (k >= C - 1 - c) { k -= C - 1 - c; ++c; }
+      cp = c + 1 + k;
+    }
+    unsigned short* lst = lists + ((size_t)tile * NU + u) * BT;
+    int n = 0;
+    for (int b0 = 0; b0 < BT; b0 += 32) {
+      const unsigned mq = sM[b0 + lane];
+      const bool in = (mq >> c & 1) && (mq >> cp & 1);
+      const unsigned b = __ballot_sync(0xffffffffu, in);
+      if (in) lst[n + __popc(b & ((1u << lane) - 1u))] = (unsigned short)(b0 + lane);
+      n += __popc(b);
+    }
+    if (lane == 0) counts[tile * NUP + u] = (unsigned short)n;
+  }
+}
+
 // ---- K4: residual + Jacobian + per-point blocks + Schur accumulation ------------------------------------
 // Persistent CTAs of BT threads loop over tiles of BT points.
 //   phase 1 (one thread per point): linearise the point's observations, build V, g, invert V + lam D, stage
@@ -149,8 +186,10 @@ struct SchurSmem {
   static constexpr int NW = BT / 32;
   static constexpr int LEN = rcs_len(C);
   static constexpr int BS = BT + 1;       // row stride of the staged arrays (odd: spreads the per-observation writes over banks)
-  static constexpr size_t n_doubles = (size_t)C * CAM_STRIDE + (size_t)C * 8 * BS + 15 * BS + LEN;   // sX is double-buffered
-  static constexpr size_t bytes = n_doubles * 8 + (size_t)NU * BT * 2 + (size_t)C * BT * 2 + NW * 4 + 16 + NU * 2 + BT + 16;
+  static constexpr int NUP = (NU + 7) & ~7;   // unit counts per tile, padded to a multiple of 16 bytes
+  static constexpr size_t n_doubles = ((size_t)C * CAM_STRIDE + (size_t)C * 8 * BS + 15 * BS + LEN + 1) & ~(size_t)1;   // sX is double-buffered; even: the lists start 16-byte aligned
+  static constexpr size_t list_bytes = (size_t)NU * BT * 2;     // one tile's unit lists (global layout = shared layout)
+  static constexpr size_t bytes = n_doubles * 8 + list_bytes + NUP * 2 + (size_t)C * BT * 2 + NW * 4 + 16 + NU * 2 + BT + 16;
 };
 
 template <int C>
@@ -159,9 +198,10 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
                    const double* __restrict__ cams0, const double* __restrict__ cams1,
                    const double* __restrict__ X0, const double* __restrict__ X1,
                    const SchurLm* __restrict__ lm, SchurParams prm,
-                   double* __restrict__ rcs_partial, double* __restrict__ max_partial) {
+                   double* __restrict__ rcs_partial, double* __restrict__ max_partial,
+                   const unsigned short* __restrict__ unit_lists, const unsigned short* __restrict__ unit_counts) {
   using L = SchurSmem<C>;
-  constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN;
+  constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN, NUP = L::NUP;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sc = reinterpret_cast<double*>(smem_raw);
   double* sN = sc + C * CAM_STRIDE;          // [(c*6+k)*BS + q]
@@ -170,8 +210,9 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   double* sVi = sXbuf + 6 * BS;              // [k*BS + q], k<6: 00 01 02 11 12 22
   double* sH = sVi + 6 * BS;                 // [k*BS + q], k<3
   double* sS = sH + 3 * BS;                  // [LEN]
-  unsigned short* list = reinterpret_cast<unsigned short*>(sS + LEN);   // [u*BT + i] points of unit u
-  unsigned short* olist = list + (size_t)NU * BT;                       // [i] observations of the tile: q*8 + c
+  unsigned short* list = reinterpret_cast<unsigned short*>(sc + L::n_doubles);   // [u*BT + i] points of unit u (16-byte aligned)
+  unsigned short* ucnt = list + (size_t)NU * BT;                        // [u] points in unit u of this tile
+  unsigned short* olist = ucnt + NUP;                                   // [i] observations of the tile: q*8 + c
   int* wtot = reinterpret_cast<int*>(olist + (size_t)C * BT);           // [w] observations per warp
   int* next_unit = wtot + NW;                                           // [0] unit counter, [1] observations in the tile
   unsigned char* u_c = reinterpret_cast<unsigned char*>(next_unit + 4); // [u] first camera
@@ -215,6 +256,14 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
     const unsigned m = m_next;
     sM[tid] = (unsigned char)m;
     cp_async_wait_all();
+    {   // this tile's unit lists (precomputed from the masks, schur_lists_kernel): in flight during phase 1
+      const char* src = reinterpret_cast<const char*>(unit_lists) + (size_t)tile * L::list_bytes;
+      char* dst = reinterpret_cast<char*>(list);
+      for (int i = tid; i < (int)(L::list_bytes / 16); i += BT) cp_async16(dst + 16 * i, src + 16 * i);
+      if (tid < NUP / 8) cp_async16(reinterpret_cast<char*>(ucnt) + 16 * tid,
+                                    reinterpret_cast<const char*>(unit_counts) + ((size_t)tile * NUP) * 2 + 16 * tid);
+      cp_async_commit();
+    }
     {
       if (m) {
         double X = sX[tid], Y = sX[BS + tid], Z = sX[2 * BS + tid];
@@ -297,8 +346,10 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
         m_next = obs_mask[pn];
         cp_async8(sXn + tid, Xp + 3 * pn); cp_async8(sXn + BS + tid, Xp + 3 * pn + 1); cp_async8(sXn + 2 * BS + tid, Xp + 3 * pn + 2);
       }
+      cp_async_commit();
       buf ^= 1;
     }
+    cp_async_wait_group1();     // the lists have landed; the next tile's points may still be in flight
     __syncthreads();
     // ---------------- phase 2: warps take units (longest first: diagonal units lead) until none is left
     for (;;) {
@@ -308,18 +359,9 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       if (u >= NU) break;
       const int c = u_c[u], cp = u_cp[u];
       const bool diag = (c == cp);
-      // the unit's point list: tile points observed by both cameras, in point order (built by this warp alone)
-      unsigned short* lst = list + (size_t)u * BT;
-      int n = 0;
-#pragma unroll 1
-      for (int b0 = 0; b0 < BT; b0 += 32) {
-        const unsigned mq = sM[b0 + lane];
-        const bool in = (mq >> c & 1) && (mq >> cp & 1);
-        const unsigned b = __ballot_sync(0xffffffffu, in);
-        if (in) lst[n + __popc(b & ((1u << lane) - 1u))] = (unsigned short)(b0 + lane);
-        n += __popc(b);
-      }
-      __syncwarp();
+      // the unit's point list: tile points observed by both cameras, in point order (precomputed, copied in above)
+      const unsigned short* lst = list + (size_t)u * BT;
+      const int n = ucnt[u];
       if (n == 0) continue;
       double acc[RCS_UNIT];
 #pragma unroll
@@ -902,6 +944,9 @@ struct SchurState {
   double* scal = nullptr;
   SchurLm* lm = nullptr;
   SchurLm* h_lm = nullptr;
+  unsigned short* unit_lists = nullptr;    // [tile][unit][BT]
+  unsigned short* unit_counts = nullptr;   // [tile][NUP]
+  int64_t n_tiles = 0;
   cudaEvent_t prof_ev[4 * PROF_MAX] = {};
 };
 
