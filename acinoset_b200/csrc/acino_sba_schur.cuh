@@ -139,14 +139,35 @@ __device__ __forceinline__ void warp_reduce_scatter40(double (&a)[RCS_UNIT], int
 template <int C>
 __global__ void __launch_bounds__(schur_bt(C))
 schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned short* __restrict__ lists,
-                   unsigned short* __restrict__ counts) {
-  constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (NU + 7) & ~7;
+                   unsigned short* __restrict__ counts, unsigned short* __restrict__ obs_lists) {
+  constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (NU + 7) & ~7, OB = 8 + C * BT;
   __shared__ unsigned char sM[BT];
+  __shared__ int wtot[NW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t tile = blockIdx.x;
   const int64_t p = tile * BT + tid;
-  sM[tid] = (p < P) ? obs_mask[p] : (unsigned char)0;
-  __syncthreads();
+  const unsigned m = (p < P) ? obs_mask[p] : 0u;
+  sM[tid] = (unsigned char)m;
+  {   // the tile's observations, point-major then camera: [0] = count, [8 + i] = q*8 + c
+    int k = __popc(m), incl = k;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) wtot[warp] = incl;
+    __syncthreads();
+    int base = incl - k;
+    for (int w = 0; w < warp; ++w) base += wtot[w];
+    unsigned short* ol = obs_lists + (size_t)tile * OB;
+    unsigned mm = m;
+    while (mm) {
+      int c = __ffs(mm) - 1;
+      mm &= mm - 1;
+      ol[8 + base++] = (unsigned short)(tid * 8 + c);
+    }
+    if (tid == BT - 1) ol[0] = (unsigned short)base;
+  }
   for (int u = warp; u < NUP; u += NW) {
     if (u >= NU) { if (lane == 0) counts[tile * NUP + u] = 0; continue; }
     int c, cp;
@@ -189,7 +210,8 @@ struct SchurSmem {
   static constexpr int NUP = (NU + 7) & ~7;   // unit counts per tile, padded to a multiple of 16 bytes
   static constexpr size_t n_doubles = ((size_t)C * CAM_STRIDE + (size_t)C * 8 * BS + 15 * BS + LEN + 1) & ~(size_t)1;   // sX is double-buffered; even: the lists start 16-byte aligned
   static constexpr size_t list_bytes = (size_t)NU * BT * 2;     // one tile's unit lists (global layout = shared layout)
-  static constexpr size_t bytes = n_doubles * 8 + list_bytes + NUP * 2 + (size_t)C * BT * 2 + NW * 4 + 16 + NU * 2 + BT + 16;
+  static constexpr int OB = 8 + C * BT;       // one tile's observation list in u16: [0] = count, [8..] = entries q*8 + c
+  static constexpr size_t bytes = n_doubles * 8 + list_bytes + NUP * 2 + (size_t)OB * 2 * 2 + 16 + NU * 2 + 16;
 };
 
 template <int C>
@@ -199,9 +221,10 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
                    const double* __restrict__ X0, const double* __restrict__ X1,
                    const SchurLm* __restrict__ lm, SchurParams prm,
                    double* __restrict__ rcs_partial, double* __restrict__ max_partial,
-                   const unsigned short* __restrict__ unit_lists, const unsigned short* __restrict__ unit_counts) {
+                   const unsigned short* __restrict__ unit_lists, const unsigned short* __restrict__ unit_counts,
+                   const unsigned short* __restrict__ obs_lists) {
   using L = SchurSmem<C>;
-  constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN, NUP = L::NUP;
+  constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN, NUP = L::NUP, OB = L::OB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sc = reinterpret_cast<double*>(smem_raw);
   double* sN = sc + C * CAM_STRIDE;          // [(c*6+k)*BS + q]
@@ -212,12 +235,10 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   double* sS = sH + 3 * BS;                  // [LEN]
   unsigned short* list = reinterpret_cast<unsigned short*>(sc + L::n_doubles);   // [u*BT + i] points of unit u (16-byte aligned)
   unsigned short* ucnt = list + (size_t)NU * BT;                        // [u] points in unit u of this tile
-  unsigned short* olist = ucnt + NUP;                                   // [i] observations of the tile: q*8 + c
-  int* wtot = reinterpret_cast<int*>(olist + (size_t)C * BT);           // [w] observations per warp
-  int* next_unit = wtot + NW;                                           // [0] unit counter, [1] observations in the tile
+  unsigned short* olbuf = ucnt + NUP;                                   // two buffers of OB: the tile's observations (q*8 + c), point-major
+  int* next_unit = reinterpret_cast<int*>(olbuf + 2 * OB);              // [0] unit counter
   unsigned char* u_c = reinterpret_cast<unsigned char*>(next_unit + 4); // [u] first camera
   unsigned char* u_cp = u_c + NU;                                       // [u] second camera
-  unsigned char* sM = u_cp + NU;                                        // [q] observation masks of the tile
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
@@ -249,12 +270,14 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       m_next = obs_mask[p0];
       cp_async8(sXbuf + tid, Xp + 3 * p0); cp_async8(sXbuf + BS + tid, Xp + 3 * p0 + 1); cp_async8(sXbuf + 2 * BS + tid, Xp + 3 * p0 + 2);
     }
+    for (int i = tid; i < OB / 8; i += BT)
+      cp_async16(reinterpret_cast<char*>(olbuf) + 16 * i, reinterpret_cast<const char*>(obs_lists) + ((size_t)blockIdx.x * OB) * 2 + 16 * i);
   }
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    // ---------------- phase 1a: stage the points, compact the tile's observations (point-major, camera-minor)
+    // ---------------- phase 1a: the tile's points and observation list were fetched while the previous tile was in phase 2
     double* sX = sXbuf + buf * 3 * BS;
+    const unsigned short* olist = olbuf + buf * OB;
     const unsigned m = m_next;
-    sM[tid] = (unsigned char)m;
     cp_async_wait_all();
     {   // this tile's unit lists (precomputed from the masks, schur_lists_kernel): in flight during phase 1
       const char* src = reinterpret_cast<const char*>(unit_lists) + (size_t)tile * L::list_bytes;
@@ -264,35 +287,16 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
                                     reinterpret_cast<const char*>(unit_counts) + ((size_t)tile * NUP) * 2 + 16 * tid);
       cp_async_commit();
     }
-    {
-      if (m) {
-        double X = sX[tid], Y = sX[BS + tid], Z = sX[2 * BS + tid];
-        xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
-      }
-      int k = __popc(m), incl = k;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-      }
-      if (lane == 31) wtot[warp] = incl;
-      __syncthreads();
-      int base = incl - k;
-      for (int w = 0; w < warp; ++w) base += wtot[w];
-      unsigned mm = m;
-      while (mm) {
-        int c = __ffs(mm) - 1;
-        mm &= mm - 1;
-        olist[base++] = (unsigned short)(tid * 8 + c);
-      }
-      if (tid == BT - 1) next_unit[1] = base;
-      __syncthreads();
+    if (m) {
+      double X = sX[tid], Y = sX[BS + tid], Z = sX[2 * BS + tid];
+      xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
     }
+    __syncthreads();
     // ---------------- phase 1b: one thread per observation: residual, Jacobian rows, robust weights
     {
-      const int n_obs = next_unit[1];
+      const int n_obs = olist[0];
       for (int i = tid; i < n_obs; i += BT) {
-        const int e = olist[i], q = e >> 3, c = e & 7;
+        const int e = olist[8 + i], q = e >> 3, c = e & 7;
         const int64_t pq = tile * BT + q;
         double2 ob = uv[pq * C + c];
         double pm1 = 0.0;
@@ -346,6 +350,10 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
         m_next = obs_mask[pn];
         cp_async8(sXn + tid, Xp + 3 * pn); cp_async8(sXn + BS + tid, Xp + 3 * pn + 1); cp_async8(sXn + 2 * BS + tid, Xp + 3 * pn + 2);
       }
+      if (tile + gridDim.x < n_tiles)
+        for (int i = tid; i < OB / 8; i += BT)
+          cp_async16(reinterpret_cast<char*>(olbuf + (buf ^ 1) * OB) + 16 * i,
+                     reinterpret_cast<const char*>(obs_lists) + ((size_t)(tile + gridDim.x) * OB) * 2 + 16 * i);
       cp_async_commit();
       buf ^= 1;
     }
@@ -946,6 +954,7 @@ struct SchurState {
   SchurLm* h_lm = nullptr;
   unsigned short* unit_lists = nullptr;    // [tile][unit][BT]
   unsigned short* unit_counts = nullptr;   // [tile][NUP]
+  unsigned short* obs_lists = nullptr;     // [tile][8 + C*BT]
   int64_t n_tiles = 0;
   cudaEvent_t prof_ev[4 * PROF_MAX] = {};
 };

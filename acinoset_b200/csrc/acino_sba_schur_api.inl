@@ -90,6 +90,7 @@ static int schur_ensure(acino_sba* h) {
     const size_t nt = tiles < 1 ? 1 : (size_t)tiles, nu = rcs_units(C), nup = (nu + 7) & ~(size_t)7;
     ACINO_CUDA(cudaMalloc(&s.unit_lists, nt * nu * bt * sizeof(unsigned short)));
     ACINO_CUDA(cudaMalloc(&s.unit_counts, nt * nup * sizeof(unsigned short)));
+    ACINO_CUDA(cudaMalloc(&s.obs_lists, nt * (8 + (size_t)C * bt) * sizeof(unsigned short)));
     s.n_tiles = (int64_t)nt;
   }
   ACINO_CUDA(cudaMemsetAsync(s.cams_alt, 0, MAX_CAMS * CAM_STRIDE * sizeof(double), h->stream));
@@ -105,7 +106,7 @@ static int schur_ensure(acino_sba* h) {
 static void schur_free(SchurState& s) {
   cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.max_partial); cudaFree(s.rcs);
   cudaFree(s.mx); cudaFree(s.delta_c); cudaFree(s.scal_partial); cudaFree(s.scal); cudaFree(s.lm);
-  cudaFree(s.unit_lists); cudaFree(s.unit_counts);
+  cudaFree(s.unit_lists); cudaFree(s.unit_counts); cudaFree(s.obs_lists);
   if (s.h_lm) cudaFreeHost(s.h_lm);
   for (cudaEvent_t e : s.prof_ev) if (e) cudaEventDestroy(e);
   s = SchurState();
@@ -132,7 +133,8 @@ static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
   // the camera-pair point lists of every tile follow from the masks alone: (re)built once per solve (the observation
   // mask may be a borrowed device buffer that changed since the last solve; it must not change during one)
   if (h->P > 0) {
-    DISPATCH_C(h->C, (schur_lists_kernel<CC><<<(unsigned)s.n_tiles, schur_bt(CC), 0, h->stream>>>(h->mask, h->P, s.unit_lists, s.unit_counts)));
+    DISPATCH_C(h->C, (schur_lists_kernel<CC><<<(unsigned)s.n_tiles, schur_bt(CC), 0, h->stream>>>(h->mask, h->P, s.unit_lists, s.unit_counts,
+                                                                                                  s.obs_lists)));
     ACINO_CUDA(cudaGetLastError());
   }
   s.inited = true;
@@ -150,7 +152,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n], st));
   DISPATCH_C(C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, st>>>(
                     h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.rcs_partial, s.max_partial, s.unit_lists,
-                    s.unit_counts)));
+                    s.unit_counts, s.obs_lists)));
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 1], st));
   ++s.launches;
@@ -261,7 +263,7 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     const int len = rcs_len(h->C);
     DISPATCH_C(h->C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, h->stream>>>(
                          h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, pf, s.rcs_partial, s.max_partial,
-                         s.unit_lists, s.unit_counts)));
+                         s.unit_lists, s.unit_counts, s.obs_lists)));
     ACINO_CUDA(cudaGetLastError());
     fold_partials_kernel<<<(len + 31) / 32, 256, 0, h->stream>>>(s.rcs_partial, s.grid_build, len, s.rcs, s.max_partial,
                                                                  s.grid_build, 2, 2, 0, s.mx);
