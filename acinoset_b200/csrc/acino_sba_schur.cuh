@@ -139,7 +139,8 @@ __device__ __forceinline__ void warp_reduce_scatter40(double (&a)[RCS_UNIT], int
 template <int C>
 __global__ void __launch_bounds__(schur_bt(C))
 schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned short* __restrict__ lists,
-                   unsigned short* __restrict__ counts, unsigned short* __restrict__ obs_lists) {
+                   unsigned short* __restrict__ counts, unsigned short* __restrict__ obs_lists,
+                   unsigned short* __restrict__ pt_start) {
   constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (NU + 7) & ~7, OB = 8 + C * BT;
   __shared__ unsigned char sM[BT];
   __shared__ int wtot[NW];
@@ -159,6 +160,7 @@ schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned sho
     __syncthreads();
     int base = incl - k;
     for (int w = 0; w < warp; ++w) base += wtot[w];
+    pt_start[(size_t)tile * BT + tid] = (unsigned short)base;
     unsigned short* ol = obs_lists + (size_t)tile * OB;
     unsigned mm = m;
     while (mm) {
@@ -222,7 +224,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
                    const SchurLm* __restrict__ lm, SchurParams prm,
                    double* __restrict__ rcs_partial, double* __restrict__ max_partial,
                    const unsigned short* __restrict__ unit_lists, const unsigned short* __restrict__ unit_counts,
-                   const unsigned short* __restrict__ obs_lists) {
+                   const unsigned short* __restrict__ obs_lists, double* __restrict__ stgN, double* __restrict__ stgP) {
   using L = SchurSmem<C>;
   constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN, NUP = L::NUP, OB = L::OB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -306,6 +308,11 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
         n[3 * BS] = o.n1[0]; n[4 * BS] = o.n1[1]; n[5 * BS] = o.n1[2];
         sE[(size_t)(c * 2) * BS + q] = o.e0;
         sE[(size_t)(c * 2 + 1) * BS + q] = o.e1;
+        {   // the rows stay in HBM for the back-substitution kernel (K6), in the tile's list order: coalesced
+          const size_t gi = (size_t)tile * (C * BT) + i, PC = (size_t)P * C;
+          stgN[gi] = o.n0[0]; stgN[PC + gi] = o.n0[1]; stgN[2 * PC + gi] = o.n0[2];
+          stgN[3 * PC + gi] = o.n1[0]; stgN[4 * PC + gi] = o.n1[1]; stgN[5 * PC + gi] = o.n1[2];
+        }
         if (need_cost) {
           cprod *= 1.0 + pm1;
           if (cprod > 1e200) { cost_acc += prm.half_c2 * log(cprod); cprod = 1.0; }
@@ -339,6 +346,15 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       sH[tid] = fma(iv.i00, g0, fma(iv.i01, g1, iv.i02 * g2));
       sH[BS + tid] = fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
       sH[2 * BS + tid] = fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
+      {   // per-point blocks for K6: V^-1, h, D, g
+        const int64_t pp = tile * BT + tid;
+        const size_t PS = (size_t)P;
+        stgP[pp] = iv.i00; stgP[PS + pp] = iv.i01; stgP[2 * PS + pp] = iv.i02;
+        stgP[3 * PS + pp] = iv.i11; stgP[4 * PS + pp] = iv.i12; stgP[5 * PS + pp] = iv.i22;
+        stgP[6 * PS + pp] = sH[tid]; stgP[7 * PS + pp] = sH[BS + tid]; stgP[8 * PS + pp] = sH[2 * BS + tid];
+        stgP[9 * PS + pp] = iv.D0; stgP[10 * PS + pp] = iv.D1; stgP[11 * PS + pp] = iv.D2;
+        stgP[12 * PS + pp] = g0; stgP[13 * PS + pp] = g1; stgP[14 * PS + pp] = g2;
+      }
       gmax_acc = fmax(gmax_acc, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
     }
     if (tid == 0) next_unit[0] = 0;
@@ -658,154 +674,127 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
 }
 
 // ---- K6: back-substitution + trial evaluation --------------------------------------------------------------
-// Warp-synchronous, no block barrier in the loop: a warp owns 32 consecutive points at a time and cuts them into
-// batches of whole points whose observations fill its 32 lanes (one lane per observation):
-//   re-linearise at the current parameters (N, e) and y = e + N d_c with d_c = w_c x X + tau_c;
-//   segmented shuffle scan over each point's lanes: V = sum N^T N, g + s = sum N^T y;
-//   the segment's last lane solves dX = -(V + lam D)^-1 (g + s), writes the trial point, and hands dX back to the
-//   segment; every lane adds its share of the predicted reduction (-0.5 e^T N dX; the tail adds 0.5 lam dX^T D dX),
-//   projects the trial point with the trial cameras and adds its robust cost 0.5 C^2 log1p((1+z_u)(1+z_v) - 1).
+// Nothing is linearised twice: K4 leaves, per observation, the weighted point-Jacobian rows N (6 doubles, in the tile's
+// observation-list order) and, per point, V^-1 (6), h = V^-1 g (3), the damping diagonal D (3) and the gradient g (3).
+// Persistent CTAs walk the same tiles as K4 with the same precomputed observation lists:
+//   stage A (thread = observation): s_o = N^T (N d_c), d_c = w_c x X + tau_c the camera step seen by the point -> shared;
+//   stage B (thread = point): s = sum of its observations' s_o, dX = -(h + V^-1 s), trial point to HBM and shared,
+//            predicted reduction of the point block 0.5 lam dX^T D dX - 0.5 g^T dX, max |dX|;
+//   stage C (thread = observation): project the trial point with the trial camera, robust cost as a running product.
 // Per-block partials: [trial cost, predicted reduction of the point blocks, max |dX|, 0].
 template <int C>
-__global__ void __launch_bounds__(256)
+struct BacksubSmem {
+  static constexpr int BT = schur_bt(C);
+  static constexpr int OB = 8 + C * BT;
+  // trial cameras, camera steps, s_o [3][C*BT], X [3][BT], dX [3][BT], observation list, point starts, masks
+  static constexpr size_t n_doubles = (size_t)C * CAM_STRIDE + 6 * C + 2 + 3 * (size_t)C * BT + 6 * BT;
+  static constexpr size_t bytes = n_doubles * 8 + (size_t)OB * 2 + BT * 2 + BT + 16;
+};
+
+template <int C>
+__global__ void __launch_bounds__(schur_bt(C), 2)
 schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
                      const double* __restrict__ cams0, const double* __restrict__ cams1,
                      const double* __restrict__ X0, const double* __restrict__ X1, double* __restrict__ Xt0,
                      double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
-                     const double* __restrict__ delta_c, double* __restrict__ scal_partial) {
-  constexpr int NW = 8;
-  __shared__ double sc[C * CAM_STRIDE];
-  __shared__ double st[C * CAM_STRIDE];
-  __shared__ double sd[6 * C];
+                     const double* __restrict__ delta_c, double* __restrict__ scal_partial,
+                     const unsigned short* __restrict__ obs_lists, const unsigned short* __restrict__ pt_start,
+                     const double* __restrict__ stgN, const double* __restrict__ stgP) {
+  using L = BacksubSmem<C>;
+  constexpr int BT = L::BT, OB = L::OB, NW = BT / 32, CB = C * BT;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* st = reinterpret_cast<double*>(smem_raw);       // trial cameras
+  double* sd = st + C * CAM_STRIDE;                        // camera steps (w, tau) per camera
+  double* sS = sd + 6 * C + 2;                             // [k*CB + i], k<3
+  double* sX = sS + 3 * (size_t)CB;                        // [k*BT + q]
+  double* sDX = sX + 3 * BT;                               // [k*BT + q]: trial point X + dX
+  unsigned short* ol = reinterpret_cast<unsigned short*>(sDX + 3 * BT);   // [OB]
+  unsigned short* ps = ol + OB;                            // [q] first observation of point q in the list
+  unsigned char* sM = reinterpret_cast<unsigned char*>(ps + BT);
   __shared__ double red[3][NW];
-  __shared__ unsigned char smap[NW][32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
   const int cur = lm->cur;
   const double lam = lm->lambda;
-  const double* __restrict__ cams = cur ? cams1 : cams0;
   const double* __restrict__ camt = cur ? cams0 : cams1;
   const double* __restrict__ Xp = cur ? X1 : X0;
   double* __restrict__ Xt = cur ? Xt0 : Xt1;
-  for (int i = tid; i < C * CAM_STRIDE; i += blockDim.x) { sc[i] = cams[i]; st[i] = camt[i]; }
+  const size_t PC = (size_t)P * C;
+  for (int i = tid; i < C * CAM_STRIDE; i += BT) st[i] = camt[i];
   if (tid < 6 * C) sd[tid] = delta_c[tid];
-  __syncthreads();
   double f_acc = 0.0, pred_acc = 0.0, dx_acc = 0.0;
-  double prod = 1.0;       // running product of (1+z_u)(1+z_v) over this lane's observations; logged when it grows large
-  const int64_t n_groups = skip ? 0 : (P + 31) / 32;
-  const unsigned FULL = 0xffffffffu;
-  for (int64_t grp = (int64_t)blockIdx.x * NW + warp; grp < n_groups; grp += (int64_t)gridDim.x * NW) {
-    const int64_t p = grp * 32 + lane;
+  double prod = 1.0;       // running product of (1+z_u)(1+z_v) over this thread's observations; logged when it grows large
+  const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t p = tile * BT + tid;
     const unsigned m = (p < P) ? obs_mask[p] : 0u;
-    const int k = __popc(m);
-    double X = 0.0, Y = 0.0, Z = 0.0;
-    if (m) { X = Xp[3 * p]; Y = Xp[3 * p + 1]; Z = Xp[3 * p + 2]; }
-    int s = k;                                  // exclusive prefix of the observation counts
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      int v = __shfl_up_sync(FULL, s, o);
-      if (lane >= o) s += v;
+    {   // the tile's observation list (16-byte chunks), point starts, points
+      const uint4* src = reinterpret_cast<const uint4*>(obs_lists + (size_t)tile * OB);
+      uint4* dst = reinterpret_cast<uint4*>(ol);
+      for (int i = tid; i < OB / 8; i += BT) dst[i] = src[i];
+      ps[tid] = pt_start[(size_t)tile * BT + tid];
+      if (m) { sX[tid] = Xp[3 * p]; sX[BT + tid] = Xp[3 * p + 1]; sX[2 * BT + tid] = Xp[3 * p + 2]; }
     }
-    const int total = __shfl_sync(FULL, s, 31);
-    s -= k;
-    int start = 0;
-    while (start < 32) {
-      // batch = points [start, end): as many whole points as fit in 32 lanes (a point has <= 8 observations)
-      const int base = __shfl_sync(FULL, s, start);
-      const unsigned fit = __ballot_sync(FULL, lane >= start && s + k - base <= 32);
-      const unsigned nofit = ~fit & (FULL << start);
-      const int end = nofit ? (__ffs(nofit) - 1) : 32;
-      const int s_end = (end < 32) ? __shfl_sync(FULL, s, end & 31) : total;
-      const int nb = s_end - base;
-      if (nb > 0) {
-        if (lane >= start && lane < end) {
-          int off = s - base;
-          unsigned mm = m;
-          while (mm) {
-            int c = __ffs(mm) - 1;
-            mm &= mm - 1;
-            smap[warp][off++] = (unsigned char)(lane << 3 | c);
-          }
-        }
-        __syncwarp();
-        const bool valid = lane < nb;
-        const int e = valid ? smap[warp][lane] : (start << 3);
-        const int j = e >> 3, c = e & 7;
-        const double Xj = __shfl_sync(FULL, X, j), Yj = __shfl_sync(FULL, Y, j), Zj = __shfl_sync(FULL, Z, j);
-        const int tail_idx = __shfl_sync(FULL, s, j) - base + __shfl_sync(FULL, k, j) - 1;
-        double v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0, g0 = 0, g1 = 0, g2 = 0;
-        ObsLin o;
-        o.n0[0] = o.n0[1] = o.n0[2] = o.n1[0] = o.n1[1] = o.n1[2] = o.e0 = o.e1 = 0.0;
-        double2 ob = make_double2(0.0, 0.0);
-        if (valid) {
-          ob = uv[(grp * 32 + j) * C + c];
-          double pm1 = 0.0;
-          o = linearise_obs(sc + c * CAM_STRIDE, Xj, Yj, Zj, ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
-          const double* d = sd + 6 * c;
-          const double dx = fma(d[1], Zj, -d[2] * Yj) + d[3];
-          const double dy = fma(d[2], Xj, -d[0] * Zj) + d[4];
-          const double dz = fma(d[0], Yj, -d[1] * Xj) + d[5];
-          const double y0 = o.e0 + fma(o.n0[0], dx, fma(o.n0[1], dy, o.n0[2] * dz));
-          const double y1 = o.e1 + fma(o.n1[0], dx, fma(o.n1[1], dy, o.n1[2] * dz));
-          g0 = fma(o.n0[0], y0, o.n1[0] * y1); g1 = fma(o.n0[1], y0, o.n1[1] * y1); g2 = fma(o.n0[2], y0, o.n1[2] * y1);
-          v00 = fma(o.n0[0], o.n0[0], o.n1[0] * o.n1[0]); v01 = fma(o.n0[0], o.n0[1], o.n1[0] * o.n1[1]);
-          v02 = fma(o.n0[0], o.n0[2], o.n1[0] * o.n1[2]); v11 = fma(o.n0[1], o.n0[1], o.n1[1] * o.n1[1]);
-          v12 = fma(o.n0[1], o.n0[2], o.n1[1] * o.n1[2]); v22 = fma(o.n0[2], o.n0[2], o.n1[2] * o.n1[2]);
-        }
-        // segmented inclusive scan over the point's lanes (segments are <= 8 lanes: offsets 1, 2, 4)
-#pragma unroll
-        for (int off = 1; off <= 4; off <<= 1) {
-          const int jo = __shfl_up_sync(FULL, j, off);
-          const bool same = valid && lane >= off && jo == j;
-          double t;
-          t = __shfl_up_sync(FULL, v00, off); if (same) v00 += t;
-          t = __shfl_up_sync(FULL, v01, off); if (same) v01 += t;
-          t = __shfl_up_sync(FULL, v02, off); if (same) v02 += t;
-          t = __shfl_up_sync(FULL, v11, off); if (same) v11 += t;
-          t = __shfl_up_sync(FULL, v12, off); if (same) v12 += t;
-          t = __shfl_up_sync(FULL, v22, off); if (same) v22 += t;
-          t = __shfl_up_sync(FULL, g0, off); if (same) g0 += t;
-          t = __shfl_up_sync(FULL, g1, off); if (same) g1 += t;
-          t = __shfl_up_sync(FULL, g2, off); if (same) g2 += t;
-        }
-        double d0 = 0.0, d1 = 0.0, d2 = 0.0;
-        if (valid && lane == tail_idx) {
-          Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
-          d0 = -fma(iv.i00, g0, fma(iv.i01, g1, iv.i02 * g2));
-          d1 = -fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
-          d2 = -fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
-          // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta), undamped gradient g;
-          // this is the damping term of the point, the gradient term is added observation by observation below
-          pred_acc += 0.5 * lam * (iv.D0 * d0 * d0 + iv.D1 * d1 * d1 + iv.D2 * d2 * d2);
-          const int64_t pj = grp * 32 + j;
-          Xt[3 * pj] = Xj + d0; Xt[3 * pj + 1] = Yj + d1; Xt[3 * pj + 2] = Zj + d2;
-          dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
-        }
-        d0 = __shfl_sync(FULL, d0, tail_idx & 31);
-        d1 = __shfl_sync(FULL, d1, tail_idx & 31);
-        d2 = __shfl_sync(FULL, d2, tail_idx & 31);
-        if (valid) {
-          const double nd0 = fma(o.n0[0], d0, fma(o.n0[1], d1, o.n0[2] * d2));
-          const double nd1 = fma(o.n1[0], d0, fma(o.n1[1], d1, o.n1[2] * d2));
-          pred_acc -= 0.5 * fma(o.e0, nd0, o.e1 * nd1);
-          double x, y, z, u, v;
-          to_camera(st + c * CAM_STRIDE, Xj + d0, Yj + d1, Zj + d2, x, y, z);
-          fisheye_uv(st + c * CAM_STRIDE, x, y, z, u, v);
-          const double fu = u - ob.x, fv = v - ob.y;
-          prod *= fma(fu * fu, prm.inv_c2, 1.0) * fma(fv * fv, prm.inv_c2, 1.0);
-          if (prod > 1e200) { f_acc += log(prod); prod = 1.0; }      // sum of log1p(z) = log of the product; rare
-        }
-        __syncwarp();
-      }
-      start = end;
+    __syncthreads();
+    const int n_obs = ol[0];
+    // ---- stage A
+    for (int i = tid; i < n_obs; i += BT) {
+      const int e = ol[8 + i], q = e >> 3, c = e & 7;
+      const size_t gi = (size_t)tile * CB + i;
+      const double n0x = stgN[gi], n0y = stgN[PC + gi], n0z = stgN[2 * PC + gi];
+      const double n1x = stgN[3 * PC + gi], n1y = stgN[4 * PC + gi], n1z = stgN[5 * PC + gi];
+      const double X = sX[q], Y = sX[BT + q], Z = sX[2 * BT + q];
+      const double* d = sd + 6 * c;
+      const double dx = fma(d[1], Z, -d[2] * Y) + d[3];
+      const double dy = fma(d[2], X, -d[0] * Z) + d[4];
+      const double dz = fma(d[0], Y, -d[1] * X) + d[5];
+      const double y0 = fma(n0x, dx, fma(n0y, dy, n0z * dz));
+      const double y1 = fma(n1x, dx, fma(n1y, dy, n1z * dz));
+      sS[i] = fma(n0x, y0, n1x * y1);
+      sS[CB + i] = fma(n0y, y0, n1y * y1);
+      sS[2 * CB + i] = fma(n0z, y0, n1z * y1);
     }
+    __syncthreads();
+    // ---- stage B
+    if (m) {
+      const int k = __popc(m), b = ps[tid];
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+      for (int i = 0; i < k; ++i) { s0 += sS[b + i]; s1 += sS[CB + b + i]; s2 += sS[2 * CB + b + i]; }
+      const double i00 = stgP[p], i01 = stgP[(size_t)P + p], i02 = stgP[2 * (size_t)P + p];
+      const double i11 = stgP[3 * (size_t)P + p], i12 = stgP[4 * (size_t)P + p], i22 = stgP[5 * (size_t)P + p];
+      const double h0 = stgP[6 * (size_t)P + p], h1 = stgP[7 * (size_t)P + p], h2 = stgP[8 * (size_t)P + p];
+      const double D0 = stgP[9 * (size_t)P + p], D1 = stgP[10 * (size_t)P + p], D2 = stgP[11 * (size_t)P + p];
+      const double g0 = stgP[12 * (size_t)P + p], g1 = stgP[13 * (size_t)P + p], g2 = stgP[14 * (size_t)P + p];
+      const double d0 = -(h0 + fma(i00, s0, fma(i01, s1, i02 * s2)));
+      const double d1 = -(h1 + fma(i01, s0, fma(i11, s1, i12 * s2)));
+      const double d2 = -(h2 + fma(i02, s0, fma(i12, s1, i22 * s2)));
+      // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta) with the undamped gradient g
+      pred_acc += 0.5 * (lam * (D0 * d0 * d0 + D1 * d1 * d1 + D2 * d2 * d2) - fma(g0, d0, fma(g1, d1, g2 * d2)));
+      const double xt = sX[tid] + d0, yt = sX[BT + tid] + d1, zt = sX[2 * BT + tid] + d2;
+      Xt[3 * p] = xt; Xt[3 * p + 1] = yt; Xt[3 * p + 2] = zt;
+      sDX[tid] = xt; sDX[BT + tid] = yt; sDX[2 * BT + tid] = zt;
+      dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
+    }
+    __syncthreads();
+    // ---- stage C
+    for (int i = tid; i < n_obs; i += BT) {
+      const int e = ol[8 + i], q = e >> 3, c = e & 7;
+      const double2 ob = uv[((size_t)tile * BT + q) * C + c];
+      double x, y, z, u, v;
+      to_camera(st + c * CAM_STRIDE, sDX[q], sDX[BT + q], sDX[2 * BT + q], x, y, z);
+      fisheye_uv(st + c * CAM_STRIDE, x, y, z, u, v);
+      const double fu = u - ob.x, fv = v - ob.y;
+      prod *= fma(fu * fu, prm.inv_c2, 1.0) * fma(fv * fv, prm.inv_c2, 1.0);
+      if (prod > 1e200) { f_acc += log(prod); prod = 1.0; }      // sum of log1p(z) = log of the product; rare
+    }
+    __syncthreads();
   }
   f_acc = prm.half_c2 * (f_acc + log(prod));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    f_acc += __shfl_xor_sync(FULL, f_acc, o);
-    pred_acc += __shfl_xor_sync(FULL, pred_acc, o);
-    dx_acc = fmax(dx_acc, __shfl_xor_sync(FULL, dx_acc, o));
+    f_acc += __shfl_xor_sync(0xffffffffu, f_acc, o);
+    pred_acc += __shfl_xor_sync(0xffffffffu, pred_acc, o);
+    dx_acc = fmax(dx_acc, __shfl_xor_sync(0xffffffffu, dx_acc, o));
   }
   if (lane == 0) { red[0][warp] = f_acc; red[1][warp] = pred_acc; red[2][warp] = dx_acc; }
   __syncthreads();
@@ -955,6 +944,9 @@ struct SchurState {
   unsigned short* unit_lists = nullptr;    // [tile][unit][BT]
   unsigned short* unit_counts = nullptr;   // [tile][NUP]
   unsigned short* obs_lists = nullptr;     // [tile][8 + C*BT]
+  unsigned short* pt_start = nullptr;      // [tile][BT] first observation of each point in its tile's list
+  double* stgN = nullptr;                  // [6][P*C] N rows per observation (tile list order), written by K4 for K6
+  double* stgP = nullptr;                  // [15][P] V^-1, h, D, g per point, written by K4 for K6
   int64_t n_tiles = 0;
   cudaEvent_t prof_ev[4 * PROF_MAX] = {};
 };
