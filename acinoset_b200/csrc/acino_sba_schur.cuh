@@ -710,7 +710,6 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
   double* sDX = sX + 3 * BT;                               // [k*BT + q]: trial point X + dX
   unsigned short* ol = reinterpret_cast<unsigned short*>(sDX + 3 * BT);   // [OB]
   unsigned short* ps = ol + OB;                            // [q] first observation of point q in the list
-  unsigned char* sM = reinterpret_cast<unsigned char*>(ps + BT);
   __shared__ double red[3][NW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
