@@ -508,7 +508,8 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   __shared__ double A[n][n + 1];
   __shared__ double rhs[n], gbar[n], D[n], dl[n];
   __shared__ double smax[2];
-  __shared__ double col[n];
+  __shared__ double col[n + 1];
+  __shared__ double rdiag[n];
   __shared__ double rhs_diag;
   __shared__ int fail;
   const int tid = threadIdx.x;
@@ -574,10 +575,13 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   const double lam = lm->lambda;
   if (tid < n) A[tid][tid] = fma(lam, D[tid], A[tid][tid]);
   __syncthreads();
-  // Cholesky (lower): one matrix element per thread, in a register; per column one sqrt by the diagonal's owner, one
-  // scaling by the column's owners and a rank-1 update by everybody else: two barriers per column, no serial loop
+  // Cholesky (lower) of the matrix bordered by the right-hand side: one element per thread, in a register. Row n holds
+  // b = -rhs, and the updates that turn the rows above into L turn it into y = L^-1 b, so the forward substitution
+  // comes with the factorisation. Per column: the diagonal's owner takes one reciprocal square root (MUFU + Newton, no
+  // division anywhere), the column's owners scale, everybody else applies the rank-1 update: two barriers per column.
   {
-    constexpr int NE = n * (n + 1) / 2;
+    constexpr int NA = n + 1;
+    constexpr int NE = NA * (NA + 1) / 2 - 1;          // without the corner (n, n)
     constexpr int EPT = (NE + 1023) / 1024;
     double a[EPT];
     int ei[EPT], ej[EPT];
@@ -588,7 +592,7 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
       while ((ii + 1) * (ii + 2) / 2 <= e) ++ii;       // row of packed lower-triangular index e
       ei[t] = e < NE ? ii : -1;
       ej[t] = e - ii * (ii + 1) / 2;
-      a[t] = e < NE ? A[ii][ej[t]] : 0.0;
+      a[t] = e < NE ? (ii < n ? A[ii][ej[t]] : -rhs[ej[t]]) : 0.0;
     }
     for (int k = 0; k < n; ++k) {
 #pragma unroll
@@ -596,44 +600,42 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
         if (ei[t] == k && ej[t] == k) {
           double d = a[t];
           if (!(d > 0.0)) { fail = 1; d = 1.0; }
-          a[t] = sqrt(d);
-          rhs_diag = a[t];
+          const double r = rsqrt_nr(d);
+          a[t] = d * r;
+          rhs_diag = r;
+          rdiag[k] = r;
         }
       __syncthreads();
 #pragma unroll
       for (int t = 0; t < EPT; ++t)
-        if (ej[t] == k && ei[t] > k) { a[t] /= rhs_diag; col[ei[t]] = a[t]; }
+        if (ej[t] == k && ei[t] > k) { a[t] *= rhs_diag; col[ei[t]] = a[t]; }
       __syncthreads();
 #pragma unroll
       for (int t = 0; t < EPT; ++t)
         if (ej[t] > k && ei[t] >= 0) a[t] = fma(-col[ei[t]], col[ej[t]], a[t]);
     }
 #pragma unroll
-    for (int t = 0; t < EPT; ++t)
-      if (ei[t] >= 0) A[ei[t]][ej[t]] = a[t];
+    for (int t = 0; t < EPT; ++t) {
+      if (ei[t] >= 0 && ei[t] < n) A[ei[t]][ej[t]] = a[t];
+      if (ei[t] == n) dl[ej[t]] = a[t];                // y
+    }
   }
   __syncthreads();
-  // the two triangular solves by one warp (dot products over lanes, shuffle reduction)
+  // L^T d = y by one warp, column oriented: every lane keeps up to two entries of y in registers; step i broadcasts
+  // d_i = y_i / L_ii (one shuffle, one multiply) and every lane j < i subtracts L_ij d_i from its entries
   if (tid < 32) {
     const int lane = tid;
-    // L y = -rhs
-    for (int i = 0; i < n; ++i) {
-      double part = 0.0;
-      for (int j2 = lane; j2 < i; j2 += 32) part = fma(A[i][j2], dl[j2], part);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-      if (lane == 0) dl[i] = (-rhs[i] - part) / A[i][i];
-      __syncwarp();
-    }
-    // L^T d = y
+    static_assert(n <= 64, "two entries per lane");
+    double ylo = lane < n ? dl[lane] : 0.0, yhi = lane + 32 < n ? dl[lane + 32] : 0.0;
+    __syncwarp();
     for (int i = n - 1; i >= 0; --i) {
-      double part = 0.0;
-      for (int j2 = i + 1 + lane; j2 < n; j2 += 32) part = fma(A[j2][i], dl[j2], part);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-      if (lane == 0) dl[i] = (dl[i] - part) / A[i][i];
-      __syncwarp();
+      const double mine = (i >= 32) ? yhi : ylo;
+      const double di = __shfl_sync(0xffffffffu, mine, i & 31) * rdiag[i];
+      if (lane < i) ylo = fma(-A[i][lane], di, ylo);
+      if (lane + 32 < i) yhi = fma(-A[i][lane + 32], di, yhi);
+      if (lane == 0) dl[i] = di;
     }
+    __syncwarp();
     double pc = 0.0;
     int bad = 0;
     for (int i = lane; i < n; i += 32) {
