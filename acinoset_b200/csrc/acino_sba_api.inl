@@ -252,6 +252,7 @@ int acino_sba_set_observations(acino_sba_t* h, const double* uv, const uint8_t* 
   h->uv = h->uv_own;
   h->mask = h->mask_own;
   h->have_obs = true;
+  h->schur.inited = false;      // the per-tile lists and the compacted observations are rebuilt by the next solve / iterate
   return ACINO_OK;
 }
 
@@ -261,6 +262,7 @@ int acino_sba_set_observations_dev(acino_sba_t* h, const double* uv_dev, const u
   h->uv = (const double2*)uv_dev;
   h->mask = obs_mask_dev;
   h->have_obs = true;
+  h->schur.inited = false;
   return ACINO_OK;
 }
 

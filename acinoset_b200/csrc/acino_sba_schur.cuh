@@ -140,15 +140,19 @@ template <int C>
 __global__ void __launch_bounds__(schur_bt(C))
 schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned short* __restrict__ lists,
                    unsigned short* __restrict__ counts, unsigned short* __restrict__ obs_lists,
-                   unsigned short* __restrict__ pt_start) {
+                   unsigned short* __restrict__ pt_start, unsigned short* __restrict__ pt_rank,
+                   const double2* __restrict__ uv, double2* __restrict__ uvc) {
   constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (NU + 7) & ~7, OB = 8 + C * BT;
   __shared__ unsigned char sM[BT];
   __shared__ int wtot[NW];
+  __shared__ int wpts[NW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t tile = blockIdx.x;
   const int64_t p = tile * BT + tid;
   const unsigned m = (p < P) ? obs_mask[p] : 0u;
   sM[tid] = (unsigned char)m;
+  const unsigned live = __ballot_sync(0xffffffffu, m != 0);
+  if (lane == 0) wpts[warp] = __popc(live);
   {   // the tile's observations, point-major then camera: [0] = count, [8 + i] = q*8 + c
     int k = __popc(m), incl = k;
 #pragma unroll
@@ -161,11 +165,17 @@ schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned sho
     int base = incl - k;
     for (int w = 0; w < warp; ++w) base += wtot[w];
     pt_start[(size_t)tile * BT + tid] = (unsigned short)base;
+    {   // rank of the point among the tile's existing points: where K4 leaves its per-point record for K6
+      int rk = __popc(live & ((1u << lane) - 1u));
+      for (int w = 0; w < warp; ++w) rk += wpts[w];
+      pt_rank[(size_t)tile * BT + tid] = (unsigned short)rk;
+    }
     unsigned short* ol = obs_lists + (size_t)tile * OB;
     unsigned mm = m;
     while (mm) {
       int c = __ffs(mm) - 1;
       mm &= mm - 1;
+      uvc[(size_t)tile * (C * BT) + base] = uv[(size_t)p * C + c];     // observations compacted in list order
       ol[8 + base++] = (unsigned short)(tid * 8 + c);
     }
     if (tid == BT - 1) ol[0] = (unsigned short)base;
@@ -224,7 +234,8 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
                    const SchurLm* __restrict__ lm, SchurParams prm,
                    double* __restrict__ rcs_partial, double* __restrict__ max_partial,
                    const unsigned short* __restrict__ unit_lists, const unsigned short* __restrict__ unit_counts,
-                   const unsigned short* __restrict__ obs_lists, double* __restrict__ stgN, double* __restrict__ stgP) {
+                   const unsigned short* __restrict__ obs_lists, double* __restrict__ stgN, double* __restrict__ stgP,
+                   const unsigned short* __restrict__ pt_rank, const double2* __restrict__ uvc) {
   using L = SchurSmem<C>;
   constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN, NUP = L::NUP, OB = L::OB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -280,6 +291,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
     double* sX = sXbuf + buf * 3 * BS;
     const unsigned short* olist = olbuf + buf * OB;
     const unsigned m = m_next;
+    const int rank = pt_rank[tile * BT + tid];       // used in phase 1c: the load has the whole of 1a/1b to land
     cp_async_wait_all();
     {   // this tile's unit lists (precomputed from the masks, schur_lists_kernel): in flight during phase 1
       const char* src = reinterpret_cast<const char*>(unit_lists) + (size_t)tile * L::list_bytes;
@@ -299,8 +311,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       const int n_obs = olist[0];
       for (int i = tid; i < n_obs; i += BT) {
         const int e = olist[8 + i], q = e >> 3, c = e & 7;
-        const int64_t pq = tile * BT + q;
-        double2 ob = uv[pq * C + c];
+        const double2 ob = uvc[(size_t)tile * (C * BT) + i];
         double pm1 = 0.0;
         ObsLin o = linearise_obs(sc + c * CAM_STRIDE, sX[q], sX[BS + q], sX[2 * BS + q], ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
         double* n = sN + (size_t)(c * 6) * BS + q;
@@ -347,7 +358,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       sH[BS + tid] = fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
       sH[2 * BS + tid] = fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
       {   // per-point blocks for K6: V^-1, h, D, g
-        const int64_t pp = tile * BT + tid;
+        const int64_t pp = tile * BT + rank;          // dense over the tile's existing points: full sectors
         const size_t PS = (size_t)P;
         stgP[pp] = iv.i00; stgP[PS + pp] = iv.i01; stgP[2 * PS + pp] = iv.i02;
         stgP[3 * PS + pp] = iv.i11; stgP[4 * PS + pp] = iv.i12; stgP[5 * PS + pp] = iv.i22;
@@ -701,7 +712,8 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
                      double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
                      const double* __restrict__ delta_c, double* __restrict__ scal_partial,
                      const unsigned short* __restrict__ obs_lists, const unsigned short* __restrict__ pt_start,
-                     const double* __restrict__ stgN, const double* __restrict__ stgP) {
+                     const double* __restrict__ stgN, const double* __restrict__ stgP,
+                     const unsigned short* __restrict__ pt_rank, const double2* __restrict__ uvc) {
   using L = BacksubSmem<C>;
   constexpr int BT = L::BT, OB = L::OB, NW = BT / 32, CB = C * BT;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -729,6 +741,7 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int64_t p = tile * BT + tid;
     const unsigned m = (p < P) ? obs_mask[p] : 0u;
+    const int64_t pr = tile * BT + pt_rank[tile * BT + tid];     // the point's record among the tile's existing points
     {   // the tile's observation list (16-byte chunks), point starts, points
       const uint4* src = reinterpret_cast<const uint4*>(obs_lists + (size_t)tile * OB);
       uint4* dst = reinterpret_cast<uint4*>(ol);
@@ -761,11 +774,12 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
       const int k = __popc(m), b = ps[tid];
       double s0 = 0.0, s1 = 0.0, s2 = 0.0;
       for (int i = 0; i < k; ++i) { s0 += sS[b + i]; s1 += sS[CB + b + i]; s2 += sS[2 * CB + b + i]; }
-      const double i00 = stgP[p], i01 = stgP[(size_t)P + p], i02 = stgP[2 * (size_t)P + p];
-      const double i11 = stgP[3 * (size_t)P + p], i12 = stgP[4 * (size_t)P + p], i22 = stgP[5 * (size_t)P + p];
-      const double h0 = stgP[6 * (size_t)P + p], h1 = stgP[7 * (size_t)P + p], h2 = stgP[8 * (size_t)P + p];
-      const double D0 = stgP[9 * (size_t)P + p], D1 = stgP[10 * (size_t)P + p], D2 = stgP[11 * (size_t)P + p];
-      const double g0 = stgP[12 * (size_t)P + p], g1 = stgP[13 * (size_t)P + p], g2 = stgP[14 * (size_t)P + p];
+      const size_t PS = (size_t)P;
+      const double i00 = stgP[pr], i01 = stgP[PS + pr], i02 = stgP[2 * PS + pr];
+      const double i11 = stgP[3 * PS + pr], i12 = stgP[4 * PS + pr], i22 = stgP[5 * PS + pr];
+      const double h0 = stgP[6 * PS + pr], h1 = stgP[7 * PS + pr], h2 = stgP[8 * PS + pr];
+      const double D0 = stgP[9 * PS + pr], D1 = stgP[10 * PS + pr], D2 = stgP[11 * PS + pr];
+      const double g0 = stgP[12 * PS + pr], g1 = stgP[13 * PS + pr], g2 = stgP[14 * PS + pr];
       const double d0 = -(h0 + fma(i00, s0, fma(i01, s1, i02 * s2)));
       const double d1 = -(h1 + fma(i01, s0, fma(i11, s1, i12 * s2)));
       const double d2 = -(h2 + fma(i02, s0, fma(i12, s1, i22 * s2)));
@@ -780,7 +794,7 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
     // ---- stage C
     for (int i = tid; i < n_obs; i += BT) {
       const int e = ol[8 + i], q = e >> 3, c = e & 7;
-      const double2 ob = uv[((size_t)tile * BT + q) * C + c];
+      const double2 ob = uvc[(size_t)tile * CB + i];
       double x, y, z, u, v;
       to_camera(st + c * CAM_STRIDE, sDX[q], sDX[BT + q], sDX[2 * BT + q], x, y, z);
       fisheye_uv(st + c * CAM_STRIDE, x, y, z, u, v);
@@ -946,6 +960,8 @@ struct SchurState {
   unsigned short* unit_counts = nullptr;   // [tile][NUP]
   unsigned short* obs_lists = nullptr;     // [tile][8 + C*BT]
   unsigned short* pt_start = nullptr;      // [tile][BT] first observation of each point in its tile's list
+  unsigned short* pt_rank = nullptr;       // [tile][BT] rank of each point among the existing points of its tile
+  double2* uvc = nullptr;                  // [tile][C*BT] observations compacted in list order (built once per solve)
   double* stgN = nullptr;                  // [6][P*C] N rows per observation (tile list order), written by K4 for K6
   double* stgP = nullptr;                  // [15][P] V^-1, h, D, g per point, written by K4 for K6
   int64_t n_tiles = 0;

@@ -93,6 +93,8 @@ static int schur_ensure(acino_sba* h) {
     ACINO_CUDA(cudaMalloc(&s.unit_counts, nt * nup * sizeof(unsigned short)));
     ACINO_CUDA(cudaMalloc(&s.obs_lists, nt * (8 + (size_t)C * bt) * sizeof(unsigned short)));
     ACINO_CUDA(cudaMalloc(&s.pt_start, nt * bt * sizeof(unsigned short)));
+    ACINO_CUDA(cudaMalloc(&s.pt_rank, nt * bt * sizeof(unsigned short)));
+    ACINO_CUDA(cudaMalloc(&s.uvc, nt * (size_t)C * bt * sizeof(double2)));
     // rows staged by K4 for K6 (6 doubles per slot, 15 per point): 1 GB per 119,490 frames at C = 6
     ACINO_CUDA(cudaMalloc(&s.stgN, 6 * nt * (size_t)C * bt * sizeof(double)));
     ACINO_CUDA(cudaMalloc(&s.stgP, 15 * nt * (size_t)bt * sizeof(double)));
@@ -111,7 +113,7 @@ static int schur_ensure(acino_sba* h) {
 static void schur_free(SchurState& s) {
   cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.max_partial); cudaFree(s.rcs);
   cudaFree(s.mx); cudaFree(s.delta_c); cudaFree(s.scal_partial); cudaFree(s.scal); cudaFree(s.lm);
-  cudaFree(s.unit_lists); cudaFree(s.unit_counts); cudaFree(s.obs_lists); cudaFree(s.pt_start); cudaFree(s.stgN); cudaFree(s.stgP);
+  cudaFree(s.unit_lists); cudaFree(s.unit_counts); cudaFree(s.obs_lists); cudaFree(s.pt_start); cudaFree(s.pt_rank); cudaFree(s.uvc); cudaFree(s.stgN); cudaFree(s.stgP);
   if (s.h_lm) cudaFreeHost(s.h_lm);
   for (cudaEvent_t e : s.prof_ev) if (e) cudaEventDestroy(e);
   s = SchurState();
@@ -139,7 +141,7 @@ static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
   // mask may be a borrowed device buffer that changed since the last solve; it must not change during one)
   if (h->P > 0) {
     DISPATCH_C(h->C, (schur_lists_kernel<CC><<<(unsigned)s.n_tiles, schur_bt(CC), 0, h->stream>>>(h->mask, h->P, s.unit_lists, s.unit_counts,
-                                                                                                  s.obs_lists, s.pt_start)));
+                                                                                                  s.obs_lists, s.pt_start, s.pt_rank, h->uv, s.uvc)));
     ACINO_CUDA(cudaGetLastError());
   }
   s.inited = true;
@@ -157,7 +159,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n], st));
   DISPATCH_C(C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, st>>>(
                     h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.rcs_partial, s.max_partial, s.unit_lists,
-                    s.unit_counts, s.obs_lists, s.stgN, s.stgP)));
+                    s.unit_counts, s.obs_lists, s.stgN, s.stgP, s.pt_rank, s.uvc)));
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 1], st));
   ++s.launches;
@@ -179,7 +181,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 2], st));
   DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, schur_bt(CC), BacksubSmem<CC>::bytes, st>>>(
                     h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, h->X, s.X_alt, s.lm, prm, s.delta_c, s.scal_partial,
-                    s.obs_lists, s.pt_start, s.stgN, s.stgP)));
+                    s.obs_lists, s.pt_start, s.stgN, s.stgP, s.pt_rank, s.uvc)));
   ACINO_CUDA(cudaGetLastError());
   if (prof) { ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 3], st)); ++s.prof_n; }
   ++s.launches;
@@ -268,7 +270,7 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     const int len = rcs_len(h->C);
     DISPATCH_C(h->C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, h->stream>>>(
                          h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, pf, s.rcs_partial, s.max_partial,
-                         s.unit_lists, s.unit_counts, s.obs_lists, s.stgN, s.stgP)));
+                         s.unit_lists, s.unit_counts, s.obs_lists, s.stgN, s.stgP, s.pt_rank, s.uvc)));
     ACINO_CUDA(cudaGetLastError());
     fold_partials_kernel<<<(len + 31) / 32, 256, 0, h->stream>>>(s.rcs_partial, s.grid_build, len, s.rcs, s.max_partial,
                                                                  s.grid_build, 2, 2, 0, s.mx);
