@@ -305,7 +305,7 @@ def cpu_baseline(frames, mode, full_obs):
     from oracle import ref_port
     t0 = time.perf_counter()
     if mode == 'extrinsics':
-        frames = max(2, min(frames, 10))
+        frames = max(2, min(frames, 40))      # ~10 s of host work at 25 function evaluations
         sc = make_shard(frames, seed=4)
         rng = np.random.default_rng(100)
         from acinoset_b200 import synth
