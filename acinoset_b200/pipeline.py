@@ -40,6 +40,28 @@ def dlc_arrays_to_dense(per_camera):
     return np.ascontiguousarray(a[..., :2]).reshape(F * K, C, 2), np.ascontiguousarray(a[..., 2]).reshape(F * K, C)
 
 
+def load_dlc_points_dense(dlc_df_fpaths, markers, start_frame, end_frame, frame_shifts=None):
+    """DeepLabCut .h5 files -> dense slots for the window [start_frame, end_frame] without the long table of
+    load_dlc_points_as_df (src/lib/utils.py:77-151) in between: uv (F*K, C, 2), lik (F*K, C) with point
+    (frame - start_frame) * K + markers.index(marker); frames or markers a file does not hold get likelihood -1."""
+    from . import utils
+    tables = utils.load_dlc_tables(dlc_df_fpaths, frame_shifts)
+    F, K, C = int(end_frame) - int(start_frame) + 1, len(markers), len(tables)
+    uv = np.zeros((F * K, C, 2))
+    lik = np.full((F * K, C), -1.0)
+    for c, (frames, parts, vals) in enumerate(tables):
+        keep = (frames >= start_frame) & (frames <= end_frame)
+        fi = (frames[keep] - int(start_frame)).astype(np.int64)
+        col = {bp: j for j, bp in enumerate(parts)}
+        for k, m in enumerate(markers):
+            if m in col:
+                v = vals[keep, col[m], :]
+                uv[fi * K + k, c, 0] = v[:, 0]
+                uv[fi * K + k, c, 1] = v[:, 1]
+                lik[fi * K + k, c] = v[:, 2]
+    return uv, lik
+
+
 def tri(uv, lik, n_markers, dlc_thresh, camera_params):
     """core.tri on dense arrays: positions (F, K, 3), NaN where no ring pair saw the marker."""
     k_arr, d_arr, r_arr, t_arr = camera_params[:4]

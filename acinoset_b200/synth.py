@@ -117,6 +117,21 @@ def make_manual_points_case(n_points=14, seed=0, noise_px=0.3, bad_cams=(3, 4, 5
                 bad_cams=list(bad_cams), gt=X)
 
 
+def make_dlc_tables(n_frames, markers, n_cams, seed=0, first_frame=0, nan_frac=0.05):
+    """DeepLabCut-style wide tables (what pd.read_hdf returns for a DLC .h5): index = frame number, columns
+    (scorer, bodyparts, coords); a few likelihood / coordinate cells are NaN."""
+    import pandas as pd
+    out = []
+    for c in range(n_cams):
+        rng = np.random.default_rng(seed * 100 + c)
+        cols = pd.MultiIndex.from_product([['DLC_resnet50'], markers, ['x', 'y', 'likelihood']], names=['scorer', 'bodyparts', 'coords'])
+        a = rng.uniform(0, 1, (n_frames, len(markers) * 3))
+        a[:, 0::3] *= 2704; a[:, 1::3] *= 1520
+        a[rng.uniform(size=a.shape) < nan_frac] = np.nan
+        out.append(pd.DataFrame(a, columns=cols, index=range(first_frame, first_frame + n_frames)))
+    return out
+
+
 def dense_to_df(uv, lik, n_kpts, first_frame=0, markers=None):
     """Dense slots -> DataFrame[frame, camera, marker, x, y, likelihood], rows camera-major then
     frame then marker, like load_dlc_points_as_df (src/lib/utils.py:139-147)."""

@@ -181,3 +181,76 @@ def save_3d_cheetah_as_2d(position3d_arr, out_dir, scene_fpath, bodyparts, proje
         print('Saved', os.path.splitext(fpath)[0] + '.csv')
     print()
     return result_dfs
+
+
+# ========== DeepLabCut tables (src/lib/utils.py:77-151) ==========
+
+def _read_dlc_table(path, dlc_head=False):
+    """One DeepLabCut .h5 -> (frames (F,), bodyparts in alphabetical order, values (F, K, 3) = x, y, likelihood).
+    Mirrors the per-file part of load_dlc_points_as_df: tables without a likelihood column get 1 where x is present and 0
+    elsewhere and their index (image file names) becomes int(name[-7:-4]); the 'dlc_head' tables of the reference's head
+    dataset are renamed the same way (utils.py:84-103)."""
+    df = pd.read_hdf(path)                    # needs PyTables, like the reference
+    if dlc_head:
+        df = df.rename(columns={'bodypart1': 'r_eye', 'bodypart2': 'l_eye', 'bodypart3': 'nose'}, level=1)
+        df = df.drop(columns=['objectA'], level=1)
+    parts = list(dict.fromkeys(df.columns.get_level_values(1)))
+    coords = set(df.columns.get_level_values(2))
+    scorer = df.columns.get_level_values(0)[0]
+    frames = np.asarray(df.index)
+    has_lik = 'likelihood' in coords and not dlc_head
+    if not has_lik:
+        frames = np.array([int(str(s_)[-7:-4]) for s_ in frames])
+    parts_sorted = sorted(parts)
+    vals = np.empty((len(df), len(parts_sorted), 3))
+    for j, bp in enumerate(parts_sorted):
+        vals[:, j, 0] = df[(scorer, bp, 'x')].to_numpy(dtype=np.float64)
+        vals[:, j, 1] = df[(scorer, bp, 'y')].to_numpy(dtype=np.float64)
+        if has_lik:
+            vals[:, j, 2] = df[(scorer, bp, 'likelihood')].to_numpy(dtype=np.float64)
+        else:
+            vals[:, j, 2] = (~np.isnan(vals[:, j, 0])).astype(np.float64)
+    return frames, parts_sorted, vals
+
+
+def _shift_frames(vals, shift):
+    """The reference's frame-drift correction (utils.py:125-137): the rows of a camera move down by `shift` frames; vacated
+    frames keep their labels with x, y = NaN; the caller's fillna(0) makes their likelihood 0."""
+    if shift == 0:
+        return vals
+    out = np.full_like(vals, np.nan)
+    if shift > 0:
+        out[shift:] = vals[:len(vals) - shift]
+    else:
+        out[:shift] = vals[-shift:]
+    return out
+
+
+def load_dlc_tables(dlc_df_fpaths, frame_shifts=None):
+    """Per camera (frames, bodyparts, values (F, K, 3)) with the frame shifts applied and NaN likelihoods set to 0."""
+    assert frame_shifts is None or len(dlc_df_fpaths) == len(frame_shifts), '`frame_shifts` should be the same size with `dlc_df_fpaths`'
+    out = []
+    for i, path in enumerate(dlc_df_fpaths):
+        frames, parts, vals = _read_dlc_table(path, dlc_head='dlc_head' in dlc_df_fpaths[0])
+        if frame_shifts is not None:
+            vals = _shift_frames(vals, int(frame_shifts[i]))
+        vals[:, :, 2] = np.nan_to_num(vals[:, :, 2], nan=0.0)
+        out.append((frames, parts, vals))
+    return out
+
+
+def load_dlc_points_as_df(dlc_df_fpaths, frame_shifts=None, verbose=False):
+    """src/lib/utils.py:77-151: the DeepLabCut .h5 files of all cameras as one long table
+    [frame, camera, marker, x, y, likelihood], rows camera-major, then frame, then marker (alphabetical, as the
+    reference's unstack leaves them). Built from arrays instead of five pandas reshapes per file. Columns are numeric
+    (the reference's come out as `object` under pandas >= 2 because it concatenates onto an empty frame)."""
+    dfs = []
+    for i, (frames, parts, vals) in enumerate(load_dlc_tables(dlc_df_fpaths, frame_shifts)):
+        F, K = len(frames), len(parts)
+        dfs.append(pd.DataFrame({'frame': np.repeat(frames, K), 'camera': i, 'marker': np.tile(np.array(parts, dtype=object), F),
+                                 'x': vals[:, :, 0].ravel(), 'y': vals[:, :, 1].ravel(), 'likelihood': vals[:, :, 2].ravel()}))
+    dlc_df = pd.concat(dfs, ignore_index=True) if dfs else pd.DataFrame(columns=['frame', 'camera', 'marker', 'x', 'y', 'likelihood'])
+    dlc_df = dlc_df[['frame', 'camera', 'marker', 'x', 'y', 'likelihood']]
+    if verbose:
+        print(f'DLC points dataframe:\n{dlc_df}\n')
+    return dlc_df

@@ -78,8 +78,40 @@ def gen_init_marker():
     np.savez_compressed(os.path.join(GOLD, 'golden_init_marker.npz'), versions=_versions(), **out)
 
 
+
+
+def gen_dlc_load():
+    """N1: the reference's load_dlc_points_as_df (/root/reference/src/lib/utils.py:77-151) on synthetic DeepLabCut tables.
+    PyTables is not in the image, so pd.read_hdf is pointed at in-memory tables for the duration of the call (harness
+    shim); the reshaping, frame shifts and fills are the reference's own code."""
+    import pandas as pd
+    calib, utils, sba = ref_shim.load()
+    from acinoset_b200 import synth
+    markers = ['nose', 'r_eye', 'l_eye', 'neck_base', 'spine', 'tail_base']
+    tabs = synth.make_dlc_tables(12, markers, 4, seed=7, first_frame=3)
+    paths = [f'/data/cam{i + 1}DLC.h5' for i in range(4)]
+    store = dict(zip(paths, tabs))
+    real = pd.read_hdf
+    pd.read_hdf = lambda p, *a, **k: store[p].copy()
+    out = {}
+    try:
+        for name, shifts in (('noshift', None), ('shift', [0, 2, -1, 0])):
+            with ref_shim.quiet():
+                df = utils.load_dlc_points_as_df(paths, frame_shifts=shifts)
+            out[f'{name}_frame'] = df['frame'].to_numpy().astype(np.int64)
+            out[f'{name}_camera'] = df['camera'].to_numpy().astype(np.int64)
+            out[f'{name}_marker'] = df['marker'].to_numpy().astype(str)
+            for col in ('x', 'y', 'likelihood'):
+                out[f'{name}_{col}'] = df[col].to_numpy().astype(np.float64)
+    finally:
+        pd.read_hdf = real
+    np.savez_compressed(os.path.join(GOLD, 'golden_dlc_load.npz'), versions=_versions(), **out)
+    print('dlc load:', len(out['noshift_frame']), 'rows')
+
+
 if __name__ == '__main__':
     if not ref_shim.available():
         raise SystemExit('reference tree not present; fixtures can only be generated in the build container')
     gen_adjust()
     gen_init_marker()
+    gen_dlc_load()
