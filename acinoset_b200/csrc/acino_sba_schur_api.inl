@@ -59,9 +59,17 @@ static void comm_destroy(acino_sba* h) {
 }
 
 // ---- state ---------------------------------------------------------------------------------------------------
+static void schur_free(SchurState& s);
+static int schur_alloc(acino_sba* h);
 static int schur_ensure(acino_sba* h) {
+  if (h->schur.ready) return ACINO_OK;
+  const int rc = schur_alloc(h);
+  if (rc) schur_free(h->schur);       // a failed allocation leaves nothing half-built behind
+  return rc;
+}
+
+static int schur_alloc(acino_sba* h) {
   SchurState& s = h->schur;
-  if (s.ready) return ACINO_OK;
   int dev = 0, sms = 148;
   ACINO_CUDA(cudaGetDevice(&dev));
   ACINO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
