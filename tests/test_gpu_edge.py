@@ -167,3 +167,36 @@ def test_full_size_schur_properties():
         outs.append((s.get_points(), s.get_cameras()))
         s.close()
     assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+
+
+def test_full_size_round_trip_and_gauge_invariance():
+    """Size-independent properties at the BASELINE size: project -> triangulate returns the point (encode/decode round
+    trip), residuals vanish at the truth, and the cost is invariant under a rigid motion of the whole scene (the 7-DoF
+    gauge of SURVEY.md F7, the reason parity in points+extrinsics mode is asserted on residuals, not coordinates)."""
+    F = 119490
+    sc = synth.make_rig_scene(F, 20, seed=11, noise_px=0.0)
+    k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
+    P, C = sc['lik'].shape
+    xyz, ex, mask = dense.triangulate_ring(sc['uv'], sc['lik'], 0.5, k, d, r, t)
+    seen = ex.astype(bool)
+    assert np.abs(xyz[seen] - sc['gt'][seen]).max() < 1e-8          # noise-free pixels: DLT is exact up to conditioning
+    s = dense.SbaSolver(C, P)
+    s.set_cameras(k, d, r, t); s.set_observations(sc['uv'], mask); s.set_points(np.where(seen[:, None], sc['gt'], 0.0))
+    sel = ((mask[:, None] >> np.arange(C)) & 1).astype(bool)
+    f = s.residuals()
+    assert np.abs(f[sel]).max() < 1e-8                                # K1 at the truth
+    # rigid motion: X' = Q X + c, R' = R Q^T, t' = t - R Q^T c  ->  identical pixels
+    rng = np.random.default_rng(3)
+    Q = synth._rot_from_axis_angle(rng.normal(0, 0.4, 3)); c = rng.normal(0, 2.0, 3)
+    noisy = synth.make_rig_scene(F, 20, seed=4)
+    xyz2, ex2, mask2 = dense.triangulate_ring(noisy['uv'], noisy['lik'], 0.5, k, d, r, t)
+    X = np.nan_to_num(xyz2)
+    s.set_observations(noisy['uv'], mask2); s.set_points(X)
+    f_a = s.residuals()
+    r_q = np.array([r[i] @ Q.T for i in range(C)])
+    t_q = np.array([t[i].reshape(3) - r_q[i] @ c for i in range(C)]).reshape(C, 3, 1)
+    s.set_cameras(k, d, r_q, t_q); s.set_points(X @ Q.T + c)
+    f_b = s.residuals()
+    sel2 = ((mask2[:, None] >> np.arange(C)) & 1).astype(bool)
+    assert np.abs(f_a[sel2] - f_b[sel2]).max() < 1e-7                 # pixels: rounding of coordinates ~10 m apart
+    s.close()
