@@ -96,16 +96,21 @@ def initialize_marker_3d(pts_2d_df, marker, k_arr, d_arr, r_arr, t_arr, dlc_thre
     return EOM_curve_fit(pts_3d, frames=frames, **kwargs)
 
 
-def install(lib_calib=None, lib_utils=None, lib_sba=None):
+def install(lib_calib=None, lib_utils=None, lib_sba=None, lib_app=None, lib_metric=None):
     """Drop-in integration: rebinds the hot functions of already-imported reference modules
-    (lib.calib, lib.utils, lib.sba) to this package's CUDA-backed ones; reference files are not edited."""
-    from . import calib, utils, sba
+    (lib.calib, lib.utils, lib.sba, lib.app, lib.metric) to this package's CUDA-backed ones; reference files are not
+    edited. lib.app binds `_sba_points` / `_sba_board_points` by name at import (src/lib/app.py:14), so pass it too when
+    it is already imported. Callables the reference took with `from lib.calib import ...` before this call keep working:
+    they are only used as selector tokens (their `__name__` is checked), never called."""
+    from . import calib, utils, sba, metric
     if lib_calib is not None:
         lib_calib.project_points_fisheye = calib.project_points_fisheye
         lib_calib.triangulate_points_fisheye = calib.triangulate_points_fisheye
         lib_calib.adjust_extrinsics_manual_points = calib.adjust_extrinsics_manual_points
     if lib_utils is not None:
         lib_utils.get_pairwise_3d_points_from_df = utils.get_pairwise_3d_points_from_df
+        lib_utils.save_3d_cheetah_as_2d = utils.save_3d_cheetah_as_2d
+        lib_utils.load_dlc_points_as_df = utils.load_dlc_points_as_df
     if lib_sba is not None:
         for name in ('cost_func_points_only', 'cost_func_points_extrinsics', 'params_to_points_extrinsics',
                      'bundle_adjust_points_only', 'bundle_adjust_points_and_extrinsics', 'bundle_adjust_board_points_only',
@@ -113,3 +118,11 @@ def install(lib_calib=None, lib_utils=None, lib_sba=None):
                      '_sba_board_points', '_sba_points'):
             setattr(lib_sba, name, getattr(sba, name))
         lib_sba.get_pairwise_3d_points_from_df = utils.get_pairwise_3d_points_from_df
+    if lib_app is not None:
+        lib_app._sba_points = sba._sba_points
+        lib_app._sba_board_points = sba._sba_board_points
+        lib_app.project_points_fisheye = calib.project_points_fisheye
+        lib_app.triangulate_points_fisheye = calib.triangulate_points_fisheye
+        lib_app.initialize_marker_3d = initialize_marker_3d
+    if lib_metric is not None:
+        lib_metric.residual_error = metric.residual_error

@@ -110,3 +110,36 @@ def test_rotation_matrix_to_rvec_matches_opencv():
         R = cv2.Rodrigues(v)[0]
         assert np.abs(sba.rotation_matrix_to_rvec(R) - cv2.Rodrigues(R)[0].ravel()).max() < 1e-9
     assert np.abs(sba.rotation_matrix_to_rvec(np.eye(3))).max() == 0.0
+
+
+def test_install_rebinds_only_names_the_reference_defines():
+    """INTEGRATION.md drop-in: every attribute app.install() sets exists in the reference module it patches (checked
+    against the reference sources when the tree is present, i.e. in the build container)."""
+    import ast
+    import os
+    import types
+    import pytest
+    ref = '/root/reference/src/lib'
+    if not os.path.isdir(ref):
+        pytest.skip('reference tree not present')
+    import acinoset_b200.app as fast
+    mods = {n: types.ModuleType(n) for n in ('calib', 'utils', 'sba', 'app', 'metric')}
+    fast.install(mods['calib'], mods['utils'], mods['sba'], mods['app'], mods['metric'])
+    def names_of(mod_name, follow_star=True):
+        tree = ast.parse(open(os.path.join(ref, mod_name + '.py')).read())
+        defined = set()
+        for node in tree.body:
+            if isinstance(node, ast.FunctionDef):
+                defined.add(node.name)
+            elif isinstance(node, ast.ImportFrom):
+                for a in node.names:
+                    if a.name == '*' and follow_star and node.level == 1:       # `from .utils import *` (src/lib/sba.py:6)
+                        defined |= names_of(node.module, follow_star=False)
+                    else:
+                        defined.add(a.asname or a.name)
+        return defined
+
+    for name, m in mods.items():
+        defined = names_of(name)
+        patched = {k for k in vars(m) if not k.startswith('__')}
+        assert patched and patched <= defined, (name, patched - defined)
