@@ -403,7 +403,12 @@ def main():
             roofline['traffic'] = ncu['kernels'][kern_name]['dram_bytes']
             roofline['traffic_source'] = 'ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r01_ncu_counts.json)'
             roofline['fp64'] = fp64_block(kern_name, kern_ms)
-            roofline['backsub_kernel']['traffic'] = ncu['kernels'][f'schur_backsub_kernel<{C}>']['dram_bytes']
+            roofline['traffic_gbs'] = roofline['traffic'] / (kern_ms * 1e-3) / 1e9
+            roofline['traffic_frac_of_hbm_peak'] = roofline['traffic_gbs'] / peak
+            bk = roofline['backsub_kernel']
+            bk['traffic'] = ncu['kernels'][f'schur_backsub_kernel<{C}>']['dram_bytes']
+            bk['traffic_gbs'] = bk['traffic'] / (ctx['kern']['backsub_ms'] * 1e-3) / 1e9
+            bk['traffic_frac_of_hbm_peak'] = bk['traffic_gbs'] / peak       # K6 is the HBM-bound kernel of the path
             roofline['backsub_kernel']['fp64'] = fp64_block(f'schur_backsub_kernel<{C}>', ctx['kern']['backsub_ms'])
     except (OSError, KeyError, ValueError):
         pass
