@@ -225,7 +225,7 @@ def prepare_manual_points_for_bundle_adjustment(img_pts_arr, k_arr, d_arr, r_arr
         raise NotImplementedError('only triangulate_points_fisheye is supported (CUDA path, no fallback)')
     pts = np.asarray(img_pts_arr, dtype=np.float64)
     n_pts, n_cam = pts.shape[0], pts.shape[1]
-    points_2d, point_3d_indices, camera_indices, points_3d = [], [], [], []
+    points_2d, point_3d_indices, camera_indices, first_two = [], [], [], []
     idx = 0
     for i in range(n_pts):
         cams = [c for c in range(n_cam) if not np.isnan(pts[i, c]).any()]
@@ -233,11 +233,16 @@ def prepare_manual_points_for_bundle_adjustment(img_pts_arr, k_arr, d_arr, r_arr
             continue
         for c in cams:
             points_2d.append(pts[i, c]); camera_indices.append(c); point_3d_indices.append(idx)
-        a, b = cams[0], cams[1]
-        points_3d.append(triangulate_func(pts[i, a], pts[i, b], k_arr[a], d_arr[a], r_arr[a], t_arr[a],
-                                          k_arr[b], d_arr[b], r_arr[b], t_arr[b])[0])
+        first_two.append((i, cams[0], cams[1]))
         idx += 1
-    return (np.array(points_2d, dtype=np.float32).reshape(-1, 2), np.array(points_3d, dtype=np.float32).reshape(-1, 3),
+    # one CUDA launch per distinct camera pair instead of one per point
+    points_3d = np.empty((idx, 3))
+    for a, b in sorted({(a, b) for _, a, b in first_two}):
+        sel = [j for j, (_, a_, b_) in enumerate(first_two) if (a_, b_) == (a, b)]
+        src = [first_two[j][0] for j in sel]
+        points_3d[sel] = triangulate_func(pts[src, a], pts[src, b], k_arr[a], d_arr[a], r_arr[a], t_arr[a],
+                                          k_arr[b], d_arr[b], r_arr[b], t_arr[b])
+    return (np.array(points_2d, dtype=np.float32).reshape(-1, 2), points_3d.astype(np.float32).reshape(-1, 3),
             np.array(point_3d_indices, dtype=int), np.array(camera_indices, dtype=int))
 
 
