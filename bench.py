@@ -349,9 +349,12 @@ def main():
         cb['value'] = v
         line = dict(impl='reference', metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=len(vals), warmup=0,
                     ms_per_step=1e3 / v, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f64',
-                    data='synthetic', config=dict(workload=f'C4 {"points+extrinsics (Schur)" if mode == "extrinsics" else "points-only"} SBA: '
+                    data='synthetic', config=dict(workload=f'{"C4" if args.frames == C4_FRAMES else "custom"} {"points+extrinsics (Schur)" if mode == "extrinsics" else "points-only"} SBA: '
                                                            f'{args.frames} frames x 20 keypoints x 6 cameras per GPU, dlc_thresh 0.5, 1 px noise',
-                                                  mode=mode, note='reference CPU algorithm, single-threaded as in the reference'),
+                                                  masked_frac=args.masked_frac, outlier_frac=args.outlier_frac, mode=mode,
+                                                  parallelism=f'frame-shard x{args.gpus}',
+                                                  note='reference CPU algorithm on rank 0, single-threaded as in the reference (its per-observation '
+                                                       'Python/OpenCV loop has no parallel section); bounded sample scaled to the workload'),
                     cpu_baseline=cb, e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
         print(json.dumps(line))
         return
