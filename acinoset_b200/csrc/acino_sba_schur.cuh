@@ -135,14 +135,14 @@ __device__ __forceinline__ void warp_reduce_scatter40(double (&a)[RCS_UNIT], int
 // ---- unit lists: for every tile of BT points and every camera pair (unit), the tile-local indices of the points both
 // cameras observe, in point order. They depend on the masks only, so they are built once per solve and K4 streams
 // them in (cp.async) instead of compacting them again in every LM iteration. lists [tile][unit][BT] u16,
-// counts [tile][NUP] u16.
+// counts [tile][NUP] u16: [0, NU) the list lengths, [NU, 2 NU) the units sorted by length (longest first).
 template <int C>
 __global__ void __launch_bounds__(schur_bt(C))
 schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned short* __restrict__ lists,
                    unsigned short* __restrict__ counts, unsigned short* __restrict__ obs_lists,
                    unsigned short* __restrict__ pt_start, unsigned short* __restrict__ pt_rank,
                    const double2* __restrict__ uv, double2* __restrict__ uvc) {
-  constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (NU + 7) & ~7, OB = 8 + C * BT;
+  constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (2 * NU + 7) & ~7, OB = 8 + C * BT;
   __shared__ unsigned char sM[BT];
   __shared__ int wtot[NW];
   __shared__ int wpts[NW];
@@ -180,8 +180,8 @@ schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned sho
     }
     if (tid == BT - 1) ol[0] = (unsigned short)base;
   }
-  for (int u = warp; u < NUP; u += NW) {
-    if (u >= NU) { if (lane == 0) counts[tile * NUP + u] = 0; continue; }
+  __shared__ unsigned short scnt[NU];
+  for (int u = warp; u < NU; u += NW) {
     int c, cp;
     if (u < C) { c = u; cp = u; }
     else {
@@ -198,7 +198,18 @@ schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned sho
       if (in) lst[n + __popc(b & ((1u << lane) - 1u))] = (unsigned short)(b0 + lane);
       n += __popc(b);
     }
-    if (lane == 0) counts[tile * NUP + u] = (unsigned short)n;
+    if (lane == 0) { counts[tile * NUP + u] = (unsigned short)n; scnt[u] = (unsigned short)n; }
+  }
+  __syncthreads();
+  if (tid == 0) {   // claim order of phase 2: longest list first (ties: lower unit first), so the tail of the tile is short work
+    unsigned short ord[NU];
+    for (int u = 0; u < NU; ++u) {
+      int k = u;
+      while (k > 0 && scnt[ord[k - 1]] < scnt[u]) { ord[k] = ord[k - 1]; --k; }
+      ord[k] = (unsigned short)u;
+    }
+    for (int u = 0; u < NU; ++u) counts[tile * NUP + NU + u] = ord[u];
+    for (int u = 2 * NU; u < NUP; ++u) counts[tile * NUP + u] = 0;
   }
 }
 
@@ -219,7 +230,7 @@ struct SchurSmem {
   static constexpr int NW = BT / 32;
   static constexpr int LEN = rcs_len(C);
   static constexpr int BS = BT + 1;       // row stride of the staged arrays (odd: spreads the per-observation writes over banks)
-  static constexpr int NUP = (NU + 7) & ~7;   // unit counts per tile, padded to a multiple of 16 bytes
+  static constexpr int NUP = (2 * NU + 7) & ~7;   // unit counts + claim order per tile, padded to a multiple of 16 bytes
   static constexpr size_t n_doubles = ((size_t)C * CAM_STRIDE + (size_t)C * 8 * BS + 15 * BS + LEN + 1) & ~(size_t)1;   // sX is double-buffered; even: the lists start 16-byte aligned
   static constexpr size_t list_bytes = (size_t)NU * BT * 2;     // one tile's unit lists (global layout = shared layout)
   static constexpr int OB = 8 + C * BT;       // one tile's observation list in u16: [0] = count, [8..] = entries q*8 + c
@@ -392,6 +403,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       if (lane == 0) u = atomicAdd(next_unit, 1);
       u = __shfl_sync(0xffffffffu, u, 0);
       if (u >= NU) break;
+      u = ucnt[NU + u];            // claim order precomputed per tile: longest list first
       const int c = u_c[u], cp = u_cp[u];
       const bool diag = (c == cp);
       // the unit's point list: tile points observed by both cameras, in point order (precomputed, copied in above)

@@ -96,7 +96,7 @@ static int schur_alloc(acino_sba* h) {
   ACINO_CUDA(cudaMalloc(&s.lm, sizeof(SchurLm)));
   ACINO_CUDA(cudaMallocHost(&s.h_lm, sizeof(SchurLm)));
   {
-    const size_t nt = tiles < 1 ? 1 : (size_t)tiles, nu = rcs_units(C), nup = (nu + 7) & ~(size_t)7;
+    const size_t nt = tiles < 1 ? 1 : (size_t)tiles, nu = rcs_units(C), nup = (2 * nu + 7) & ~(size_t)7;
     ACINO_CUDA(cudaMalloc(&s.unit_lists, nt * nu * bt * sizeof(unsigned short)));
     ACINO_CUDA(cudaMalloc(&s.unit_counts, nt * nup * sizeof(unsigned short)));
     ACINO_CUDA(cudaMalloc(&s.obs_lists, nt * (8 + (size_t)C * bt) * sizeof(unsigned short)));
