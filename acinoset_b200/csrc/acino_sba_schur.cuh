@@ -750,7 +750,9 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
   double f_acc = 0.0, pred_acc = 0.0, dx_acc = 0.0;
   double prod = 1.0;       // running product of (1+z_u)(1+z_v) over this thread's observations; logged when it grows large
   const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  // tiles in the reverse of K4's order: the rows K4 staged last are still in the 126 MB L2
+  for (int64_t tile_r = blockIdx.x; tile_r < n_tiles; tile_r += gridDim.x) {
+    const int64_t tile = n_tiles - 1 - tile_r;
     const int64_t p = tile * BT + tid;
     const unsigned m = (p < P) ? obs_mask[p] : 0u;
     const int64_t pr = tile * BT + pt_rank[tile * BT + tid];     // the point's record among the tile's existing points
