@@ -9,6 +9,7 @@
 #include "acino_sba_points.cuh"
 #include "acino_sba_schur.cuh"
 #include "acino_calib.cuh"
+#include "acino_ekf.cuh"
 
 namespace acino {
 static thread_local char g_err[512] = "";
@@ -270,6 +271,34 @@ int acino_ring_critical(const double* lik, int64_t P, int n_cams, double* crit) 
   ring_critical_kernel<<<grid_for(P, 256), 256>>>(dL.as<double>(), P, n_cams, dO.as<double>());
   ACINO_CUDA(cudaGetLastError());
   ACINO_CUDA(cudaMemcpy(crit, dO.p, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
+// ---------------------------------------------------------------- N4: EKF measurement and its numerical Jacobian
+int acino_ekf_measurement(const double* x, int n_pose, int mode, const double* cams24, int n_cams, double eps, int n_states,
+                          double* h, double* H, double* coords) {
+  ARG_CHECK(x && cams24 && h && H, "ekf_measurement null pointer");
+  ARG_CHECK(mode >= 0 && mode <= 3, "ekf_measurement: marker mode must be 0 (default), 1 (head), 2 (upper_body) or 3 (head_stabilize)");
+  ARG_CHECK(n_pose == ekf_n_pose(mode), "ekf_measurement: pose vector length does not match the marker mode");
+  ARG_CHECK(n_cams > 0 && n_cams <= 32 && n_states >= n_pose && eps != 0.0, "ekf_measurement sizes");
+  const int n_mk = ekf_n_markers(mode), R = n_cams * n_mk * 2, B = 1 + n_pose;
+  DevBuf dX, dC, dP, dh, dH, dM;
+  ACINO_CUDA(dX.alloc(n_pose * sizeof(double)));
+  ACINO_CUDA(dC.alloc((size_t)n_cams * CAM_STRIDE * sizeof(double)));
+  ACINO_CUDA(dP.alloc((size_t)B * R * sizeof(double)));
+  ACINO_CUDA(dh.alloc((size_t)R * sizeof(double)));
+  ACINO_CUDA(dH.alloc((size_t)R * n_states * sizeof(double)));
+  ACINO_CUDA(dM.alloc((size_t)n_mk * 3 * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(dX.p, x, n_pose * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dC.p, cams24, (size_t)n_cams * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  ekf_project_kernel<<<B, 128, n_cams * CAM_STRIDE * sizeof(double)>>>(dX.as<double>(), mode, dC.as<double>(), n_cams, eps,
+                                                                      dP.as<double2>(), dM.as<double>());
+  ACINO_CUDA(cudaGetLastError());
+  ekf_jacobian_kernel<<<(R * n_states + 255) / 256, 256>>>(dP.as<double>(), R, n_pose, n_states, eps, dh.as<double>(), dH.as<double>());
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaMemcpy(h, dh.p, (size_t)R * sizeof(double), cudaMemcpyDeviceToHost));
+  ACINO_CUDA(cudaMemcpy(H, dH.p, (size_t)R * n_states * sizeof(double), cudaMemcpyDeviceToHost));
+  if (coords) ACINO_CUDA(cudaMemcpy(coords, dM.p, (size_t)n_mk * 3 * sizeof(double), cudaMemcpyDeviceToHost));
   return ACINO_OK;
 }
 

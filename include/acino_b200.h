@@ -70,6 +70,15 @@ int acino_manual_residuals(const double* img_pts, int n_points, const double* ca
  * (-inf when no pair exists; NaN likelihoods never pass). lik double[P][n_cams]. Host pointers. */
 int acino_ring_critical(const double* lik, int64_t P, int n_cams, double* crit);
 
+/* N4 — the measurement of the EKF update, src/core/ekf.py:66-96,245-251: the skeleton's markers for the pose x
+ * (get_3d_marker_coords, src/lib/misc.py:144-327; mode 0 default / 1 head / 2 upper_body / 3 head_stabilize,
+ * n_pose = 29 / 6 / 11 / 11) projected into every camera, h double[n_cams*n_markers*2] in the reference's order
+ * [camera][marker][x,y], and the forward-difference Jacobian of numerical_jacobian (eps as given, 1e-3 in the
+ * reference) H double[n_cams*n_markers*2][n_states], columns >= n_pose zero. coords (optional) receives the
+ * markers' 3-D positions double[n_markers][3]. Host pointers. */
+int acino_ekf_measurement(const double* x, int n_pose, int mode, const double* cams24, int n_cams, double eps, int n_states,
+                          double* h, double* H, double* coords);
+
 /* cv::Rodrigues(rvec)->R for n vectors (src/lib/sba.py:29), the device routine the extrinsics solver uses. */
 int acino_rodrigues(const double* rvecs, int n, double* R_out);
 

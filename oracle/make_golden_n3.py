@@ -109,9 +109,68 @@ def gen_dlc_load():
     print('dlc load:', len(out['noshift_frame']), 'rows')
 
 
+def _cut_nested(path, outer, names):
+    """Source text of the functions `names` nested inside the top-level function `outer`, dedented."""
+    import textwrap
+    src = open(path).read()
+    lines = src.splitlines()
+    out = []
+    for node in ast.parse(src).body:
+        if isinstance(node, ast.FunctionDef) and node.name == outer:
+            for sub in node.body:
+                if isinstance(sub, ast.FunctionDef) and sub.name in names:
+                    out.append(textwrap.dedent('\n'.join(lines[sub.lineno - 1:sub.end_lineno])))
+    assert len(out) == len(names)
+    return '\n\n'.join(out)
+
+
+def ekf_pose(mode, seed):
+    """A plausible pose for marker mode `mode`: head inside the rig's view volume, moderate joint angles."""
+    from acinoset_b200 import ekf as fast
+    rng = np.random.default_rng(seed)
+    x = rng.uniform(-0.4, 0.4, fast.N_POSE[mode])
+    x[0:3] = [2.0 + rng.uniform(-1, 1), 6.5 + rng.uniform(-0.5, 0.5), 0.6]
+    if mode != 'head':
+        x[6] = -0.28                         # neck length l_1
+    if mode == 'default':
+        x[26:29] = [3.0, 7.0, 0.1]           # lure
+    return x
+
+
+def gen_ekf():
+    """N4: h_function and numerical_jacobian of the reference's EKF (/root/reference/src/core/ekf.py:66-96) — nested
+    functions of ekf(), so their source text is cut out and executed unmodified with the reference's lib.misc and
+    lib.calib — assembled per camera exactly as the loop at :245-251 does, for float64 poses. (Inside the reference's
+    loop the pose is float32 because predict_next_state casts it, so its own H carries ~1e-4 relative noise; a float32
+    run is stored too, for the record.)"""
+    calib, utils, sba = ref_shim.load()
+    from lib import misc
+    from acinoset_b200 import synth, ekf as fast
+    rig = synth.load_rig(os.path.join(GOLD, 'scene_6cam.json'))
+    k, d, r, t, _ = rig
+    text = _cut_nested(os.path.join(ref_shim.REF_SRC, 'core', 'ekf.py'), 'ekf', ['h_function', 'numerical_jacobian'])
+    out = {}
+    for mode in ('default', 'head', 'upper_body', 'head_stabilize'):
+        ns = dict(np=np, misc=misc, project_points_fisheye=calib.project_points_fisheye, marker_mode=mode)
+        exec(compile(text, 'reference:core/ekf.py', 'exec'), ns)
+        x = ekf_pose(mode, seed=5)
+        n_mk = len(misc.get_markers(mode=mode))
+        for tag, xx in (('f64', x), ('f32', x.astype(np.float32))):
+            h = np.zeros(6 * n_mk * 2); H = np.zeros((6 * n_mk * 2, 3 * len(x)))
+            for j in range(6):
+                h[j * n_mk * 2:(j + 1) * n_mk * 2] = ns['h_function'](xx, k[j], d[j], r[j], t[j]).flatten()
+                H[j * n_mk * 2:(j + 1) * n_mk * 2, 0:len(x)] = ns['numerical_jacobian'](ns['h_function'], xx, k[j], d[j], r[j], t[j])
+            out[f'{mode}_{tag}_h'] = h; out[f'{mode}_{tag}_H'] = H
+        out[f'{mode}_x'] = x
+        out[f'{mode}_coords'] = np.array(misc.get_3d_marker_coords({'x': x}, mode=mode), dtype=np.float64)
+    np.savez_compressed(os.path.join(GOLD, 'golden_ekf.npz'), versions=_versions(), **out)
+    print('ekf:', {m: out[f'{m}_f64_H'].shape for m in ('default', 'head', 'upper_body', 'head_stabilize')})
+
+
 if __name__ == '__main__':
     if not ref_shim.available():
         raise SystemExit('reference tree not present; fixtures can only be generated in the build container')
     gen_adjust()
     gen_init_marker()
     gen_dlc_load()
+    gen_ekf()

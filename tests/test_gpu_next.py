@@ -180,3 +180,29 @@ def test_initialize_marker_3d_vs_reference_golden(golden_dir, capsys):
         assert fit.shape == (60, 3) and fit_deriv.shape == (60, 3)
         assert np.abs(fit - g[f'{marker}_fit']).max() < 1e-6
         assert np.abs(fit_deriv - g[f'{marker}_fit_deriv']).max() < 1e-6
+
+
+def test_ekf_measurement_vs_reference_golden(golden_dir):
+    """N4: EKF measurement h and numerical Jacobian H (src/core/ekf.py:66-96,245-251) for all cameras and perturbed poses
+    in two launches, against the reference's own functions (golden) and the numpy oracle; all four marker modes."""
+    from acinoset_b200 import ekf
+    from oracle import ekf_np
+    g = np.load(os.path.join(golden_dir, 'golden_ekf.npz'))
+    k, d, r, t, _ = synth.load_rig(os.path.join(golden_dir, 'scene_6cam.json'))
+    for mode in ('default', 'head', 'upper_body', 'head_stabilize'):
+        x = g[f'{mode}_x']
+        h, H, coords = ekf.measurement(x, k, d, r, t, mode, with_coords=True)
+        assert H.shape == g[f'{mode}_f64_H'].shape and h.shape == g[f'{mode}_f64_h'].shape
+        assert np.abs(coords - g[f'{mode}_coords']).max() < 1e-13
+        assert np.abs(h - g[f'{mode}_f64_h']).max() < 1e-8
+        assert np.abs(H - g[f'{mode}_f64_H']).max() < 1e-6
+        assert not H[:, len(x):].any()                                 # velocity / acceleration columns stay zero
+        ho, Ho = ekf_np.measurement(x, k, d, r, t, mode)
+        assert np.abs(H - Ho).max() < 1e-6 and np.abs(h - ho).max() < 1e-9
+        # single-camera helpers of the reference's interface
+        assert np.allclose(ekf.h_function(x, k[2], d[2], r[2], t[2], mode).ravel(), h.reshape(6, -1)[2], rtol=0, atol=1e-9)
+        assert np.array_equal(ekf.get_3d_marker_coords({'x': x}, mode), coords)
+    with pytest.raises(ValueError):
+        ekf.measurement(np.zeros(5), k, d, r, t, 'head')
+    with pytest.raises(ValueError):
+        ekf.measurement(np.zeros(6), k, d, r, t, 'tail')

@@ -159,3 +159,22 @@ def test_oracle_ring_critical_is_the_threshold_loop():
         m = lik > t
         has_pair = (m & np.roll(m, -1, axis=1)).any(axis=1)
         assert np.array_equal(has_pair, crit > t)
+
+
+def test_oracle_ekf_measurement_vs_reference_golden(golden_dir):
+    """N4 oracle pin: skeleton forward kinematics, per-camera pixels and forward-difference Jacobian against the reference's
+    own get_3d_marker_coords / h_function / numerical_jacobian (float64 poses)."""
+    import os
+    import numpy as np
+    from oracle import ekf_np
+    from acinoset_b200 import synth
+    g = np.load(os.path.join(golden_dir, 'golden_ekf.npz'))
+    k, d, r, t, _ = synth.load_rig(os.path.join(golden_dir, 'scene_6cam.json'))
+    for mode in ('default', 'head', 'upper_body', 'head_stabilize'):
+        x = g[f'{mode}_x']
+        assert np.abs(ekf_np.marker_coords(x, mode) - g[f'{mode}_coords']).max() < 1e-13
+        h, H = ekf_np.measurement(x, k, d, r, t, mode)
+        assert np.abs(h - g[f'{mode}_f64_h']).max() < 1e-8
+        assert np.abs(H - g[f'{mode}_f64_H']).max() < 1e-6          # differences of ~1e3 px numbers divided by 1e-3
+        # the reference's in-loop float32 pose gives the same Jacobian up to its own rounding noise
+        assert np.abs(H - g[f'{mode}_f32_H']).max() < 2.0
