@@ -50,6 +50,7 @@ manual_residuals_kernel(const double2* __restrict__ img_pts, int N, const double
         out[18 + r] = cam[18 + r] - (cam[9 + 3 * r] * p[3] + cam[9 + 3 * r + 1] * p[4] + cam[9 + 3 * r + 2] * p[5]);
       }
     }
+    out[21] = 1.0 / cam[0]; out[22] = 1.0 / cam[1];      // for undistort_fisheye
   }
   __syncthreads();
   const int total = B * n_pairs * N;

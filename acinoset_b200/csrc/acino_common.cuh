@@ -85,6 +85,29 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_group1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// ---- tan on [0, pi/2): sine and cosine kernels on [0, pi/4] (the fdlibm minimax coefficients, 1 ulp each), the
+// complement pi/2 - x above pi/4, one reciprocal; 4.4e-16 relative. No argument reduction, no slow path.
+__device__ __forceinline__ double tan_first_quadrant(double x) {
+  const bool big = x > 0.78539816339744831;
+  const double t = big ? (1.5707963267948966 - x) + 6.123233995736766e-17 : x;
+  const double z = t * t;
+  double ps = 1.58969099521155010221e-10;
+  ps = fma(ps, z, -2.50507602534068634195e-08);
+  ps = fma(ps, z, 2.75573137070700676789e-06);
+  ps = fma(ps, z, -1.98412698298579493134e-04);
+  ps = fma(ps, z, 8.33333333332248946124e-03);
+  ps = fma(ps, z, -1.66666666666666324348e-01);
+  const double sn = fma(t * z, ps, t);
+  double pc = -1.13596475577881948265e-11;
+  pc = fma(pc, z, 2.08757232129817482790e-09);
+  pc = fma(pc, z, -2.75573143513906633035e-07);
+  pc = fma(pc, z, 2.48015872894767294178e-05);
+  pc = fma(pc, z, -1.38888888888741095749e-03);
+  pc = fma(pc, z, 4.16666666666666019037e-02);
+  const double cs = fma(z * z, pc, fma(-0.5, z, 1.0));
+  return big ? cs * rcp_nr(sn) : sn * rcp_nr(cs);
+}
+
 // ---- camera in shared memory ----------------------------------------------------------------
 // c points at 24 doubles: fx fy cx cy alpha k1 k2 k3 k4 R[9] t[3] pad[3]
 __device__ __forceinline__ void to_camera(const double* __restrict__ c, double X, double Y, double Z,

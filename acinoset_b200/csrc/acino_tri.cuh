@@ -6,14 +6,22 @@
 
 namespace acino {
 
+// camera value i of a staged cam24 block: the reserved slots 21, 22 receive 1/fx, 1/fy for undistort_fisheye
+__device__ __forceinline__ double stage_cam(const double* __restrict__ cams, int i) {
+  const int k = i % CAM_STRIDE;
+  return k == 21 ? 1.0 / cams[i - 21] : (k == 22 ? 1.0 / cams[i - 21] : cams[i]);
+}
+
 // cv::fisheye::undistortPoints(pt, K, D) with R=I, P=I, criteria (COUNT+EPS, 10, 1e-8):
 // pw=((u-cx)/fx,(v-cy)/fy); theta_d=|pw| clamped to pi/2; Newton on theta; scale=tan(theta)/theta_d;
 // non-converged or sign-flipped -> (-1e6,-1e6).
 __device__ __forceinline__ void undistort_fisheye(const double* __restrict__ c, double u, double v,
                                                   double& nx, double& ny) {
-  double pw0 = (u - c[2]) / c[0];
-  double pw1 = (v - c[3]) / c[1];
-  double thd = sqrt(fma(pw0, pw0, pw1 * pw1));
+  // c[21], c[22] = 1/fx, 1/fy, filled in when the kernel stages the camera (stage_cam): no division per pixel
+  double pw0 = (u - c[2]) * c[21];
+  double pw1 = (v - c[3]) * c[22];
+  const double thd2 = fma(pw0, pw0, pw1 * pw1);
+  double thd = thd2 > 0.0 ? thd2 * rsqrt_nr(thd2) : 0.0;
   thd = fmin(fmax(-1.5707963267948966, thd), 1.5707963267948966);
   bool converged = false;
   double th = thd, scale = 0.0;
@@ -22,11 +30,12 @@ __device__ __forceinline__ void undistort_fisheye(const double* __restrict__ c, 
     for (int j = 0; j < 10; ++j) {
       double t2 = th * th, t4 = t2 * t2, t6 = t4 * t2, t8 = t4 * t4;
       double k0 = c[5] * t2, k1 = c[6] * t4, k2 = c[7] * t6, k3 = c[8] * t8;
-      double fix = (th * (1.0 + k0 + k1 + k2 + k3) - thd) / (1.0 + 3.0 * k0 + 5.0 * k1 + 7.0 * k2 + 9.0 * k3);
+      double fix = (th * (1.0 + k0 + k1 + k2 + k3) - thd) * rcp_nr(1.0 + 3.0 * k0 + 5.0 * k1 + 7.0 * k2 + 9.0 * k3);
       th -= fix;
       if (fabs(fix) < 1e-8) { converged = true; break; }
     }
-    scale = tan(th) / thd;
+    // th and thd share their sign and |th| < pi/2 here (flipped or non-converged results are discarded below)
+    scale = (th > 0.0 && th < 1.5707963267948966 ? tan_first_quadrant(th) : tan(th)) * rcp_nr(thd);
   } else {
     converged = true;
   }
@@ -108,7 +117,7 @@ __device__ __forceinline__ void dlt_pair(const double* __restrict__ ca, const do
     h0 = z0; h1 = z1; h2 = z2; h3 = z3;
     if (fmax(fmax(fabs(d0), fabs(d1)), fmax(fabs(d2), fabs(d3))) < 1e-15 && dot > 0.0) break;
   }
-  const double ih = 1.0 / h3;
+  const double ih = rcp_nr(h3);
   X[0] = h0 * ih; X[1] = h1 * ih; X[2] = h2 * ih;
 }
 
@@ -116,7 +125,7 @@ __global__ void __launch_bounds__(128) tri_pair_kernel(const double2* __restrict
                                                        int64_t M, const double* __restrict__ cams2,
                                                        double* __restrict__ xyz) {
   __shared__ double sc[2 * CAM_STRIDE];
-  if (threadIdx.x < 2 * CAM_STRIDE) sc[threadIdx.x] = cams2[threadIdx.x];
+  if (threadIdx.x < 2 * CAM_STRIDE) sc[threadIdx.x] = stage_cam(cams2, threadIdx.x);
   __syncthreads();
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= M) return;
@@ -138,7 +147,7 @@ __global__ void __launch_bounds__(128) tri_ring_kernel(const double2* __restrict
                                                        double* __restrict__ xyz, uint8_t* __restrict__ obs_mask,
                                                        uint8_t* __restrict__ exists) {
   __shared__ double sc[C * CAM_STRIDE];
-  for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[i] = cams.v[i];
+  for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[i] = stage_cam(cams.v, i);
   __syncthreads();
   int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
