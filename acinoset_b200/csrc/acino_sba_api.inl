@@ -159,6 +159,7 @@ void acino_sba_default_opts(acino_sba_opts* o, int mode) {
     o->hess_floor = 0.3;
     o->point_refine_iters = 2;
     o->point_refine_skip = 1e-11;
+    o->polish_tol = 3e-5;
     o->lambda0 = 1e-4;
   } else {
     o->max_iter = 200;

@@ -157,7 +157,7 @@ lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs
         if (!prm.force && !(gmax > prm.gtol)) { st = ST_CONVERGED; break; }
         double d[3];
         double pred = lm_step3(ne, lam, d);
-        if (prm.skip_pred > 0.0 && pred <= prm.skip_pred * fmax(ne.F, prm.half_c2)) break;     // nothing to gain (refinement between camera steps)
+        if (prm.skip_pred > 0.0 && pred <= prm.skip_pred * fmax(ne.F, prm.half_c2)) { st = ST_CONVERGED; break; }     // nothing to gain (refinement between camera steps)
         NormalEq nt;
         const bool last = (it + 1 == prm.inner_iters);      // no further linearisation in this launch: cost only
         if (last) nt.F = eval_point_cost<C>(sc, uvr, 128, m, X + d[0], Y + d[1], Z + d[2], prm.inv_c2, prm.half_c2);

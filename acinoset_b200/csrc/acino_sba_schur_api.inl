@@ -253,6 +253,32 @@ static int schur_iterate(acino_sba* h, const acino_sba_opts* o) {
   return schur_launch_iteration(h, make_schur_params(o));
 }
 
+// the points solved to convergence with the cameras fixed (K3 on the current buffers until no point is active);
+// h_lm must hold the current device state (synchronised). No collective: every rank polishes its own shard.
+static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_launches) {
+  SchurState& s = h->schur;
+  const bool alt = s.h_lm->cur != 0;
+  const double* cams = alt ? s.cams_alt : h->cams;
+  double* X = alt ? s.X_alt : h->X;
+  LmParams lp;
+  lp.inv_c2 = prm.inv_c2; lp.half_c2 = prm.half_c2; lp.gtol = 1e-9; lp.xtol = 1e-13; lp.lambda0 = 1e-4;
+  lp.inner_iters = 8; lp.force = 0; lp.ignore_status = 1;
+  lp.skip_pred = prm.refine_skip;
+  for (int l = 0; l < max_launches; ++l) {
+    ACINO_CUDA(cudaMemsetAsync(h->counters, 0, 8 * sizeof(unsigned long long), h->stream));
+    DISPATCH_C(h->C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, h->stream>>>(
+                         h->uv, h->mask, h->P, cams, X, h->lam, h->cost_p, h->status, lp, h->counters,
+                         LmPointsCtl{nullptr, nullptr, nullptr, nullptr})));
+    ACINO_CUDA(cudaGetLastError());
+    ++s.launches;
+    ACINO_CUDA(cudaMemcpyAsync(h->h_counters, h->counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->h_counters[0] == 0) break;
+    lp.ignore_status = 0;
+  }
+  return ACINO_OK;
+}
+
 static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* st) {
   int rc = schur_ensure(h);
   if (rc) return rc;
@@ -264,11 +290,31 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
   if (rc) return rc;
   SchurParams prm = make_schur_params(o);
   int it = 0;
+  // Polishing (polish_tol): the joint steps settle the cameras within a few tens of iterations, after which the cost
+  // only creeps down because 10^6 points each finish their own small robust problem two refinement steps at a time.
+  // Once an accepted step gains less than polish_tol the points are therefore solved to convergence with the cameras
+  // fixed, and the ftol / stall rules may end the solve only on a step that directly follows such a polish.
+  const bool polish = o->polish_tol > 0.0 && prm.refine > 0 && !o->force_iters;
+  int last_polish = -1000;
   for (; it < o->max_iter; ++it) {
     rc = schur_launch_iteration(h, prm);
     if (rc) return rc;
     ACINO_CUDA(cudaMemcpyAsync(s.h_lm, s.lm, sizeof(SchurLm), cudaMemcpyDeviceToHost, h->stream));
     ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    if (polish) {
+      const bool ended = (s.h_lm->status == 2 || s.h_lm->status == 4) && it - last_polish > 1;
+      const bool creeping = s.h_lm->status == 0 && s.h_lm->last_accept && s.h_lm->last_rel_dec < o->polish_tol && it - last_polish >= 4;
+      if (ended || creeping) {
+        rc = schur_polish_points(h, prm, 12);
+        if (rc) return rc;
+        last_polish = it;
+        s.h_lm->status = 0;
+        s.h_lm->need_cost = 1;         // the next linearisation evaluates the cost of the polished points
+        if (ended) { s.h_lm->lambda = fmin(s.h_lm->lambda, 1e-2); s.h_lm->nu = 2.0; }
+        ACINO_CUDA(cudaMemcpyAsync(s.lm, s.h_lm, sizeof(SchurLm), cudaMemcpyHostToDevice, h->stream));
+        continue;
+      }
+    }
     if (s.h_lm->status != 0 && !o->force_iters) break;
   }
   if (s.h_lm->need_cost) {

@@ -121,6 +121,9 @@ typedef struct {
                                 the cameras fixed (K3 on the current buffers; each point has its own damping) */
   double point_refine_skip;  /* the refinement leaves a point alone when its model predicts a cost decrease
                               * <= point_refine_skip * max(cost of the point, f_scale^2/2); 0 = refine every point */
+  double polish_tol;         /* points+extrinsics, acino_sba_solve: once an accepted step gains less than polish_tol
+                              * (relative), and again before ftol may end the solve, the points are solved to convergence
+                              * with the cameras fixed (K3 until no point is active); 0 = never */
 } acino_sba_opts;
 
 typedef struct {
