@@ -1,6 +1,8 @@
 // acino.cu — C ABI (include/acino_b200.h) over the sm_100a kernels. Single translation unit.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <new>
 #include <vector>

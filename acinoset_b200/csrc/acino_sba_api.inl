@@ -157,10 +157,10 @@ void acino_sba_default_opts(acino_sba_opts* o, int mode) {
     o->xtol = 1e-14;
     o->ftol = 1e-14;
     o->hess_floor = 0.3;
-    o->point_refine_iters = 2;
+    o->point_refine_iters = 3;
     o->point_refine_skip = 1e-11;
-    o->polish_tol = 3e-5;
-    o->lambda0 = 1e-4;
+    o->polish_tol = 3e-4;
+    o->lambda0 = 1.0;            // cautious first steps: a small start lets the first accepted step throw points into worse basins of the robust cost
   } else {
     o->max_iter = 200;
     o->inner_iters = 8;

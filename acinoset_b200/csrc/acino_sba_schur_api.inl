@@ -264,7 +264,9 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
   lp.inv_c2 = prm.inv_c2; lp.half_c2 = prm.half_c2; lp.gtol = 1e-9; lp.xtol = 1e-13; lp.lambda0 = 1e-4;
   lp.inner_iters = 8; lp.force = 0; lp.ignore_status = 1;
   lp.skip_pred = prm.refine_skip;
+  const bool trace = getenv("ACINO_TRACE") != nullptr;
   for (int l = 0; l < max_launches; ++l) {
+    const auto t0 = std::chrono::steady_clock::now();
     ACINO_CUDA(cudaMemsetAsync(h->counters, 0, 8 * sizeof(unsigned long long), h->stream));
     DISPATCH_C(h->C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, h->stream>>>(
                          h->uv, h->mask, h->P, cams, X, h->lam, h->cost_p, h->status, lp, h->counters,
@@ -273,6 +275,9 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
     ++s.launches;
     ACINO_CUDA(cudaMemcpyAsync(h->h_counters, h->counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
     ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    if (trace)
+      fprintf(stderr, "[acino]   polish launch %d: %llu points still active, %.3f ms\n", l, h->h_counters[0],
+              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     if (h->h_counters[0] == 0) break;
     lp.ignore_status = 0;
   }
@@ -296,17 +301,35 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
   // fixed, and the ftol / stall rules may end the solve only on a step that directly follows such a polish.
   const bool polish = o->polish_tol > 0.0 && prm.refine > 0 && !o->force_iters;
   int last_polish = -1000;
+  const bool trace = getenv("ACINO_TRACE") != nullptr;
+  auto t_prev = std::chrono::steady_clock::now();
+  if (trace) {
+    ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    fprintf(stderr, "[acino] init %.3f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_prev).count());
+    t_prev = std::chrono::steady_clock::now();
+  }
   for (; it < o->max_iter; ++it) {
     rc = schur_launch_iteration(h, prm);
     if (rc) return rc;
     ACINO_CUDA(cudaMemcpyAsync(s.h_lm, s.lm, sizeof(SchurLm), cudaMemcpyDeviceToHost, h->stream));
     ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    if (trace) {
+      const auto t = std::chrono::steady_clock::now();
+      fprintf(stderr, "[acino] it %d: %.3f ms, status %d accept %d rel_dec %.3g lambda %.3g cost %.6f\n", it,
+              std::chrono::duration<double, std::milli>(t - t_prev).count(), s.h_lm->status, s.h_lm->last_accept,
+              s.h_lm->last_rel_dec, s.h_lm->lambda, s.h_lm->F);
+      t_prev = t;
+    }
     if (polish) {
       const bool ended = (s.h_lm->status == 2 || s.h_lm->status == 4) && it - last_polish > 1;
       const bool creeping = s.h_lm->status == 0 && s.h_lm->last_accept && s.h_lm->last_rel_dec < o->polish_tol && it - last_polish >= 4;
       if (ended || creeping) {
+        const int l0 = s.launches;
         rc = schur_polish_points(h, prm, 12);
         if (rc) return rc;
+        if (getenv("ACINO_TRACE"))
+          fprintf(stderr, "[acino] polish at iteration %d (%s, rel_dec %.3g, cost %.6f): %d launches\n", it,
+                  ended ? "end rule" : "creeping", s.h_lm->last_rel_dec, s.h_lm->F, s.launches - l0);
         last_polish = it;
         s.h_lm->status = 0;
         s.h_lm->need_cost = 1;         // the next linearisation evaluates the cost of the polished points

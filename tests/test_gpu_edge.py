@@ -159,7 +159,7 @@ def test_full_size_schur_properties():
         for it in range(12):
             s.iterate(o)
             costs.append(s.lm_state()['cost'])
-        assert all(b <= a for a, b in zip(costs, costs[1:])) and costs[-1] < 0.5 * costs[0]
+        assert all(b <= a for a, b in zip(costs, costs[1:])) and costs[-1] < 0.5 * s.lm_state()['cost_first']
         f = s.residuals()
         sel = ((mask[:, None] >> np.arange(C)) & 1).astype(bool)
         c_chk = fe.cauchy_cost(f[sel], 1.0)
