@@ -15,6 +15,8 @@ struct acino_sba {
   double* lam = nullptr;             // P
   double* cost_p = nullptr;          // P
   uint8_t* status = nullptr;         // P
+  uint16_t* order = nullptr;         // P: K3's visiting order (point_order_kernel), tile-local offsets
+  bool order_valid = false;
   unsigned long long* counters = nullptr;   // device, 8
   unsigned long long* h_counters = nullptr; // pinned, 8
   double* partial = nullptr;         // device, 1024
@@ -61,9 +63,22 @@ static LmParams make_lm_params(const acino_sba_opts* o, int inner) {
   return p;
 }
 
+// K3's visiting order for the current masks (rebuilt after set_observations*, and by every solve: a device-side mask may
+// have been rewritten in place)
+static int ensure_point_order(acino_sba* h, bool rebuild = false) {
+  if ((h->order_valid && !rebuild) || !h->P) return ACINO_OK;
+  point_order_kernel<<<grid_for(h->P, ORDER_TILE), 256, 0, h->stream>>>(h->mask, h->P, h->order);
+  ACINO_CUDA(cudaGetLastError());
+  h->order_valid = true;
+  return ACINO_OK;
+}
+
 static int launch_lm_points(acino_sba* h, const LmParams& prm) {
+  int rc = ensure_point_order(h);
+  if (rc) return rc;
   DISPATCH_C(h->C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, h->stream>>>(
-                       h->uv, h->mask, h->P, h->cams, h->X, h->lam, h->cost_p, h->status, prm, h->counters, LmPointsCtl{nullptr, nullptr, nullptr, nullptr})));
+                       h->uv, h->mask, h->P, h->cams, h->X, h->lam, h->cost_p, h->status, prm, h->counters,
+                       LmPointsCtl{nullptr, nullptr, nullptr, nullptr}, h->order)));
   ACINO_CUDA(cudaGetLastError());
   return ACINO_OK;
 }
@@ -94,6 +109,7 @@ __global__ void count_obs_kernel(const uint8_t* __restrict__ m, int64_t P, unsig
 static int solve_points_only(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* st) {
   int launches = 0, iters = 0;
   ACINO_CUDA(cudaEventRecord(h->e0, h->stream));
+  { int rc = ensure_point_order(h, true); if (rc) return rc; ++launches; }
   // initial cost: evaluation only
   {
     acino_sba_opts o0 = *o;
@@ -191,6 +207,7 @@ acino_sba_t* acino_sba_create(int n_cams, int64_t n_points) {
   ok(cudaMalloc(&h->lam, P * sizeof(double)));
   ok(cudaMalloc(&h->cost_p, P * sizeof(double)));
   ok(cudaMalloc(&h->status, P));
+  ok(cudaMalloc(&h->order, (P + ORDER_TILE) * sizeof(uint16_t)));
   ok(cudaMalloc(&h->counters, 8 * sizeof(unsigned long long)));
   ok(cudaMallocHost(&h->h_counters, 8 * sizeof(unsigned long long)));
   ok(cudaMalloc(&h->partial, 1024 * sizeof(double)));
@@ -216,7 +233,7 @@ void acino_sba_destroy(acino_sba_t* h) {
   acino::comm_destroy(h);
   schur_free(h->schur);
   cudaFree(h->cams); cudaFree(h->rvec_t); cudaFree(h->uv_own); cudaFree(h->mask_own);
-  cudaFree(h->X); cudaFree(h->X0); cudaFree(h->lam); cudaFree(h->cost_p); cudaFree(h->status);
+  cudaFree(h->X); cudaFree(h->X0); cudaFree(h->lam); cudaFree(h->cost_p); cudaFree(h->status); cudaFree(h->order);
   cudaFree(h->counters); cudaFree(h->partial);
   if (h->h_counters) cudaFreeHost(h->h_counters);
   if (h->h_partial) cudaFreeHost(h->h_partial);
@@ -254,6 +271,7 @@ int acino_sba_set_observations(acino_sba_t* h, const double* uv, const uint8_t* 
   h->mask = h->mask_own;
   h->have_obs = true;
   h->schur.inited = false;      // the per-tile lists and the compacted observations are rebuilt by the next solve / iterate
+  h->order_valid = false;
   return ACINO_OK;
 }
 
@@ -264,6 +282,7 @@ int acino_sba_set_observations_dev(acino_sba_t* h, const double* uv_dev, const u
   h->mask = obs_mask_dev;
   h->have_obs = true;
   h->schur.inited = false;
+  h->order_valid = false;
   return ACINO_OK;
 }
 

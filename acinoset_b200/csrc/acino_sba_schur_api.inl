@@ -151,6 +151,8 @@ static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
     DISPATCH_C(h->C, (schur_lists_kernel<CC><<<(unsigned)s.n_tiles, schur_bt(CC), 0, h->stream>>>(h->mask, h->P, s.unit_lists, s.unit_counts,
                                                                                                   s.obs_lists, s.pt_start, s.pt_rank, h->uv, s.uvc)));
     ACINO_CUDA(cudaGetLastError());
+    int rc = ensure_point_order(h, true);      // K3 (refinement, polishing) visits the points by observation count
+    if (rc) return rc;
   }
   s.inited = true;
   s.launches = 0;
@@ -217,7 +219,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
     lp.skip_pred = prm.refine_skip;
     LmPointsCtl ctl{&s.lm->last_accept, &s.lm->cur, s.cams_alt, s.X_alt};
     DISPATCH_C(C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, st>>>(h->uv, h->mask, h->P, h->cams, h->X, h->lam, h->cost_p,
-                                                                          h->status, lp, h->counters, ctl)));
+                                                                          h->status, lp, h->counters, ctl, h->order)));
     ACINO_CUDA(cudaGetLastError());
     ++s.launches;
   }
@@ -270,7 +272,7 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
     ACINO_CUDA(cudaMemsetAsync(h->counters, 0, 8 * sizeof(unsigned long long), h->stream));
     DISPATCH_C(h->C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, h->stream>>>(
                          h->uv, h->mask, h->P, cams, X, h->lam, h->cost_p, h->status, lp, h->counters,
-                         LmPointsCtl{nullptr, nullptr, nullptr, nullptr})));
+                         LmPointsCtl{nullptr, nullptr, nullptr, nullptr}, h->order)));
     ACINO_CUDA(cudaGetLastError());
     ++s.launches;
     ACINO_CUDA(cudaMemcpyAsync(h->h_counters, h->counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
