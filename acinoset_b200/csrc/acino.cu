@@ -174,7 +174,7 @@ int acino_triangulate_pair(const double* uv1, const double* uv2, int64_t M, cons
 template <int C>
 static void launch_tri_ring(const double* uv, const double* lik, double thresh, int64_t P, const CamPack& cams,
                             double* xyz, uint8_t* mask, uint8_t* exists, cudaStream_t st) {
-  tri_ring_kernel<C><<<grid_for(P, 128), 128, 0, st>>>((const double2*)uv, lik, thresh, P, cams, xyz, mask, exists);
+  tri_ring_kernel<C><<<grid_for(P, TRI_BT), TRI_BT, 0, st>>>((const double2*)uv, lik, thresh, P, cams, xyz, mask, exists);
 }
 extern "C" {
 

@@ -9,6 +9,9 @@
 #include "../../include/acino_b200.h"
 
 #define CAM_STRIDE ACINO_CAM_STRIDE
+// stride of a camera block in shared memory where the lanes of a warp read DIFFERENT cameras (K2 phases 1-2, K3): odd, so
+// that the same field of up to 8 cameras falls into different banks
+#define CAM_SMEM_STRIDE 25
 #define MAX_CAMS ACINO_MAX_CAMS
 
 namespace acino {

@@ -12,7 +12,7 @@ namespace acino {
 // K3 keeps the cameras in shared memory with an odd stride: the lanes of a warp work on different cameras (points are
 // visited in the order of point_order_kernel, the warp's lanes share the NUMBER of observations, not the cameras), and
 // 25 doubles put the same field of the C cameras into different banks.
-#define K3_CAM_STRIDE 25
+#define K3_CAM_STRIDE CAM_SMEM_STRIDE
 #define ORDER_TILE 4096          // points per tile of the visiting order
 
 struct NormalEq {

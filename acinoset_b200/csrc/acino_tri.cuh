@@ -137,55 +137,96 @@ __global__ void __launch_bounds__(128) tri_pair_kernel(const double2* __restrict
   xyz[3 * i] = X[0]; xyz[3 * i + 1] = X[1]; xyz[3 * i + 2] = X[2];
 }
 
-// One thread per (frame, keypoint) point. C is a template parameter so the per-camera normalised
-// coordinates stay in registers.
+// One CTA per 128 (frame, keypoint) slot groups. The work of a slot group depends on its likelihoods (0..C undistortions,
+// 0..C ring pairs; at 50 % masking a third of the slots need either), so a thread per point leaves two thirds of the
+// lanes idle. The CTA therefore compacts the work in shared memory:
+//   phase 0  thread = point: threshold the likelihoods, ring-pair and needed-slot masks, block scan of the task counts,
+//            task lists (point, camera) and (point, pair)
+//   phase 1  thread = undistortion task -> normalised coordinates in shared memory
+//   phase 2  thread = pair task -> 4x4 DLT -> pair result in shared memory
+//   phase 3  thread = point: mean of its pair results in ring order (the summation order of the per-point loop it
+//            replaces: results are bit-identical), outputs
+// Lanes of a warp work on different cameras in phases 1-2: the cameras are staged with stride CAM_SMEM_STRIDE (25
+// doubles), which puts the same field of the C cameras into different banks.
 struct CamPack { double v[MAX_CAMS * CAM_STRIDE]; };   // cameras by value in the kernel parameters (1.5 KB)
+#define TRI_BT 128
 
 template <int C>
-__global__ void __launch_bounds__(128) tri_ring_kernel(const double2* __restrict__ uv, const double* __restrict__ lik,
-                                                       double thresh, int64_t P, const __grid_constant__ CamPack cams,
-                                                       double* __restrict__ xyz, uint8_t* __restrict__ obs_mask,
-                                                       uint8_t* __restrict__ exists) {
-  __shared__ double sc[C * CAM_STRIDE];
-  for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[i] = stage_cam(cams.v, i);
-  __syncthreads();
-  int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= P) return;
-  unsigned m = 0;
-  double nx[C], ny[C];
+__global__ void __launch_bounds__(TRI_BT) tri_ring_kernel(const double2* __restrict__ uv, const double* __restrict__ lik,
+                                                          double thresh, int64_t P, const __grid_constant__ CamPack cams,
+                                                          double* __restrict__ xyz, uint8_t* __restrict__ obs_mask,
+                                                          uint8_t* __restrict__ exists) {
+  constexpr int BT = TRI_BT, NW = BT / 32;
+  __shared__ double sc[C * CAM_SMEM_STRIDE];
+  __shared__ double2 s_n[C * BT];              // [c][q] normalised coordinates
+  __shared__ double s_X[3 * C * BT];           // [(a * 3 + k)][q] result of ring pair (a, a+1)
+  __shared__ unsigned short s_ul[C * BT], s_pl[C * BT];
+  __shared__ int s_wsum[2][NW];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < C * CAM_STRIDE; i += BT) sc[(i / CAM_STRIDE) * CAM_SMEM_STRIDE + i % CAM_STRIDE] = stage_cam(cams.v, i);
+  const int64_t p0 = (int64_t)blockIdx.x * BT, p = p0 + tid;
+  // ---- phase 0
+  unsigned m = 0, pairs = 0, need = 0;
+  if (p < P) {
 #pragma unroll
-  for (int c = 0; c < C; ++c) {
-    double l = lik[p * C + c];
-    if (l > thresh) m |= 1u << c;
-  }
-  // a slot is needed only if one of its ring neighbours is present too
-  unsigned rot_l = ((m << 1) | (m >> (C - 1))) & ((1u << C) - 1);   // bit c set if cam c-1 present
-  unsigned rot_r = ((m >> 1) | (m << (C - 1))) & ((1u << C) - 1);   // bit c set if cam c+1 present
-  unsigned pairs = m & rot_r;                                       // bit a: pair (a, a+1) valid
-  unsigned need = m & (rot_l | rot_r);
-#pragma unroll
-  for (int c = 0; c < C; ++c) {
-    if (need >> c & 1) {
-      double2 q = uv[p * C + c];
-      undistort_fisheye(sc + c * CAM_STRIDE, q.x, q.y, nx[c], ny[c]);
-    } else { nx[c] = 0; ny[c] = 0; }
-  }
-  double sx = 0, sy = 0, sz = 0;
-  int n = 0;
-#pragma unroll
-  for (int a = 0; a < C; ++a) {
-    const int b = (a + 1) % C;
-    if (pairs >> a & 1) {
-      double X[3];
-      dlt_pair(sc + a * CAM_STRIDE, sc + b * CAM_STRIDE, nx[a], ny[a], nx[b], ny[b], X);
-      sx += X[0]; sy += X[1]; sz += X[2];
-      ++n;
+    for (int c = 0; c < C; ++c) {
+      double l = lik[p * C + c];
+      if (l > thresh) m |= 1u << c;
     }
+    // a slot is needed only if one of its ring neighbours is present too
+    unsigned rot_l = ((m << 1) | (m >> (C - 1))) & ((1u << C) - 1);   // bit c set if cam c-1 present
+    unsigned rot_r = ((m >> 1) | (m << (C - 1))) & ((1u << C) - 1);   // bit c set if cam c+1 present
+    pairs = m & rot_r;                                                // bit a: pair (a, a+1) valid
+    need = m & (rot_l | rot_r);
   }
-  obs_mask[p] = n > 0 ? (uint8_t)m : (uint8_t)0;   // observations of existing points only (inner merge, src/lib/sba.py:299)
-  exists[p] = n > 0;
-  if (n > 0) {
-    double dn = (double)n;           // pandas mean: sum / count
+  const int nu = __popc(need), np = __popc(pairs);
+  int su = nu, sp = np;                         // inclusive warp scans
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int tu = __shfl_up_sync(0xffffffffu, su, o), tp = __shfl_up_sync(0xffffffffu, sp, o);
+    if (lane >= o) { su += tu; sp += tp; }
+  }
+  if (lane == 31) { s_wsum[0][warp] = su; s_wsum[1][warp] = sp; }
+  __syncthreads();
+  int ou = su - nu, op = sp - np, tot_u = 0, tot_p = 0;
+#pragma unroll
+  for (int w = 0; w < NW; ++w) {
+    const int a = s_wsum[0][w], b = s_wsum[1][w];
+    if (w < warp) { ou += a; op += b; }
+    tot_u += a; tot_p += b;
+  }
+  for (unsigned mm = need; mm; mm &= mm - 1) s_ul[ou++] = (unsigned short)(tid | (__ffs(mm) - 1) << 8);
+  for (unsigned mm = pairs; mm; mm &= mm - 1) s_pl[op++] = (unsigned short)(tid | (__ffs(mm) - 1) << 8);
+  __syncthreads();
+  // ---- phase 1
+  for (int i = tid; i < tot_u; i += BT) {
+    const int t = s_ul[i], q = t & 255, c = t >> 8;
+    const double2 o = uv[(p0 + q) * C + c];
+    double nx, ny;
+    undistort_fisheye(sc + c * CAM_SMEM_STRIDE, o.x, o.y, nx, ny);
+    s_n[c * BT + q] = make_double2(nx, ny);
+  }
+  __syncthreads();
+  // ---- phase 2
+  for (int i = tid; i < tot_p; i += BT) {
+    const int t = s_pl[i], q = t & 255, a = t >> 8, b = a + 1 == C ? 0 : a + 1;
+    const double2 na = s_n[a * BT + q], nb = s_n[b * BT + q];
+    double X[3];
+    dlt_pair(sc + a * CAM_SMEM_STRIDE, sc + b * CAM_SMEM_STRIDE, na.x, na.y, nb.x, nb.y, X);
+    s_X[(a * 3) * BT + q] = X[0]; s_X[(a * 3 + 1) * BT + q] = X[1]; s_X[(a * 3 + 2) * BT + q] = X[2];
+  }
+  __syncthreads();
+  // ---- phase 3
+  if (p >= P) return;
+  obs_mask[p] = np > 0 ? (uint8_t)m : (uint8_t)0;   // observations of existing points only (inner merge, src/lib/sba.py:299)
+  exists[p] = np > 0;
+  if (np > 0) {
+    double sx = 0, sy = 0, sz = 0;
+    for (unsigned mm = pairs; mm; mm &= mm - 1) {
+      const int a = __ffs(mm) - 1;
+      sx += s_X[(a * 3) * BT + tid]; sy += s_X[(a * 3 + 1) * BT + tid]; sz += s_X[(a * 3 + 2) * BT + tid];
+    }
+    double dn = (double)np;          // pandas mean: sum / count
     xyz[3 * p] = sx / dn; xyz[3 * p + 1] = sy / dn; xyz[3 * p + 2] = sz / dn;
   } else {
     double nan = __longlong_as_double(0x7ff8000000000000LL);
