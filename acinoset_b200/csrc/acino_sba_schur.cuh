@@ -285,7 +285,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
   double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0;
   double cprod = 1.0;     // running product of (1+z_u)(1+z_v): sum of log1p(z) = log of the product
   const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
-  // the first tile's points and mask; later tiles are fetched while the previous tile is in phase 2
+  // the first tile's points, mask and observation list; later tiles are fetched one tile ahead
   unsigned m_next = 0u;
   int buf = 0;
   if ((int64_t)blockIdx.x < n_tiles) {
@@ -296,14 +296,30 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
     }
     for (int i = tid; i < OB / 8; i += BT)
       cp_async16(reinterpret_cast<char*>(olbuf) + 16 * i, reinterpret_cast<const char*>(obs_lists) + ((size_t)blockIdx.x * OB) * 2 + 16 * i);
+    cp_async_wait_all();
+    __syncthreads();
   }
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    // ---------------- phase 1a: the tile's points and observation list were fetched while the previous tile was in phase 2
+    // ---------------- phase 1a: the tile's points and observation list are in shared memory and visible (they were waited
+    // for before the barrier that opened phase 2 of the previous tile): no barrier here. Issue the copies that phase 2
+    // will need: the next tile's points, list and mask (other buffers) and this tile's unit lists.
     double* sX = sXbuf + buf * 3 * BS;
     const unsigned short* olist = olbuf + buf * OB;
     const unsigned m = m_next;
     const int rank = pt_rank[tile * BT + tid];       // used in phase 1c: the load has the whole of 1a/1b to land
-    cp_async_wait_all();
+    {
+      const int64_t pn = (tile + gridDim.x) * BT + tid;
+      m_next = 0u;
+      if (pn < P) {
+        double* sXn = sXbuf + (buf ^ 1) * 3 * BS;
+        m_next = obs_mask[pn];
+        cp_async8(sXn + tid, Xp + 3 * pn); cp_async8(sXn + BS + tid, Xp + 3 * pn + 1); cp_async8(sXn + 2 * BS + tid, Xp + 3 * pn + 2);
+      }
+      if (tile + gridDim.x < n_tiles)
+        for (int i = tid; i < OB / 8; i += BT)
+          cp_async16(reinterpret_cast<char*>(olbuf + (buf ^ 1) * OB) + 16 * i,
+                     reinterpret_cast<const char*>(obs_lists) + ((size_t)(tile + gridDim.x) * OB) * 2 + 16 * i);
+    }
     {   // this tile's unit lists (precomputed from the masks, schur_lists_kernel): in flight during phase 1
       const char* src = reinterpret_cast<const char*>(unit_lists) + (size_t)tile * L::list_bytes;
       char* dst = reinterpret_cast<char*>(list);
@@ -316,7 +332,6 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       double X = sX[tid], Y = sX[BS + tid], Z = sX[2 * BS + tid];
       xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
     }
-    __syncthreads();
     // ---------------- phase 1b: one thread per observation: residual, Jacobian rows, robust weights
     {
       const int n_obs = olist[0];
@@ -380,22 +395,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       gmax_acc = fmax(gmax_acc, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
     }
     if (tid == 0) next_unit[0] = 0;
-    {   // fetch the next tile's points (other buffer) and mask: the latency hides behind phase 2
-      const int64_t pn = (tile + gridDim.x) * BT + tid;
-      m_next = 0u;
-      if (pn < P) {
-        double* sXn = sXbuf + (buf ^ 1) * 3 * BS;
-        m_next = obs_mask[pn];
-        cp_async8(sXn + tid, Xp + 3 * pn); cp_async8(sXn + BS + tid, Xp + 3 * pn + 1); cp_async8(sXn + 2 * BS + tid, Xp + 3 * pn + 2);
-      }
-      if (tile + gridDim.x < n_tiles)
-        for (int i = tid; i < OB / 8; i += BT)
-          cp_async16(reinterpret_cast<char*>(olbuf + (buf ^ 1) * OB) + 16 * i,
-                     reinterpret_cast<const char*>(obs_lists) + ((size_t)(tile + gridDim.x) * OB) * 2 + 16 * i);
-      cp_async_commit();
-      buf ^= 1;
-    }
-    cp_async_wait_group1();     // the lists have landed; the next tile's points may still be in flight
+    cp_async_wait_all();        // the unit lists and the next tile's points / observation list have landed
     __syncthreads();
     // ---------------- phase 2: warps take units (longest first: diagonal units lead) until none is left
     for (;;) {
@@ -492,6 +492,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
         for (int i = 0; i < 5; ++i) dst[i] += acc[i];
       }
     }
+    buf ^= 1;
     __syncthreads();
   }
 
