@@ -702,41 +702,32 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
 // ---- K6: back-substitution + trial evaluation --------------------------------------------------------------
 // Nothing is linearised twice: K4 leaves, per observation, the weighted point-Jacobian rows N (6 doubles, in the tile's
 // observation-list order) and, per point, V^-1 (6), h = V^-1 g (3), the damping diagonal D (3) and the gradient g (3).
-// Persistent CTAs walk the same tiles as K4 with the same precomputed observation lists:
-//   stage A (thread = observation): s_o = N^T (N d_c), d_c = w_c x X + tau_c the camera step seen by the point -> shared;
-//   stage B (thread = point): s = sum of its observations' s_o, dX = -(h + V^-1 s), trial point to HBM and shared,
-//            predicted reduction of the point block 0.5 lam dX^T D dX - 0.5 g^T dX, max |dX|;
-//   stage C (thread = observation): project the trial point with the trial camera, robust cost as a running product.
-// Per-block partials: [trial cost, predicted reduction of the point blocks, max |dX|, 0].
+// One thread owns one point, without tiles, shared staging or barriers: it walks the point's own observations (they are
+// consecutive in the tile's list order, so the staged rows of a warp's points form one contiguous run per plane) for
+// s = sum N^T (N d_c), d_c = w_c x X + tau_c the camera step seen by the point; takes the step dX = -(h + V^-1 s); writes
+// the trial point; adds the predicted reduction of the point block 0.5 lam dX^T D dX - 0.5 g^T dX and max |dX|; and
+// projects the trial point with the trial cameras for the robust trial cost (a running product, one log per overflow).
+// Only the trial cameras and the camera steps sit in shared memory, so an SM holds 32 warps and the loads of different
+// points overlap: the kernel is HBM bound, and this form took it from 0.218 ms (tiles of 384 points staged in shared
+// memory, thread per observation, four barriers per tile) to 0.172 ms at 119,490 frames. The rows of the next
+// observation are requested before the current one is used. Points are visited from the last to the first (the rows
+// K4 staged last are still in the 126 MB L2). Sums per thread run in camera order; the per-CTA partials
+// [trial cost, predicted reduction, max |dX|, 0] are folded in a fixed order by K7: deterministic.
+#define SCHUR_BACKSUB_TB 256
+#define SCHUR_BACKSUB_MINB 4     // 64 registers: 32 warps per SM (3 CTAs of 80 registers measured 0.180 ms, 4 of 64: 0.172 ms)
 template <int C>
-struct BacksubSmem {
-  static constexpr int BT = schur_bt(C);
-  static constexpr int OB = 8 + C * BT;
-  // trial cameras, camera steps, s_o [3][C*BT], X [3][BT], dX [3][BT], observation list, point starts, masks
-  static constexpr size_t n_doubles = (size_t)C * CAM_STRIDE + 6 * C + 2 + 3 * (size_t)C * BT + 6 * BT;
-  static constexpr size_t bytes = n_doubles * 8 + (size_t)OB * 2 + BT * 2 + BT + 16;
-};
-
-template <int C>
-__global__ void __launch_bounds__(schur_bt(C), 2)
-schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
-                     const double* __restrict__ cams0, const double* __restrict__ cams1,
-                     const double* __restrict__ X0, const double* __restrict__ X1, double* __restrict__ Xt0,
-                     double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
-                     const double* __restrict__ delta_c, double* __restrict__ scal_partial,
-                     const unsigned short* __restrict__ obs_lists, const unsigned short* __restrict__ pt_start,
-                     const double* __restrict__ stgN, const double* __restrict__ stgP,
-                     const unsigned short* __restrict__ pt_rank, const double2* __restrict__ uvc) {
-  using L = BacksubSmem<C>;
-  constexpr int BT = L::BT, OB = L::OB, NW = BT / 32, CB = C * BT;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* st = reinterpret_cast<double*>(smem_raw);       // trial cameras
-  double* sd = st + C * CAM_STRIDE;                        // camera steps (w, tau) per camera
-  double* sS = sd + 6 * C + 2;                             // [k*CB + i], k<3
-  double* sX = sS + 3 * (size_t)CB;                        // [k*BT + q]
-  double* sDX = sX + 3 * BT;                               // [k*BT + q]: trial point X + dX
-  unsigned short* ol = reinterpret_cast<unsigned short*>(sDX + 3 * BT);   // [OB]
-  unsigned short* ps = ol + OB;                            // [q] first observation of point q in the list
+__global__ void __launch_bounds__(SCHUR_BACKSUB_TB, SCHUR_BACKSUB_MINB)
+schur_backsub_kernel(const uint8_t* __restrict__ obs_mask, int64_t P,
+                            const double* __restrict__ cams0, const double* __restrict__ cams1,
+                            const double* __restrict__ X0, const double* __restrict__ X1, double* __restrict__ Xt0,
+                            double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
+                            const double* __restrict__ delta_c, double* __restrict__ scal_partial,
+                            const unsigned short* __restrict__ pt_start, const double* __restrict__ stgN,
+                            const double* __restrict__ stgP, const unsigned short* __restrict__ pt_rank,
+                            const double2* __restrict__ uvc) {
+  constexpr int BT = schur_bt(C), CB = C * BT, TB = SCHUR_BACKSUB_TB, NW = TB / 32;
+  __shared__ double st[C * CAM_SMEM_STRIDE];   // trial cameras, odd stride: lanes on different cameras hit different banks
+  __shared__ double sd[6 * C + 2];             // camera steps (w, tau)
   __shared__ double red[3][NW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
@@ -745,79 +736,84 @@ schur_backsub_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__
   const double* __restrict__ camt = cur ? cams0 : cams1;
   const double* __restrict__ Xp = cur ? X1 : X0;
   double* __restrict__ Xt = cur ? Xt0 : Xt1;
-  const size_t PC = (size_t)P * C;
-  for (int i = tid; i < C * CAM_STRIDE; i += BT) st[i] = camt[i];
+  const size_t PC = (size_t)P * C, PS = (size_t)P;
+  for (int i = tid; i < C * CAM_STRIDE; i += TB) st[(i / CAM_STRIDE) * CAM_SMEM_STRIDE + i % CAM_STRIDE] = camt[i];
   if (tid < 6 * C) sd[tid] = delta_c[tid];
+  __syncthreads();
   double f_acc = 0.0, pred_acc = 0.0, dx_acc = 0.0;
-  double prod = 1.0;       // running product of (1+z_u)(1+z_v) over this thread's observations; logged when it grows large
-  const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
-  // tiles in the reverse of K4's order: the rows K4 staged last are still in the 126 MB L2
-  for (int64_t tile_r = blockIdx.x; tile_r < n_tiles; tile_r += gridDim.x) {
-    const int64_t tile = n_tiles - 1 - tile_r;
-    const int64_t p = tile * BT + tid;
-    const unsigned m = (p < P) ? obs_mask[p] : 0u;
-    const int64_t pr = tile * BT + pt_rank[tile * BT + tid];     // the point's record among the tile's existing points
-    {   // the tile's observation list (16-byte chunks), point starts, points
-      const uint4* src = reinterpret_cast<const uint4*>(obs_lists + (size_t)tile * OB);
-      uint4* dst = reinterpret_cast<uint4*>(ol);
-      for (int i = tid; i < OB / 8; i += BT) dst[i] = src[i];
-      ps[tid] = pt_start[(size_t)tile * BT + tid];
-      if (m) { sX[tid] = Xp[3 * p]; sX[BT + tid] = Xp[3 * p + 1]; sX[2 * BT + tid] = Xp[3 * p + 2]; }
+  double prod = 1.0;
+  const int64_t n_groups = skip ? 0 : (P + TB - 1) / TB;
+  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+    const int64_t p = P - 1 - (g * TB + tid);
+    if (p < 0) continue;
+    const unsigned m = obs_mask[p];
+    if (!m) continue;
+    const int64_t tile = p / BT;
+    const size_t gi0 = (size_t)tile * CB + pt_start[p];
+    const size_t pr = (size_t)tile * BT + pt_rank[p];
+    const double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+    const int k = __popc(m);
+    double2 ob_n = uvc[gi0];                     // first observation of stage C: in flight during the sums
+    {
+      unsigned mm = m;
+      size_t gi = gi0;
+      // the rows of the next observation are requested before the current one is used
+      double a0 = stgN[gi], a1 = stgN[PC + gi], a2 = stgN[2 * PC + gi];
+      double a3 = stgN[3 * PC + gi], a4 = stgN[4 * PC + gi], a5 = stgN[5 * PC + gi];
+#pragma unroll 1
+      for (int j = 0; j < k; ++j) {
+        const int c = __ffs(mm) - 1;
+        mm &= mm - 1;
+        const double n0x = a0, n0y = a1, n0z = a2, n1x = a3, n1y = a4, n1z = a5;
+        ++gi;
+        if (j + 1 < k) {
+          a0 = stgN[gi]; a1 = stgN[PC + gi]; a2 = stgN[2 * PC + gi];
+          a3 = stgN[3 * PC + gi]; a4 = stgN[4 * PC + gi]; a5 = stgN[5 * PC + gi];
+        }
+        const double* d = sd + 6 * c;
+        const double dx = fma(d[1], Z, -d[2] * Y) + d[3];
+        const double dy = fma(d[2], X, -d[0] * Z) + d[4];
+        const double dz = fma(d[0], Y, -d[1] * X) + d[5];
+        const double y0 = fma(n0x, dx, fma(n0y, dy, n0z * dz));
+        const double y1 = fma(n1x, dx, fma(n1y, dy, n1z * dz));
+        s0 += fma(n0x, y0, n1x * y1);
+        s1 += fma(n0y, y0, n1y * y1);
+        s2 += fma(n0z, y0, n1z * y1);
+      }
     }
-    __syncthreads();
-    const int n_obs = ol[0];
-    // ---- stage A
-    for (int i = tid; i < n_obs; i += BT) {
-      const int e = ol[8 + i], q = e >> 3, c = e & 7;
-      const size_t gi = (size_t)tile * CB + i;
-      const double n0x = stgN[gi], n0y = stgN[PC + gi], n0z = stgN[2 * PC + gi];
-      const double n1x = stgN[3 * PC + gi], n1y = stgN[4 * PC + gi], n1z = stgN[5 * PC + gi];
-      const double X = sX[q], Y = sX[BT + q], Z = sX[2 * BT + q];
-      const double* d = sd + 6 * c;
-      const double dx = fma(d[1], Z, -d[2] * Y) + d[3];
-      const double dy = fma(d[2], X, -d[0] * Z) + d[4];
-      const double dz = fma(d[0], Y, -d[1] * X) + d[5];
-      const double y0 = fma(n0x, dx, fma(n0y, dy, n0z * dz));
-      const double y1 = fma(n1x, dx, fma(n1y, dy, n1z * dz));
-      sS[i] = fma(n0x, y0, n1x * y1);
-      sS[CB + i] = fma(n0y, y0, n1y * y1);
-      sS[2 * CB + i] = fma(n0z, y0, n1z * y1);
+    // the point's record is requested after the sums: 30 fewer live registers in the loop above
+    const double i00 = stgP[pr], i01 = stgP[PS + pr], i02 = stgP[2 * PS + pr];
+    const double i11 = stgP[3 * PS + pr], i12 = stgP[4 * PS + pr], i22 = stgP[5 * PS + pr];
+    const double h0 = stgP[6 * PS + pr], h1 = stgP[7 * PS + pr], h2 = stgP[8 * PS + pr];
+    const double D0 = stgP[9 * PS + pr], D1 = stgP[10 * PS + pr], D2 = stgP[11 * PS + pr];
+    const double g0 = stgP[12 * PS + pr], g1 = stgP[13 * PS + pr], g2 = stgP[14 * PS + pr];
+    const double d0 = -(h0 + fma(i00, s0, fma(i01, s1, i02 * s2)));
+    const double d1 = -(h1 + fma(i01, s0, fma(i11, s1, i12 * s2)));
+    const double d2 = -(h2 + fma(i02, s0, fma(i12, s1, i22 * s2)));
+    // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta) with the undamped gradient g
+    pred_acc += 0.5 * (lam * (D0 * d0 * d0 + D1 * d1 * d1 + D2 * d2 * d2) - fma(g0, d0, fma(g1, d1, g2 * d2)));
+    const double xt = X + d0, yt = Y + d1, zt = Z + d2;
+    Xt[3 * p] = xt; Xt[3 * p + 1] = yt; Xt[3 * p + 2] = zt;
+    dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
+    {
+      unsigned mm = m;
+      size_t gi = gi0;
+#pragma unroll 1
+      for (int j = 0; j < k; ++j) {
+        const int c = __ffs(mm) - 1;
+        mm &= mm - 1;
+        const double2 ob = ob_n;
+        ++gi;
+        if (j + 1 < k) ob_n = uvc[gi];
+        double x, y, z, u, v;
+        to_camera(st + c * CAM_SMEM_STRIDE, xt, yt, zt, x, y, z);
+        fisheye_uv(st + c * CAM_SMEM_STRIDE, x, y, z, u, v);
+        const double fu = u - ob.x, fv = v - ob.y;
+        prod *= fma(fu * fu, prm.inv_c2, 1.0) * fma(fv * fv, prm.inv_c2, 1.0);
+        if (prod > 1e200) { f_acc += log(prod); prod = 1.0; }      // sum of log1p(z) = log of the product; rare
+      }
     }
-    __syncthreads();
-    // ---- stage B
-    if (m) {
-      const int k = __popc(m), b = ps[tid];
-      double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-      for (int i = 0; i < k; ++i) { s0 += sS[b + i]; s1 += sS[CB + b + i]; s2 += sS[2 * CB + b + i]; }
-      const size_t PS = (size_t)P;
-      const double i00 = stgP[pr], i01 = stgP[PS + pr], i02 = stgP[2 * PS + pr];
-      const double i11 = stgP[3 * PS + pr], i12 = stgP[4 * PS + pr], i22 = stgP[5 * PS + pr];
-      const double h0 = stgP[6 * PS + pr], h1 = stgP[7 * PS + pr], h2 = stgP[8 * PS + pr];
-      const double D0 = stgP[9 * PS + pr], D1 = stgP[10 * PS + pr], D2 = stgP[11 * PS + pr];
-      const double g0 = stgP[12 * PS + pr], g1 = stgP[13 * PS + pr], g2 = stgP[14 * PS + pr];
-      const double d0 = -(h0 + fma(i00, s0, fma(i01, s1, i02 * s2)));
-      const double d1 = -(h1 + fma(i01, s0, fma(i11, s1, i12 * s2)));
-      const double d2 = -(h2 + fma(i02, s0, fma(i12, s1, i22 * s2)));
-      // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta) with the undamped gradient g
-      pred_acc += 0.5 * (lam * (D0 * d0 * d0 + D1 * d1 * d1 + D2 * d2 * d2) - fma(g0, d0, fma(g1, d1, g2 * d2)));
-      const double xt = sX[tid] + d0, yt = sX[BT + tid] + d1, zt = sX[2 * BT + tid] + d2;
-      Xt[3 * p] = xt; Xt[3 * p + 1] = yt; Xt[3 * p + 2] = zt;
-      sDX[tid] = xt; sDX[BT + tid] = yt; sDX[2 * BT + tid] = zt;
-      dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
-    }
-    __syncthreads();
-    // ---- stage C
-    for (int i = tid; i < n_obs; i += BT) {
-      const int e = ol[8 + i], q = e >> 3, c = e & 7;
-      const double2 ob = uvc[(size_t)tile * CB + i];
-      double x, y, z, u, v;
-      to_camera(st + c * CAM_STRIDE, sDX[q], sDX[BT + q], sDX[2 * BT + q], x, y, z);
-      fisheye_uv(st + c * CAM_STRIDE, x, y, z, u, v);
-      const double fu = u - ob.x, fv = v - ob.y;
-      prod *= fma(fu * fu, prm.inv_c2, 1.0) * fma(fv * fv, prm.inv_c2, 1.0);
-      if (prod > 1e200) { f_acc += log(prod); prod = 1.0; }      // sum of log1p(z) = log of the product; rare
-    }
-    __syncthreads();
   }
   f_acc = prm.half_c2 * (f_acc + log(prod));
 #pragma unroll

@@ -78,11 +78,12 @@ static int schur_alloc(acino_sba* h) {
   int64_t tiles = (h->P + bt - 1) / bt;
   { const int64_t cap = (int64_t)sms * schur_ctas_per_sm(C); s.grid_build = (int)(tiles < 1 ? 1 : (tiles < cap ? tiles : cap)); }
   int occ = 1;     // resident CTAs per SM of the persistent back-substitution kernel
-  DISPATCH_C(C, (cudaFuncSetAttribute(schur_backsub_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)BacksubSmem<CC>::bytes)));
-  DISPATCH_C(C, (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, schur_backsub_kernel<CC>, schur_bt(CC), BacksubSmem<CC>::bytes)));
+  DISPATCH_C(C, (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, schur_backsub_kernel<CC>, SCHUR_BACKSUB_TB, 0)));
   if (occ < 1) occ = 1;
-  s.grid_back = (int)(tiles < 1 ? 1 : (tiles < (int64_t)sms * occ ? tiles : (int64_t)sms * occ));
+  {
+    const int64_t groups = (h->P + SCHUR_BACKSUB_TB - 1) / SCHUR_BACKSUB_TB;
+    s.grid_back = (int)(groups < 1 ? 1 : (groups < (int64_t)sms * occ ? groups : (int64_t)sms * occ));
+  }
   size_t P = h->P ? (size_t)h->P : 1;
   ACINO_CUDA(cudaMalloc(&s.cams_alt, MAX_CAMS * CAM_STRIDE * sizeof(double)));
   ACINO_CUDA(cudaMalloc(&s.X_alt, P * 3 * sizeof(double)));
@@ -189,9 +190,9 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   ++s.launches;
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 2], st));
-  DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, schur_bt(CC), BacksubSmem<CC>::bytes, st>>>(
-                    h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, h->X, s.X_alt, s.lm, prm, s.delta_c, s.scal_partial,
-                    s.obs_lists, s.pt_start, s.stgN, s.stgP, s.pt_rank, s.uvc)));
+  DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, SCHUR_BACKSUB_TB, 0, st>>>(
+                    h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, h->X, s.X_alt, s.lm, prm, s.delta_c, s.scal_partial,
+                    s.pt_start, s.stgN, s.stgP, s.pt_rank, s.uvc)));
   ACINO_CUDA(cudaGetLastError());
   if (prof) { ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 3], st)); ++s.prof_n; }
   ++s.launches;
