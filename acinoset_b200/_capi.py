@@ -84,6 +84,7 @@ SIGNATURES = {
     'acino_fp64_peak': (_I, [ct.POINTER(_D)]),
     'acino_nccl_unique_id': (_I, [_P]),
     'acino_sba_comm_init': (_I, [_P, _P, _I, _I]),
+    'acino_sba_comm_mode': (_I, [_P]),
 }
 
 _lib = None

@@ -27,6 +27,7 @@ struct acino_sba {
   acino::SchurState schur;
   void* nccl_comm = nullptr;
   int rank = 0, nranks = 1;
+  acino::PeerXchg xchg;              // NVLink peer-memory exchange for the per-iteration all-reduces (falls back to NCCL)
 };
 
 namespace acino {

@@ -14,6 +14,7 @@
 //   scalars               : [0] robust cost at the current parameters
 #pragma once
 #include "acino_common.cuh"
+#include "acino_sba_xchg.cuh"
 
 namespace acino {
 
@@ -526,7 +527,7 @@ __global__ void __launch_bounds__(1024)
 schur_solve_kernel(const double* __restrict__ partial, int n_partial, const double* __restrict__ maxp, int n_max,
                    const double* __restrict__ cams0, const double* __restrict__ cams1, double* __restrict__ cams_trial0,
                    double* __restrict__ cams_trial1, SchurLm* __restrict__ lm, SchurParams prm,
-                   double* __restrict__ delta_c) {
+                   double* __restrict__ delta_c, const unsigned long long* wait_flags, unsigned long long wait_seq) {
   constexpr int NU = rcs_units(C), LEN = rcs_len(C), n = 6 * C;
   __shared__ double r[LEN];
   __shared__ double A[n][n + 1];
@@ -538,22 +539,32 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   __shared__ int fail;
   const int tid = threadIdx.x;
   if (lm->status != 0 && !prm.force) return;
+  if (wait_flags) {
+    // peer exchange (acino_sba_xchg.cuh): partial / maxp are this rank's slots, one row per rank, written by the peers
+    // over NVLink; wait for every rank's sequence number, then add the rows in rank order (the same on every rank)
+    const bool ok = xchg_wait(wait_flags, n_partial, wait_seq, tid);
+    if (__syncthreads_or(!ok)) {
+      if (tid == 0) lm->status = 7;      // a peer never arrived: fail the solve instead of hanging
+      return;
+    }
+  }
   for (int i = tid; i < LEN; i += blockDim.x) {
-    // fixed summation order (four interleaved chains, then a fixed combine): deterministic, and the loads overlap
+    // fixed summation order (four interleaved chains, then a fixed combine): deterministic, and the loads overlap.
+    // ld.cg: the rows may have been written by another GPU, L1 must not answer
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
     int b = 0;
     for (; b + 4 <= n_partial; b += 4) {
-      s0 += partial[(size_t)b * LEN + i];
-      s1 += partial[(size_t)(b + 1) * LEN + i];
-      s2 += partial[(size_t)(b + 2) * LEN + i];
-      s3 += partial[(size_t)(b + 3) * LEN + i];
+      s0 += __ldcg(partial + (size_t)b * LEN + i);
+      s1 += __ldcg(partial + (size_t)(b + 1) * LEN + i);
+      s2 += __ldcg(partial + (size_t)(b + 2) * LEN + i);
+      s3 += __ldcg(partial + (size_t)(b + 3) * LEN + i);
     }
-    for (; b < n_partial; ++b) s0 += partial[(size_t)b * LEN + i];
+    for (; b < n_partial; ++b) s0 += __ldcg(partial + (size_t)b * LEN + i);
     r[i] = (s0 + s1) + (s2 + s3);
   }
   if (tid < 2) {
     double mx = 0.0;
-    for (int b = 0; b < n_max; ++b) mx = fmax(mx, maxp[2 * b + tid]);
+    for (int b = 0; b < n_max; ++b) mx = fmax(mx, __ldcg(maxp + 2 * b + tid));
     smax[tid] = mx;
   }
   if (tid == 0) fail = 0;
@@ -838,14 +849,22 @@ schur_backsub_kernel(const uint8_t* __restrict__ obs_mask, int64_t P,
 // scal = [n_scal][4] partials of the back-substitution kernel (or one all-reduced row).
 __global__ void __launch_bounds__(256)
 schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* __restrict__ dx_override,
-                    const double* __restrict__ delta_c, int n6, SchurLm* __restrict__ lm, SchurParams prm) {
+                    const double* __restrict__ delta_c, int n6, SchurLm* __restrict__ lm, SchurParams prm,
+                    const unsigned long long* wait_flags, unsigned long long wait_seq) {
   __shared__ double red[3][8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (lm->status != 0 && !prm.force) return;
+  if (wait_flags) {      // peer exchange: scal holds one row per rank, written by the peers
+    const bool ok = xchg_wait(wait_flags, n_scal, wait_seq, tid);
+    if (__syncthreads_or(!ok)) {
+      if (tid == 0) lm->status = 7;
+      return;
+    }
+  }
   double a = 0, b = 0, c = 0;
   for (int i = tid; i < n_scal; i += blockDim.x) {
-    a += scal[4 * i]; b += scal[4 * i + 1];
-    c = fmax(c, dx_override ? dx_override[0] : scal[4 * i + 2]);
+    a += __ldcg(scal + 4 * i); b += __ldcg(scal + 4 * i + 1);
+    c = fmax(c, dx_override ? dx_override[0] : __ldcg(scal + 4 * i + 2));
   }
   for (int i = tid; i < n6; i += blockDim.x) c = fmax(c, fabs(delta_c[i]));
 #pragma unroll

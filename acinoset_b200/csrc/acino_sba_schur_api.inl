@@ -12,12 +12,13 @@ struct NcclApi {
   int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
   int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
   int (*GroupStart)() = nullptr;
   int (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
 };
 static NcclApi g_nccl;
-static const int kNcclDouble = 8, kNcclSum = 0, kNcclMax = 2;
+static const int kNcclDouble = 8, kNcclChar = 0, kNcclSum = 0, kNcclMax = 2;
 
 static int nccl_load() {
   if (g_nccl.lib) return ACINO_OK;
@@ -34,6 +35,7 @@ static int nccl_load() {
   a.CommInitRank = (int (*)(void**, int, NcclId, int))dlsym(l, "ncclCommInitRank");
   a.CommDestroy = (int (*)(void*))dlsym(l, "ncclCommDestroy");
   a.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(l, "ncclAllReduce");
+  a.AllGather = (int (*)(const void*, void*, size_t, int, void*, cudaStream_t))dlsym(l, "ncclAllGather");
   a.GroupStart = (int (*)())dlsym(l, "ncclGroupStart");
   a.GroupEnd = (int (*)())dlsym(l, "ncclGroupEnd");
   a.GetErrorString = (const char* (*)(int))dlsym(l, "ncclGetErrorString");
@@ -53,7 +55,67 @@ static int nccl_load() {
     }                                                                                                      \
   } while (0)
 
+static void xchg_destroy(acino_sba* h) {
+  PeerXchg& x = h->xchg;
+  for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
+    if (x.mapped[r]) cudaIpcCloseMemHandle(x.mapped[r]);
+    x.mapped[r] = nullptr;
+  }
+  if (x.local) cudaFree(x.local);
+  x = PeerXchg();
+}
+
+// Peer-memory exchange (acino_sba_xchg.cuh): every rank exports a small buffer, the handles travel by ncclAllGather,
+// every rank maps every peer's buffer. All ranks then vote (NCCL sum) and use the exchange only if every mapping
+// succeeded everywhere; otherwise the per-iteration all-reduces stay on NCCL. ACINO_P2P=0 in the environment forces NCCL.
+static int xchg_setup(acino_sba* h) {
+  PeerXchg& x = h->xchg;
+  const int R = h->nranks, len = rcs_len(h->C);
+  const char* env = getenv("ACINO_P2P");
+  double ok = (R <= XCHG_MAX_RANKS && !(env && env[0] == '0') && g_nccl.AllGather) ? 1.0 : 0.0;
+  const size_t bytes = xchg_bytes(R, len);
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  if (ok != 0.0) {
+    if (cudaMalloc(&x.local, bytes) != cudaSuccess || cudaMemset(x.local, 0, bytes) != cudaSuccess ||
+        cudaDeviceSynchronize() != cudaSuccess || cudaIpcGetMemHandle(&mine, x.local) != cudaSuccess)
+      ok = 0.0;     // (flags and slots are zero before any peer can learn the handle)
+  }
+  // handles of all ranks (the collective runs even when this rank already failed: every rank must take part)
+  DevBuf hb;
+  ACINO_CUDA(hb.alloc((size_t)R * sizeof(cudaIpcMemHandle_t) + 16));
+  ACINO_CUDA(cudaMemcpyAsync(hb.as<char>() + (size_t)h->rank * sizeof(mine), &mine, sizeof(mine), cudaMemcpyHostToDevice, h->stream));
+  if (g_nccl.AllGather)
+    ACINO_NCCL(g_nccl.AllGather(hb.as<char>() + (size_t)h->rank * sizeof(mine), hb.as<char>(), sizeof(mine), kNcclChar,
+                                h->nccl_comm, h->stream));
+  std::vector<cudaIpcMemHandle_t> all((size_t)R);
+  ACINO_CUDA(cudaMemcpyAsync(all.data(), hb.as<char>(), (size_t)R * sizeof(mine), cudaMemcpyDeviceToHost, h->stream));
+  ACINO_CUDA(cudaStreamSynchronize(h->stream));
+  if (ok != 0.0) {
+    for (int r = 0; r < R; ++r) {
+      if (r == h->rank) { x.dev.base[r] = (unsigned char*)x.local; continue; }
+      if (cudaIpcOpenMemHandle(&x.mapped[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0.0; break; }
+      x.dev.base[r] = (unsigned char*)x.mapped[r];
+    }
+  }
+  cudaGetLastError();      // a failed mapping is not an error of the handle: the vote below decides
+  DevBuf vb;
+  ACINO_CUDA(vb.alloc(sizeof(double)));
+  ACINO_CUDA(cudaMemcpyAsync(vb.as<double>(), &ok, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  ACINO_NCCL(g_nccl.AllReduce(vb.as<double>(), vb.as<double>(), 1, kNcclDouble, kNcclSum, h->nccl_comm, h->stream));
+  double sum = 0.0;
+  ACINO_CUDA(cudaMemcpyAsync(&sum, vb.as<double>(), sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  ACINO_CUDA(cudaStreamSynchronize(h->stream));
+  if (sum != (double)R) { xchg_destroy(h); return ACINO_OK; }
+  x.dev.rank = h->rank;
+  x.dev.nranks = R;
+  x.dev.len = len;
+  x.enabled = true;
+  return ACINO_OK;
+}
+
 static void comm_destroy(acino_sba* h) {
+  xchg_destroy(h);
   if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
   h->nccl_comm = nullptr;
 }
@@ -178,15 +240,29 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
                                                         2, 2, 0, s.mx);
   ACINO_CUDA(cudaGetLastError());
   ++s.launches;
-  if (h->nranks > 1) {
-    ACINO_NCCL(g_nccl.GroupStart());
-    ACINO_NCCL(g_nccl.AllReduce(s.rcs, s.rcs, (size_t)len, kNcclDouble, kNcclSum, h->nccl_comm, st));
-    ACINO_NCCL(g_nccl.AllReduce(s.mx, s.mx, 2, kNcclDouble, kNcclMax, h->nccl_comm, st));
-    ACINO_NCCL(g_nccl.GroupEnd());
+  PeerXchg& px = h->xchg;
+  if (h->nranks > 1 && px.enabled) {
+    // peer exchange: push this rank's folded system into every rank's slot; K5 waits for all ranks and adds the rows
+    const unsigned long long seq = ++px.seq_a;
+    xchg_push_rcs_kernel<<<h->nranks, 256, 0, st>>>(px.dev, s.rcs, s.mx, seq);
+    ACINO_CUDA(cudaGetLastError());
     ++s.launches;
+    unsigned char* own = (unsigned char*)px.local;
+    const double* slot = xchg_slot_a(own, h->nranks, len, (int)(seq & 1));
+    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, 1024, 0, st>>>(slot, h->nranks, slot + (size_t)h->nranks * len, h->nranks, h->cams,
+                                                            s.cams_alt, h->cams, s.cams_alt, s.lm, prm, s.delta_c,
+                                                            xchg_flags(own, 0), seq)));
+  } else {
+    if (h->nranks > 1) {
+      ACINO_NCCL(g_nccl.GroupStart());
+      ACINO_NCCL(g_nccl.AllReduce(s.rcs, s.rcs, (size_t)len, kNcclDouble, kNcclSum, h->nccl_comm, st));
+      ACINO_NCCL(g_nccl.AllReduce(s.mx, s.mx, 2, kNcclDouble, kNcclMax, h->nccl_comm, st));
+      ACINO_NCCL(g_nccl.GroupEnd());
+      ++s.launches;
+    }
+    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, 1024, 0, st>>>(s.rcs, 1, s.mx, 1, h->cams, s.cams_alt, h->cams, s.cams_alt, s.lm, prm,
+                                                            s.delta_c, nullptr, 0ull)));
   }
-  DISPATCH_C(C, (schur_solve_kernel<CC><<<1, 1024, 0, st>>>(s.rcs, 1, s.mx, 1, h->cams, s.cams_alt, h->cams, s.cams_alt, s.lm, prm,
-                                                          s.delta_c)));
   ++s.launches;
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 2], st));
@@ -196,7 +272,15 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   ACINO_CUDA(cudaGetLastError());
   if (prof) { ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 3], st)); ++s.prof_n; }
   ++s.launches;
-  if (h->nranks > 1) {
+  if (h->nranks > 1 && px.enabled) {
+    const unsigned long long seq = ++px.seq_b;
+    unsigned char* own = (unsigned char*)px.local;
+    xchg_push_scal_kernel<<<1, 256, 0, st>>>(px.dev, s.scal_partial, s.grid_back, seq);
+    ACINO_CUDA(cudaGetLastError());
+    schur_decide_kernel<<<1, 256, 0, st>>>(xchg_slot_b(own, h->nranks, len, (int)(seq & 1)), h->nranks, nullptr, s.delta_c, 6 * C,
+                                           s.lm, prm, xchg_flags(own, 1), seq);
+    s.launches += 2;
+  } else if (h->nranks > 1) {
     fold_partials_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, 4, s.scal, s.scal_partial, s.grid_back, 1, 4, 2,
                                             s.scal + 4);
     ACINO_CUDA(cudaGetLastError());
@@ -204,10 +288,10 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
     ACINO_NCCL(g_nccl.AllReduce(s.scal, s.scal, 4, kNcclDouble, kNcclSum, h->nccl_comm, st));
     ACINO_NCCL(g_nccl.AllReduce(s.scal + 4, s.scal + 4, 1, kNcclDouble, kNcclMax, h->nccl_comm, st));
     ACINO_NCCL(g_nccl.GroupEnd());
-    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal, 1, s.scal + 4, s.delta_c, 6 * C, s.lm, prm);
+    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal, 1, s.scal + 4, s.delta_c, 6 * C, s.lm, prm, nullptr, 0ull);
     s.launches += 3;
   } else {
-    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm);
+    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm, nullptr, 0ull);
     ++s.launches;
   }
   ACINO_CUDA(cudaGetLastError());
@@ -340,6 +424,10 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
         ACINO_CUDA(cudaMemcpyAsync(s.lm, s.h_lm, sizeof(SchurLm), cudaMemcpyHostToDevice, h->stream));
         continue;
       }
+    }
+    if (s.h_lm->status == 7) {
+      set_error("peer exchange timed out: a rank of the communicator never delivered its partial sums");
+      return ACINO_ENCCL;
     }
     if (s.h_lm->status != 0 && !o->force_iters) break;
   }
@@ -517,7 +605,16 @@ int acino_sba_comm_init(acino_sba_t* h, const void* id128, int rank, int nranks)
   if (nranks > 1) ACINO_NCCL(g_nccl.CommInitRank(&h->nccl_comm, nranks, id, rank));
   h->rank = rank;
   h->nranks = nranks;
+  if (nranks > 1) {
+    rc = xchg_setup(h);
+    if (rc) return rc;
+  }
   return ACINO_OK;
+}
+
+int acino_sba_comm_mode(acino_sba_t* h) {
+  H_CHECK(h);
+  return h->nranks <= 1 ? 0 : (h->xchg.enabled ? 2 : 1);
 }
 
 int acino_fp64_peak(double* tflops) {

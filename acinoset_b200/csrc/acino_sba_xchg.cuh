@@ -1,0 +1,135 @@
+// acino_sba_xchg.cuh — the two small all-reduces of one LM iteration over NVLink peer memory instead of NCCL.
+//
+// per iteration every rank contributes its partial reduced camera system (848 doubles at 6 cameras,
+// + 2 maxima) and later 3 trial scalars. Both payloads are a few KB, so the cost of a collective is pure latency:
+// an NCCL group launch costs about 40 us per collective on 8 GPUs, 10 % of the iteration. Here each rank owns an
+// exchange buffer (cudaMalloc, exported with cudaIpcGetMemHandle, mapped by every peer at comm_init). A rank WRITES
+// its vector straight into its slot of every peer's buffer (stores over NVLink / NVSwitch), fences, and stores a
+// sequence number into its flag on that peer. The consumer kernels (K5 for the camera system, K7 for the trial scalars)
+// spin on their LOCAL flags until every rank's sequence number has arrived and then add the slots in rank order - the
+// same order on every rank, so all ranks hold bit-identical sums and take identical decisions without a broadcast.
+// The reduction is thus fused into the kernel that needs the result; nothing but the pushing kernel is launched.
+//
+// Slots are double buffered by the parity of the sequence number. A rank can start collective n+1 while a peer still
+// reads collective n (other parity), and cannot start n+2 before that peer has pushed n+1, which the peer does only
+// after its reading kernel of n has finished (stream order): two parities are enough.
+//
+// Layout of one rank's buffer (R ranks, LEN = rcs_len(C)):
+//   u64 flagA[16], u64 flagB[16]                       sequence numbers written by the peers
+//   double A[2][R*LEN + R*2]                           per parity: rcs[R][LEN] then maxima[R][2]
+//   double B[2][R*4]                                   per parity: rows [trial cost, predicted reduction, max |dX|, 0]
+#pragma once
+#include "acino_common.cuh"
+
+namespace acino {
+
+#define XCHG_MAX_RANKS 16
+
+struct XchgDev {
+  unsigned char* base[XCHG_MAX_RANKS];   // base[r]: rank r's exchange buffer as mapped into this process (base[rank]: own)
+  int rank, nranks, len;
+};
+
+// host side of one handle's exchange (acino_sba_comm_init sets it up, comm_destroy tears it down)
+struct PeerXchg {
+  bool enabled = false;
+  XchgDev dev{};
+  void* local = nullptr;                       // this rank's buffer (cudaMalloc)
+  void* mapped[XCHG_MAX_RANKS] = {};           // peers' buffers opened with cudaIpcOpenMemHandle (nullptr for the own rank)
+  unsigned long long seq_a = 0, seq_b = 0;     // collectives issued so far (all ranks issue the same sequence)
+};
+
+__host__ __device__ inline size_t xchg_a_doubles(int R, int len) { return (size_t)R * len + (size_t)R * 2; }
+__host__ __device__ inline size_t xchg_bytes(int R, int len) {
+  return 2 * XCHG_MAX_RANKS * 8 + 2 * xchg_a_doubles(R, len) * 8 + 2 * (size_t)R * 4 * 8;
+}
+__host__ __device__ inline unsigned long long* xchg_flags(unsigned char* b, int which) {
+  return reinterpret_cast<unsigned long long*>(b) + which * XCHG_MAX_RANKS;
+}
+__host__ __device__ inline double* xchg_slot_a(unsigned char* b, int R, int len, int parity) {
+  return reinterpret_cast<double*>(b + 2 * XCHG_MAX_RANKS * 8) + parity * xchg_a_doubles(R, len);
+}
+__host__ __device__ inline double* xchg_slot_b(unsigned char* b, int R, int len, int parity) {
+  return reinterpret_cast<double*>(b + 2 * XCHG_MAX_RANKS * 8) + 2 * xchg_a_doubles(R, len) + (size_t)parity * R * 4;
+}
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Thread `t` < n waits until flags[t] >= seq. Returns false after 10 s (a peer died): the caller marks the solve failed
+// instead of hanging the GPU. Call from all threads of the CTA and follow with __syncthreads().
+__device__ __forceinline__ bool xchg_wait(const unsigned long long* flags, int n, unsigned long long seq, int t) {
+  bool ok = true;
+  if (t < n) {
+    const unsigned long long t0 = global_timer_ns();
+    while (ld_acquire_sys(flags + t) < seq) {
+      if (global_timer_ns() - t0 > 10000000000ull) { ok = false; break; }
+    }
+  }
+  return ok;
+}
+
+// Collective A, producer side: CTA b writes this rank's folded camera system (len doubles) and its two maxima into
+// slot [rank] of peer b (b == rank: the own buffer), then publishes sequence number seq on that peer.
+__global__ void __launch_bounds__(256)
+xchg_push_rcs_kernel(XchgDev x, const double* __restrict__ rcs, const double* __restrict__ mx, unsigned long long seq) {
+  unsigned char* dst_base = x.base[blockIdx.x];
+  double* slot = xchg_slot_a(dst_base, x.nranks, x.len, (int)(seq & 1));
+  double* d_rcs = slot + (size_t)x.rank * x.len;
+  double* d_mx = slot + (size_t)x.nranks * x.len + 2 * x.rank;
+  for (int i = threadIdx.x; i < x.len; i += blockDim.x) d_rcs[i] = rcs[i];
+  if (threadIdx.x < 2) d_mx[threadIdx.x] = mx[threadIdx.x];
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) st_release_sys(xchg_flags(dst_base, 0) + x.rank, seq);
+}
+
+// Collective B, producer side (one CTA): fold the back-substitution kernel's per-CTA partials
+// [trial cost, predicted reduction, max |dX|, 0] in a fixed order, write the row into slot [rank] of every peer and
+// publish seq there.
+__global__ void __launch_bounds__(256)
+xchg_push_scal_kernel(XchgDev x, const double* __restrict__ scal_partial, int n_partial, unsigned long long seq) {
+  __shared__ double red[3][8];
+  __shared__ double row[4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double a = 0.0, b = 0.0, c = 0.0;
+  for (int i = tid; i < n_partial; i += blockDim.x) {
+    a += scal_partial[4 * i];
+    b += scal_partial[4 * i + 1];
+    c = fmax(c, scal_partial[4 * i + 2]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+    c = fmax(c, __shfl_xor_sync(0xffffffffu, c, o));
+  }
+  if (lane == 0) { red[0][warp] = a; red[1][warp] = b; red[2][warp] = c; }
+  __syncthreads();
+  if (tid == 0) {
+    a = 0.0; b = 0.0; c = 0.0;
+    for (int w = 0; w < 8; ++w) { a += red[0][w]; b += red[1][w]; c = fmax(c, red[2][w]); }
+    row[0] = a; row[1] = b; row[2] = c; row[3] = 0.0;
+  }
+  __syncthreads();
+  if (tid < x.nranks) {
+    unsigned char* dst_base = x.base[tid];
+    double* d = xchg_slot_b(dst_base, x.nranks, x.len, (int)(seq & 1)) + 4 * x.rank;
+    d[0] = row[0]; d[1] = row[1]; d[2] = row[2]; d[3] = row[3];
+    __threadfence_system();
+    st_release_sys(xchg_flags(dst_base, 1) + x.rank, seq);
+  }
+}
+
+}  // namespace acino

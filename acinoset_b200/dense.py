@@ -181,6 +181,13 @@ class SbaSolver:
         buf = ct.create_string_buffer(unique_id, 128)
         _capi.check(_capi.lib().acino_sba_comm_init(self._h, buf, rank, nranks))
 
+    def comm_mode(self) -> str:
+        """How the per-iteration all-reduces travel: 'single', 'nccl' or 'peer' (NVLink peer-memory exchange)."""
+        m = _capi.lib().acino_sba_comm_mode(self._h)
+        if m < 0:
+            _capi.check(m)
+        return ('single', 'nccl', 'peer')[m]
+
 
 def nccl_unique_id() -> bytes:
     buf = ct.create_string_buffer(128)

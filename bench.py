@@ -194,6 +194,7 @@ def native_arm(args):
         uid = [dense.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         solver.comm_init(uid[0], rank, world)
+    comm_mode = solver.comm_mode()
 
     m = _capi.MODE_POINTS_AND_EXTRINSICS if mode == 'extrinsics' else _capi.MODE_POINTS_ONLY
     # full solve from the TRI initialisation (solve ms, iterations to converge); at N > 1 the ranks enter together and the
@@ -237,7 +238,7 @@ def native_arm(args):
         build_bytes = P * 1 + n_pts * 24 + n_obs * 16
         back_bytes = build_bytes + n_pts * 24
         kern = dict(name=f'schur_build_kernel<{C}>', ms_per_launch=pr['build_ms'], bytes_per_launch=build_bytes,
-                    launches_per_step=5 if world == 1 else 8, backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes,
+                    launches_per_step=5 if world == 1 else (7 if comm_mode == 'peer' else 8), collective=comm_mode, backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes,
                     profiled_iterations=pr['iterations'])
     fp64_peak = dense.fp64_peak_tflops()
     if world > 1:
@@ -432,7 +433,9 @@ def main():
                 config=dict(workload=f'{"C4" if args.frames == C4_FRAMES else "custom"} {"points+extrinsics (Schur)" if mode == "extrinsics" else "points-only"} SBA: '
                                      f'{args.frames} frames x 20 keypoints x 6 cameras per GPU, dlc_thresh 0.5, 1 px noise',
                             masked_frac=args.masked_frac, outlier_frac=args.outlier_frac, mode=mode, points_per_gpu=n_pts, observations_per_gpu=n_obs,
-                            l2='inputs larger than L2 (229 MB of observations per GPU vs 126 MB L2)', parallelism=f'frame-shard x{world}'),
+                            l2='inputs larger than L2 (229 MB of observations per GPU vs 126 MB L2)', parallelism=f'frame-shard x{world}',
+                            collective={'single': 'none (one GPU)', 'nccl': 'NCCL all-reduce, 2 grouped launches per iteration',
+                                        'peer': 'NVLink peer-memory exchange fused into K5 / K7 (csrc/acino_sba_xchg.cuh)'}[(ctx['kern'] or {}).get('collective', 'single')]),
                 clocks=ctx['clk'], e2e=e2e, gpu_launches=launches, roofline=roofline, cpu_baseline=cb,
                 solve=dict(ms=st['solve_ms'], iterations=st['iterations'], launches=st['launches'], cost_initial=st['cost_initial'],
                            cost_final=st['cost_final'], n_unconverged=st['n_unconverged']),

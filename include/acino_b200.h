@@ -133,7 +133,7 @@ typedef struct {
   int32_t launches;        /* CUDA kernel launches issued by the solve */
   double cost_initial, cost_final;   /* scipy-convention robust cost */
   double solve_ms;         /* device time of the solve (CUDA events) */
-  double status;           /* points+extrinsics exit reason: 1 gtol, 2 ftol, 3 xtol, 4 stalled, 0 max_iter */
+  double status;           /* points+extrinsics exit reason: 1 gtol, 2 ftol, 3 xtol, 4 stalled, 0 max_iter (7: peer exchange timed out, the solve returns an error) */
   double n_accept;         /* accepted LM steps */
   double lambda_final;     /* Marquardt damping at exit */
   double gmax;             /* max |gradient| at the last linearisation */
@@ -168,11 +168,16 @@ int acino_sba_profile_read(acino_sba_t* h, double* build_ms, double* backsub_ms,
  * the last accepted step, [13]=rejected, [14]=Cholesky failures, [15]=cost at the first linearisation */
 int acino_sba_lm_state(acino_sba_t* h, double* out16);
 
-/* multi-GPU (frame-sharded) — one handle per rank; NCCL is dlopen'ed from the process (libnccl.so.2). Every rank
- * calls solve / iterate collectively; the reduced camera system (6C x 6C + gradient + cost) is all-reduced once per LM
- * iteration and the trial cost once more, each a single grouped NCCL launch. */
+/* multi-GPU (frame-sharded) — one handle per rank (one process per GPU); NCCL is dlopen'ed from the process
+ * (libnccl.so.2). Every rank calls solve / iterate collectively; the reduced camera system (6C x 6C + gradient + cost)
+ * is all-reduced once per LM iteration and the trial scalars once more. comm_init also maps a small exchange buffer of
+ * every peer (CUDA IPC over NVLink): when that succeeds on all ranks the two all-reduces are done by the kernels
+ * themselves (each rank stores its partial sums into every peer's buffer, the consuming kernel waits for all ranks and
+ * adds the rows in rank order; csrc/acino_sba_xchg.cuh), otherwise by one grouped NCCL launch each. ACINO_P2P=0 in the
+ * environment forces the NCCL path. acino_sba_comm_mode: 0 single rank, 1 NCCL all-reduce, 2 peer-memory exchange. */
 int acino_nccl_unique_id(void* id128);
 int acino_sba_comm_init(acino_sba_t* h, const void* id128, int rank, int nranks);
+int acino_sba_comm_mode(acino_sba_t* h);
 
 /* fp64 FMA throughput of the device (dependent-chain-free DFMA microbenchmark), TFLOP/s: the second roofline
  * denominator bench.py reports next to the measured HBM bandwidth. */

@@ -39,6 +39,7 @@ if rank == 0:
     for c in allc[1:]:
         ok &= bool(np.array_equal(c, allc[0]))             # every rank took identical decisions
     print('cameras identical on all ranks:', ok)
+    print('collective:', pipe.solver.comm_mode())
     full = dense.solve_scene_host(sc['uv'], sc['lik'], 0.5, k, d, r, t, mode=_capi.MODE_POINTS_AND_EXTRINSICS, rvec_t0=(rv, tv), **opts)
     s1 = dense.SbaSolver  # noqa
     print(f"sharded: cost {st['cost_final']:.12e} it {st['iterations']} | single: cost {full['cost_final']:.12e} it {full['iterations']}")
