@@ -27,6 +27,7 @@ struct acino_sba {
   acino::SchurState schur;
   void* nccl_comm = nullptr;
   int rank = 0, nranks = 1;
+  double* schur_barrier_buf = nullptr;   // device, 2 doubles: payload of the tear-down barrier
   acino::PeerXchg xchg;              // NVLink peer-memory exchange for the per-iteration all-reduces (falls back to NCCL)
 };
 
@@ -232,6 +233,7 @@ acino_sba_t* acino_sba_create(int n_cams, int64_t n_points) {
 void acino_sba_destroy(acino_sba_t* h) {
   if (!h) return;
   acino::comm_destroy(h);
+  cudaFree(h->schur_barrier_buf);
   schur_free(h->schur);
   cudaFree(h->cams); cudaFree(h->rvec_t); cudaFree(h->uv_own); cudaFree(h->mask_own);
   cudaFree(h->X); cudaFree(h->X0); cudaFree(h->lam); cudaFree(h->cost_p); cudaFree(h->status); cudaFree(h->order);

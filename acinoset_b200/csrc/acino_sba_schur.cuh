@@ -538,16 +538,17 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   __shared__ double rhs_diag;
   __shared__ int fail;
   const int tid = threadIdx.x;
-  if (lm->status != 0 && !prm.force) return;
   if (wait_flags) {
     // peer exchange (acino_sba_xchg.cuh): partial / maxp are this rank's slots, one row per rank, written by the peers
-    // over NVLink; wait for every rank's sequence number, then add the rows in rank order (the same on every rank)
+    // over NVLink; wait for every rank's sequence number, then add the rows in rank order (the same on every rank).
+    // The wait comes before the early return: every push is consumed, which is what makes two slot parities enough.
     const bool ok = xchg_wait(wait_flags, n_partial, wait_seq, tid);
     if (__syncthreads_or(!ok)) {
       if (tid == 0) lm->status = 7;      // a peer never arrived: fail the solve instead of hanging
       return;
     }
   }
+  if (lm->status != 0 && !prm.force) return;
   for (int i = tid; i < LEN; i += blockDim.x) {
     // fixed summation order (four interleaved chains, then a fixed combine): deterministic, and the loads overlap.
     // ld.cg: the rows may have been written by another GPU, L1 must not answer
@@ -853,14 +854,14 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
                     const unsigned long long* wait_flags, unsigned long long wait_seq) {
   __shared__ double red[3][8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (lm->status != 0 && !prm.force) return;
-  if (wait_flags) {      // peer exchange: scal holds one row per rank, written by the peers
+  if (wait_flags) {      // peer exchange: scal holds one row per rank, written by the peers (waited for even when idle)
     const bool ok = xchg_wait(wait_flags, n_scal, wait_seq, tid);
     if (__syncthreads_or(!ok)) {
       if (tid == 0) lm->status = 7;
       return;
     }
   }
+  if (lm->status != 0 && !prm.force) return;
   double a = 0, b = 0, c = 0;
   for (int i = tid; i < n_scal; i += blockDim.x) {
     a += __ldcg(scal + 4 * i); b += __ldcg(scal + 4 * i + 1);

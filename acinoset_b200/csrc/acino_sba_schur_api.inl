@@ -55,11 +55,37 @@ static int nccl_load() {
     }                                                                                                      \
   } while (0)
 
-static void xchg_destroy(acino_sba* h) {
+// All ranks meet on the stream (a one-element NCCL all-reduce) and the host waits for it, at most timeout_ms: what a
+// rank enqueued before the barrier (its stores into the peers' buffers) has completed on every rank when it returns true.
+static bool xchg_barrier(acino_sba* h, int timeout_ms) {
+  if (!h->nccl_comm || !h->schur_barrier_buf) return false;
+  if (g_nccl.AllReduce(h->schur_barrier_buf, h->schur_barrier_buf, 1, kNcclDouble, kNcclSum, h->nccl_comm, h->stream) != 0) return false;
+  const auto t0 = std::chrono::steady_clock::now();
+  for (;;) {
+    const cudaError_t q = cudaStreamQuery(h->stream);
+    if (q == cudaSuccess) return true;
+    if (q != cudaErrorNotReady) { cudaGetLastError(); return false; }
+    if (std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() > timeout_ms) return false;
+  }
+}
+
+// Tear-down is collective, like the communicator's: nobody unmaps or frees while a peer may still store into the buffer
+// (barrier 1), and nobody frees an exported buffer before every importer has unmapped it (barrier 2; CUDA leaves the
+// other order undefined). If a peer is gone the barrier times out and the buffers are left to process exit.
+static void xchg_destroy(acino_sba* h, bool collective) {
   PeerXchg& x = h->xchg;
-  for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
-    if (x.mapped[r]) cudaIpcCloseMemHandle(x.mapped[r]);
-    x.mapped[r] = nullptr;
+  if (collective) {
+    if (!xchg_barrier(h, 5000)) { x = PeerXchg(); return; }
+    for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
+      if (x.mapped[r]) cudaIpcCloseMemHandle(x.mapped[r]);
+      x.mapped[r] = nullptr;
+    }
+    if (!xchg_barrier(h, 5000)) { x = PeerXchg(); return; }
+  } else {
+    for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
+      if (x.mapped[r]) cudaIpcCloseMemHandle(x.mapped[r]);
+      x.mapped[r] = nullptr;
+    }
   }
   if (x.local) cudaFree(x.local);
   x = PeerXchg();
@@ -74,6 +100,10 @@ static int xchg_setup(acino_sba* h) {
   const char* env = getenv("ACINO_P2P");
   double ok = (R <= XCHG_MAX_RANKS && !(env && env[0] == '0') && g_nccl.AllGather) ? 1.0 : 0.0;
   const size_t bytes = xchg_bytes(R, len);
+  if (!h->schur_barrier_buf) {
+    ACINO_CUDA(cudaMalloc(&h->schur_barrier_buf, 2 * sizeof(double)));
+    ACINO_CUDA(cudaMemset(h->schur_barrier_buf, 0, 2 * sizeof(double)));
+  }
   cudaIpcMemHandle_t mine;
   memset(&mine, 0, sizeof(mine));
   if (ok != 0.0) {
@@ -106,7 +136,7 @@ static int xchg_setup(acino_sba* h) {
   double sum = 0.0;
   ACINO_CUDA(cudaMemcpyAsync(&sum, vb.as<double>(), sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   ACINO_CUDA(cudaStreamSynchronize(h->stream));
-  if (sum != (double)R) { xchg_destroy(h); return ACINO_OK; }
+  if (sum != (double)R) { xchg_destroy(h, true); return ACINO_OK; }      // every rank is here: collective tear-down
   x.dev.rank = h->rank;
   x.dev.nranks = R;
   x.dev.len = len;
@@ -115,7 +145,7 @@ static int xchg_setup(acino_sba* h) {
 }
 
 static void comm_destroy(acino_sba* h) {
-  xchg_destroy(h);
+  xchg_destroy(h, h->xchg.enabled);
   if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
   h->nccl_comm = nullptr;
 }
