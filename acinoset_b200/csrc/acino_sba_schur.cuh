@@ -398,6 +398,13 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
     if (tid == 0) next_unit[0] = 0;
     cp_async_wait_all();        // the unit lists and the next tile's points / observation list have landed
     __syncthreads();
+    if (tile + gridDim.x < n_tiles) {
+      // the next tile's observations towards L2 (its list has landed: the count is known), so that phase 1b of the next
+      // tile does not start with a full DRAM latency in every round
+      const int n_next = olbuf[(buf ^ 1) * OB];
+      const char* nx = reinterpret_cast<const char*>(uvc + (size_t)(tile + gridDim.x) * (C * BT));
+      for (int i = tid * 128; i < n_next * 16; i += BT * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + i));
+    }
     // ---------------- phase 2: warps take units (longest first: diagonal units lead) until none is left
     for (;;) {
       int u = 0;
