@@ -418,6 +418,8 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
   // fixed, and the ftol / stall rules may end the solve only on a step that directly follows such a polish.
   const bool polish = o->polish_tol > 0.0 && prm.refine > 0 && !o->force_iters;
   int last_polish = -1000;
+  double F_end_polish = -1.0;     // cost when the ftol / stall rule last led to a polish instead of ending the solve
+  bool terminal_polish = false;   // the polish followed an accepted step that gained <= ftol: what comes next decides
   const bool trace = getenv("ACINO_TRACE") != nullptr;
   auto t_prev = std::chrono::steady_clock::now();
   if (trace) {
@@ -438,9 +440,25 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
       t_prev = t;
     }
     if (polish) {
-      const bool ended = (s.h_lm->status == 2 || s.h_lm->status == 4) && it - last_polish > 1;
+      // relative cost changes below 1e-12 are the rounding of the cost sums (10^5 .. 10^7 terms), whatever ftol asks for
+      const double ftol_eff = fmax(o->ftol, 1e-12), ftol_abs = ftol_eff * s.h_lm->F;
+      if (terminal_polish && s.h_lm->status == 0 && it == last_polish + 1 &&
+          !(s.h_lm->last_accept && s.h_lm->last_rel_dec > ftol_eff)) {
+        // the points were polished after a step that gained <= ftol, and the joint step from the polished points gains
+        // nothing either: converged (ftol). Without this rule the damping first has to run up through a series of
+        // rejected steps whose cost differences are rounding noise.
+        s.h_lm->status = 2;
+        ACINO_CUDA(cudaMemcpyAsync(s.lm, s.h_lm, sizeof(SchurLm), cudaMemcpyHostToDevice, h->stream));
+      }
+      terminal_polish = false;     // only the iteration right after the polish counts
+      bool ended = (s.h_lm->status == 2 || s.h_lm->status == 4) && it - last_polish > 1;
+      // a second end without any gain since the polish of the first one is the end (otherwise polish -> rejected steps ->
+      // end rule -> polish ... runs to max_iter on small scenes)
+      if (ended && F_end_polish >= 0.0 && F_end_polish - s.h_lm->F <= ftol_abs) ended = false;
       const bool creeping = s.h_lm->status == 0 && s.h_lm->last_accept && s.h_lm->last_rel_dec < o->polish_tol && it - last_polish >= 4;
       if (ended || creeping) {
+        if (ended) F_end_polish = s.h_lm->F;
+        terminal_polish = creeping && s.h_lm->last_rel_dec <= ftol_eff;
         const int l0 = s.launches;
         rc = schur_polish_points(h, prm, 12);
         if (rc) return rc;
