@@ -178,6 +178,28 @@ def test_polishing_reaches_the_same_minimum_in_fewer_iterations():
     s.close()
 
 
+def test_board_calibration_ends_by_a_stopping_rule():
+    """Config C2 in small: a checkerboard scene converges within a few tens of joint iterations, and the
+    solve has to END there by one of scipy's rules. (Polishing used to reset the ftol / stall status each time it ran,
+    so that on small scenes polish -> rejected steps -> polish cycled until max_iter.)"""
+    b = synth.make_board_scene(60, seed=3)
+    p2, p3, pi, ci = sba.prepare_calib_board_data_for_bundle_adjustment(b['img_pts_arr'], b['fnames_arr'], (9, 6), b['k'], b['d'],
+                                                                        b['r0'], b['t0'], calib.triangulate_points_fisheye)
+    obj, r1, t1, res = sba.bundle_adjust_points_and_extrinsics(p2, p3, pi, ci, b['k'], b['d'], b['r0'].copy(), b['t0'].copy(),
+                                                               calib.project_points_fisheye)
+    st = sba.bundle_adjust_points_and_extrinsics.last_stats
+    assert st['status'] in (1.0, 2.0, 3.0, 4.0), st
+    assert st['iterations'] < 80, st
+    rmse0, rmse1 = np.sqrt(np.mean(res['before'] ** 2)), np.sqrt(np.mean(res['after'] ** 2))
+    assert rmse1 < rmse0 and rmse1 < 0.35          # 0.3 px pixel noise: the solve reaches the noise floor
+    # the reference's own ftol ends no later, at a cost that is the same to 1e-8
+    obj2, r2, t2, res2 = sba.bundle_adjust_points_and_extrinsics(p2, p3, pi, ci, b['k'], b['d'], b['r0'].copy(), b['t0'].copy(),
+                                                                 calib.project_points_fisheye, ftol=1e-10)
+    st2 = sba.bundle_adjust_points_and_extrinsics.last_stats
+    assert st2['status'] in (1.0, 2.0, 3.0, 4.0) and st2['iterations'] <= st['iterations']
+    assert abs(st2['cost_final'] - st['cost_final']) <= 1e-8 * st['cost_final']
+
+
 def test_point_order_does_not_change_results():
     """K3 visits the points sorted by observation count (point_order_kernel); every point is still solved by the same
     arithmetic, so a scene and its frame-reversed copy give bit-identical points, also when P is not a multiple of the
