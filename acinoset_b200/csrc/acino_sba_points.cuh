@@ -126,6 +126,12 @@ struct LmPointsCtl {
   const int* cur;
   const double* cams_alt;
   double* X_alt;
+  // polishing: visit only the points of `list` (n_list entries) instead of all P, and append the points that are still
+  // active at exit to `list_out` (cursor counters[1], at most list_cap entries) for the next launch
+  const unsigned* list;
+  int n_list;
+  unsigned* list_out;
+  int list_cap;
 };
 
 // Visiting order of K3: within tiles of ORDER_TILE points, the points sorted by their number of observations
@@ -186,7 +192,8 @@ lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs
   for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[(i / CAM_STRIDE) * K3_CAM_STRIDE + i % CAM_STRIDE] = cams[i];
   __syncthreads();
   int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (order && p < P) p = (p & ~(int64_t)(ORDER_TILE - 1)) + order[p];     // tile-local offsets
+  if (ctl.list) p = (p < ctl.n_list) ? (int64_t)ctl.list[p] : P;
+  else if (order && p < P) p = (p & ~(int64_t)(ORDER_TILE - 1)) + order[p];     // tile-local offsets
   double2* uvr = s_uv + threadIdx.x;
   unsigned still = 0;
   if (p < P) {
@@ -242,8 +249,16 @@ lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs
       still = (st == ST_ACTIVE);
     }
   }
-  unsigned cnt = __popc(__ballot_sync(0xffffffffu, still));
+  const unsigned bal = __ballot_sync(0xffffffffu, still);
+  const unsigned cnt = __popc(bal);
   if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&counters[0], (unsigned long long)cnt);
+  if (ctl.list_out && cnt) {      // warp-aggregated append (the order of the list does not matter: points are independent)
+    unsigned long long base = 0;
+    if ((threadIdx.x & 31) == 0) base = atomicAdd(&counters[1], (unsigned long long)cnt);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    const unsigned long long pos = base + __popc(bal & ((1u << (threadIdx.x & 31)) - 1u));
+    if (still && pos < (unsigned long long)ctl.list_cap) ctl.list_out[pos] = (unsigned)p;
+  }
 }
 
 // deterministic two-stage sum of a double array (scene cost)

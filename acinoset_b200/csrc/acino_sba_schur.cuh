@@ -996,6 +996,8 @@ struct SchurState {
   SchurLm* h_lm = nullptr;
   unsigned short* unit_lists = nullptr;    // [tile][unit][BT]
   unsigned short* unit_counts = nullptr;   // [tile][NUP]
+  static constexpr int POLISH_CAP = 1 << 18;
+  unsigned* polish_list[2] = {nullptr, nullptr};   // still-active points of the previous / this polish launch
   unsigned short* obs_lists = nullptr;     // [tile][8 + C*BT]
   unsigned short* pt_start = nullptr;      // [tile][BT] first observation of each point in its tile's list
   unsigned short* pt_rank = nullptr;       // [tile][BT] rank of each point among the existing points of its tile
