@@ -2,7 +2,7 @@
 (/root/reference/src/lib/{calib,utils,sba}.py, unmodified, loaded through oracle/ref_shim.py)
 on seeded synthetic inputs. Run in the build container only:
 
-    python -m oracle.make_golden [camera|c1|calib|all]
+    python -m oracle.make_golden [camera|c1|c5small|calib|metric|project2d|all]
 
 Versions of record for the un-pinned third-party numerics: see the 'versions' entry stored in
 every fixture (OpenCV / scipy / numpy / pandas of the build image).
@@ -112,6 +112,46 @@ def gen_c1():
     print(f'c1: {len(points_3d)} points, {len(pidx)} obs, tri {t_tri:.2f}s sba {t_sba:.2f}s')
 
 
+def c5small_inputs():
+    from acinoset_b200 import synth
+    rig = synth.load_rig(os.path.join(GOLD, 'scene_6cam.json'))
+    # config C5 in small: 30 % of the slots below the threshold, 5 % of the observations with N(0, 50 px)
+    # outlier noise on top of N(0, 1 px), seed 5
+    sc = synth.make_rig_scene(60, 20, seed=5, masked_frac=0.3, outlier_frac=0.05, rig=rig)
+    df = synth.dense_to_df(sc['uv'], sc['lik'], 20, first_frame=0)
+    return sc, df
+
+
+def gen_c5small():
+    """Config C5 in small: TRI + points-only SBA through the reference's own functions on a scene with gross outliers,
+    where the Cauchy loss (f_scale 50) actually bends: pins the robust objective, not only the least-squares one."""
+    calib, utils, sba = ref_shim.load()
+    sc, df = c5small_inputs()
+    k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
+    df_t = df.query('likelihood > 0.5')
+    t0 = time.time()
+    with ref_shim.quiet():
+        p3 = utils.get_pairwise_3d_points_from_df(df_t, k, d.reshape((-1, 4)), r, t, calib.triangulate_points_fisheye)
+    t_tri = time.time() - t0
+    p3[['x', 'y', 'z']] = p3[['x', 'y', 'z']].astype(np.float64)
+    p3['point_index'] = p3.index
+    points_3d = np.array(p3[['x', 'y', 'z']], dtype=np.float64)
+    pdf = df_t.merge(p3, how='inner', on=['frame', 'marker'], suffixes=('_cam', ''))
+    points_2d = np.array(pdf[['x_cam', 'y_cam']], dtype=np.float64)
+    pidx = np.array(pdf['point_index']).astype(np.int64)
+    cidx = np.array(pdf['camera']).astype(np.int64)
+    t0 = time.time()
+    with ref_shim.quiet():
+        obj, res = sba.bundle_adjust_points_only(points_2d, points_3d, pidx, cidx, k, d, r, t,
+                                                 calib.project_points_fisheye, f_scale=50)
+    t_sba = time.time() - t0
+    np.savez_compressed(os.path.join(GOLD, 'golden_c5small.npz'),
+                        frame=np.array(p3['frame']).astype(np.int64), marker=np.array(p3['marker']).astype(str),
+                        points_3d=points_3d, points_2d=points_2d, point_indices=pidx, camera_indices=cidx,
+                        f_before=res['before'], f_after=res['after'], obj_pts=obj, t_tri=t_tri, t_sba=t_sba, versions=_versions())
+    print(f'c5small: {len(points_3d)} points, {len(pidx)} obs, tri {t_tri:.2f}s sba {t_sba:.2f}s')
+
+
 def gen_metric():
     """a12: the reference's own metric.residual_error (src/lib/metric.py:36-101) on config C1 (thresholded 2-D frame vs the
     reference's triangulated points)."""
@@ -186,6 +226,8 @@ def main():
         gen_camera()
     if what in ('c1', 'all'):
         gen_c1()
+    if what in ('c5small', 'all'):
+        gen_c5small()
     if what in ('calib', 'all'):
         from .make_golden_calib import gen_calib
         gen_calib()

@@ -66,6 +66,26 @@ def test_ring_triangulation_restatement_c1(gc1):
     assert np.abs(xyz[exists][order] - gc1['points_3d']).max() < 1e-10
 
 
+def test_restatements_on_the_outlier_scene(rig, golden_dir):
+    """Config C5 in small (30 % of the slots masked, 5 % gross outliers; golden_c5small.npz from the real reference):
+    the dense-slot triangulation reproduces the reference's rows and values, and the residual restatement its vector -
+    also where undistortion fails or residuals are hundreds of pixels."""
+    g = np.load(os.path.join(golden_dir, 'golden_c5small.npz'))
+    k, d, r, t, _ = rig
+    sc = synth.make_rig_scene(60, 20, seed=5, masked_frac=0.3, outlier_frac=0.05)
+    xyz, exists, mask = oracle.ring_triangulate_dense(sc['uv'], sc['lik'], 0.5, sc['k'], sc['d'], sc['r'], sc['t'])
+    frames = np.repeat(np.arange(60), 20)
+    markers = np.tile(np.array(synth.MARKERS), 60)
+    order = np.lexsort((markers[exists], frames[exists]))
+    assert (frames[exists][order] == g['frame']).all()
+    assert (markers[exists][order] == g['marker']).all()
+    assert np.abs(xyz[exists][order] - g['points_3d']).max() < 1e-9
+    f = oracle.residuals_points_only(g['points_3d'].ravel(), len(g['points_3d']), g['point_indices'], g['camera_indices'],
+                                     k, d, r, t, g['points_2d'])
+    assert _rel(f, g['f_before']).max() < 1e-10
+    assert np.abs(g['f_before']).max() > 100.0          # the scene does contain gross outliers
+
+
 def test_residual_restatement_c1(rig, gc1):
     k, d, r, t, _ = rig
     n = len(gc1['points_3d'])
