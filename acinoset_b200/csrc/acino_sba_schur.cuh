@@ -133,27 +133,87 @@ __device__ __forceinline__ void warp_reduce_scatter40(double (&a)[RCS_UNIT], int
   }
 }
 
+// ---- existing points, compacted ------------------------------------------------------------------------------
+// Only (frame, keypoint) slot groups with a non-empty observation mask are points of the problem (72 % of them at 50 %
+// masking). K4 / K6 tile the EXISTING points: pid[g] = index of the g-th existing point (increasing), cmask[g] its mask,
+// so that a tile of BT points is BT points of work: 28 % fewer tiles, barriers, unit claims and warp reductions at C4,
+// and longer camera-pair lists per tile (fuller last rounds). Three small kernels, once per solve: per-block counts,
+// a single-block scan of the counts, scatter.
+#define EXIST_TB 1024
+__global__ void __launch_bounds__(EXIST_TB)
+exist_count_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned* __restrict__ block_counts) {
+  const int64_t p = (int64_t)blockIdx.x * EXIST_TB + threadIdx.x;
+  const int n = __syncthreads_count(p < P && obs_mask[p] != 0);
+  if (threadIdx.x == 0) block_counts[blockIdx.x] = (unsigned)n;
+}
+
+// in place: block_counts[i] <- sum of the counts before block i; total[0] <- number of existing points
+__global__ void __launch_bounds__(EXIST_TB)
+exist_scan_kernel(unsigned* __restrict__ block_counts, int n_blocks, unsigned long long* __restrict__ total) {
+  __shared__ unsigned wsum[EXIST_TB / 32];
+  __shared__ unsigned long long carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) carry = 0ull;
+  __syncthreads();
+  for (int base = 0; base < n_blocks; base += EXIST_TB) {
+    const int i = base + tid;
+    const unsigned v = i < n_blocks ? block_counts[i] : 0u;
+    unsigned incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    unsigned before = 0;
+    for (int w = 0; w < warp; ++w) before += wsum[w];
+    const unsigned long long c0 = carry;
+    if (i < n_blocks) block_counts[i] = (unsigned)(c0 + before + incl - v);
+    __syncthreads();
+    if (tid == EXIST_TB - 1) carry = c0 + before + incl;
+    __syncthreads();
+  }
+  if (tid == 0) total[0] = carry;
+}
+
+__global__ void __launch_bounds__(EXIST_TB)
+exist_scatter_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, const unsigned* __restrict__ block_offsets,
+                     unsigned* __restrict__ pid, uint8_t* __restrict__ cmask) {
+  __shared__ unsigned wsum[EXIST_TB / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t p = (int64_t)blockIdx.x * EXIST_TB + tid;
+  const unsigned m = p < P ? obs_mask[p] : 0u;
+  const unsigned bal = __ballot_sync(0xffffffffu, m != 0);
+  if (lane == 0) wsum[warp] = __popc(bal);
+  __syncthreads();
+  if (m) {
+    unsigned g = block_offsets[blockIdx.x] + __popc(bal & ((1u << lane) - 1u));
+    for (int w = 0; w < warp; ++w) g += wsum[w];
+    pid[g] = (unsigned)p;
+    cmask[g] = (uint8_t)m;
+  }
+}
+
 // ---- unit lists: for every tile of BT points and every camera pair (unit), the tile-local indices of the points both
 // cameras observe, in point order. They depend on the masks only, so they are built once per solve and K4 streams
 // them in (cp.async) instead of compacting them again in every LM iteration. lists [tile][unit][BT] u16,
 // counts [tile][NUP] u16: [0, NU) the list lengths, [NU, 2 NU) the units sorted by length (longest first).
 template <int C>
 __global__ void __launch_bounds__(schur_bt(C))
-schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned short* __restrict__ lists,
-                   unsigned short* __restrict__ counts, unsigned short* __restrict__ obs_lists,
-                   unsigned short* __restrict__ pt_start, unsigned short* __restrict__ pt_rank,
+schur_lists_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict__ pid, int64_t E,
+                   unsigned short* __restrict__ lists, unsigned short* __restrict__ counts,
+                   unsigned short* __restrict__ obs_lists, unsigned short* __restrict__ pt_start,
                    const double2* __restrict__ uv, double2* __restrict__ uvc) {
   constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (2 * NU + 7) & ~7, OB = 8 + C * BT;
   __shared__ unsigned char sM[BT];
   __shared__ int wtot[NW];
-  __shared__ int wpts[NW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t tile = blockIdx.x;
-  const int64_t p = tile * BT + tid;
-  const unsigned m = (p < P) ? obs_mask[p] : 0u;
+  const int64_t g = tile * BT + tid;                 // existing point g of the compacted numbering (tile-local index tid)
+  const unsigned m = (g < E) ? cmask[g] : 0u;
+  const size_t p = (g < E) ? pid[g] : 0;
   sM[tid] = (unsigned char)m;
-  const unsigned live = __ballot_sync(0xffffffffu, m != 0);
-  if (lane == 0) wpts[warp] = __popc(live);
   {   // the tile's observations, point-major then camera: [0] = count, [8 + i] = q*8 + c
     int k = __popc(m), incl = k;
 #pragma unroll
@@ -166,17 +226,12 @@ schur_lists_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned sho
     int base = incl - k;
     for (int w = 0; w < warp; ++w) base += wtot[w];
     pt_start[(size_t)tile * BT + tid] = (unsigned short)base;
-    {   // rank of the point among the tile's existing points: where K4 leaves its per-point record for K6
-      int rk = __popc(live & ((1u << lane) - 1u));
-      for (int w = 0; w < warp; ++w) rk += wpts[w];
-      pt_rank[(size_t)tile * BT + tid] = (unsigned short)rk;
-    }
     unsigned short* ol = obs_lists + (size_t)tile * OB;
     unsigned mm = m;
     while (mm) {
       int c = __ffs(mm) - 1;
       mm &= mm - 1;
-      uvc[(size_t)tile * (C * BT) + base] = uv[(size_t)p * C + c];     // observations compacted in list order
+      uvc[(size_t)tile * (C * BT) + base] = uv[p * C + c];     // observations compacted in list order
       ol[8 + base++] = (unsigned short)(tid * 8 + c);
     }
     if (tid == BT - 1) ol[0] = (unsigned short)base;
@@ -240,14 +295,14 @@ struct SchurSmem {
 
 template <int C>
 __global__ void __launch_bounds__(schur_bt(C), schur_ctas_per_sm(C))
-schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, int64_t P,
+schur_build_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict__ pid, int64_t E, int64_t P,
                    const double* __restrict__ cams0, const double* __restrict__ cams1,
                    const double* __restrict__ X0, const double* __restrict__ X1,
                    const SchurLm* __restrict__ lm, SchurParams prm,
                    double* __restrict__ rcs_partial, double* __restrict__ max_partial,
                    const unsigned short* __restrict__ unit_lists, const unsigned short* __restrict__ unit_counts,
                    const unsigned short* __restrict__ obs_lists, double* __restrict__ stgN, double* __restrict__ stgP,
-                   const unsigned short* __restrict__ pt_rank, const double2* __restrict__ uvc) {
+                   const double2* __restrict__ uvc) {
   using L = SchurSmem<C>;
   constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN, NUP = L::NUP, OB = L::OB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -285,16 +340,22 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
 
   double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0;
   double cprod = 1.0;     // running product of (1+z_u)(1+z_v): sum of log1p(z) = log of the product
-  const int64_t n_tiles = skip ? 0 : (P + BT - 1) / BT;
-  // the first tile's points, mask and observation list; later tiles are fetched one tile ahead
+  // tiles of BT EXISTING points (compacted numbering g, pid[g] = the point's index in the scene)
+  const int64_t n_tiles = skip ? 0 : (E + BT - 1) / BT;
+  // the first tile's points, mask and observation list; later tiles are fetched one tile ahead, and the scene index of
+  // this thread's point one tile further ahead still (pid_next: the copy of the point must not wait for its index)
   unsigned m_next = 0u;
+  unsigned pid_next = 0u;
   int buf = 0;
   if ((int64_t)blockIdx.x < n_tiles) {
-    const int64_t p0 = (int64_t)blockIdx.x * BT + tid;
-    if (p0 < P) {
-      m_next = obs_mask[p0];
+    const int64_t g0 = (int64_t)blockIdx.x * BT + tid;
+    if (g0 < E) {
+      m_next = cmask[g0];
+      const size_t p0 = pid[g0];
       cp_async8(sXbuf + tid, Xp + 3 * p0); cp_async8(sXbuf + BS + tid, Xp + 3 * p0 + 1); cp_async8(sXbuf + 2 * BS + tid, Xp + 3 * p0 + 2);
     }
+    const int64_t g1 = g0 + (int64_t)gridDim.x * BT;
+    if (g1 < E) pid_next = pid[g1];
     for (int i = tid; i < OB / 8; i += BT)
       cp_async16(reinterpret_cast<char*>(olbuf) + 16 * i, reinterpret_cast<const char*>(obs_lists) + ((size_t)blockIdx.x * OB) * 2 + 16 * i);
     cp_async_wait_all();
@@ -307,15 +368,17 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
     double* sX = sXbuf + buf * 3 * BS;
     const unsigned short* olist = olbuf + buf * OB;
     const unsigned m = m_next;
-    const int rank = pt_rank[tile * BT + tid];       // used in phase 1c: the load has the whole of 1a/1b to land
     {
-      const int64_t pn = (tile + gridDim.x) * BT + tid;
+      const int64_t gn = (tile + gridDim.x) * BT + tid;
       m_next = 0u;
-      if (pn < P) {
+      if (gn < E) {
         double* sXn = sXbuf + (buf ^ 1) * 3 * BS;
-        m_next = obs_mask[pn];
+        m_next = cmask[gn];
+        const size_t pn = pid_next;
         cp_async8(sXn + tid, Xp + 3 * pn); cp_async8(sXn + BS + tid, Xp + 3 * pn + 1); cp_async8(sXn + 2 * BS + tid, Xp + 3 * pn + 2);
       }
+      const int64_t gnn = gn + (int64_t)gridDim.x * BT;
+      if (gnn < E) pid_next = pid[gnn];
       if (tile + gridDim.x < n_tiles)
         for (int i = tid; i < OB / 8; i += BT)
           cp_async16(reinterpret_cast<char*>(olbuf + (buf ^ 1) * OB) + 16 * i,
@@ -385,7 +448,7 @@ schur_build_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ o
       sH[BS + tid] = fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
       sH[2 * BS + tid] = fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
       {   // per-point blocks for K6: V^-1, h, D, g
-        const int64_t pp = tile * BT + rank;          // dense over the tile's existing points: full sectors
+        const int64_t pp = tile * BT + tid;           // = g: dense over the existing points
         const size_t PS = (size_t)P;
         stgP[pp] = iv.i00; stgP[PS + pp] = iv.i01; stgP[2 * PS + pp] = iv.i02;
         stgP[3 * PS + pp] = iv.i11; stgP[4 * PS + pp] = iv.i12; stgP[5 * PS + pp] = iv.i22;
@@ -736,14 +799,13 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
 #define SCHUR_BACKSUB_MINB 4     // 64 registers: 32 warps per SM (3 CTAs of 80 registers measured 0.180 ms, 4 of 64: 0.172 ms)
 template <int C>
 __global__ void __launch_bounds__(SCHUR_BACKSUB_TB, SCHUR_BACKSUB_MINB)
-schur_backsub_kernel(const uint8_t* __restrict__ obs_mask, int64_t P,
+schur_backsub_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict__ pid, int64_t E, int64_t P,
                             const double* __restrict__ cams0, const double* __restrict__ cams1,
                             const double* __restrict__ X0, const double* __restrict__ X1, double* __restrict__ Xt0,
                             double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
                             const double* __restrict__ delta_c, double* __restrict__ scal_partial,
                             const unsigned short* __restrict__ pt_start, const double* __restrict__ stgN,
-                            const double* __restrict__ stgP, const unsigned short* __restrict__ pt_rank,
-                            const double2* __restrict__ uvc) {
+                            const double* __restrict__ stgP, const double2* __restrict__ uvc) {
   constexpr int BT = schur_bt(C), CB = C * BT, TB = SCHUR_BACKSUB_TB, NW = TB / 32;
   __shared__ double st[C * CAM_SMEM_STRIDE];   // trial cameras, odd stride: lanes on different cameras hit different banks
   __shared__ double sd[6 * C + 2];             // camera steps (w, tau)
@@ -761,15 +823,15 @@ schur_backsub_kernel(const uint8_t* __restrict__ obs_mask, int64_t P,
   __syncthreads();
   double f_acc = 0.0, pred_acc = 0.0, dx_acc = 0.0;
   double prod = 1.0;
-  const int64_t n_groups = skip ? 0 : (P + TB - 1) / TB;
-  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
-    const int64_t p = P - 1 - (g * TB + tid);
-    if (p < 0) continue;
-    const unsigned m = obs_mask[p];
-    if (!m) continue;
-    const int64_t tile = p / BT;
-    const size_t gi0 = (size_t)tile * CB + pt_start[p];
-    const size_t pr = (size_t)tile * BT + pt_rank[p];
+  const int64_t n_groups = skip ? 0 : (E + TB - 1) / TB;
+  for (int64_t grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+    const int64_t g = E - 1 - (grp * TB + tid);          // existing point g (compacted numbering), last to first
+    if (g < 0) continue;
+    const unsigned m = cmask[g];
+    const size_t p = pid[g];
+    const int64_t tile = g / BT;
+    const size_t gi0 = (size_t)tile * CB + pt_start[g];
+    const size_t pr = (size_t)g;
     const double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
     double s0 = 0.0, s1 = 0.0, s2 = 0.0;
     const int k = __popc(m);
@@ -982,7 +1044,7 @@ __global__ void schur_init_kernel(SchurLm* lm, double lambda0) {
 struct SchurState {
   static constexpr int PROF_MAX = 256;
   bool ready = false, inited = false, prof_on = false;
-  int grid_build = 0, grid_back = 0, launches = 0, prof_n = 0;
+  int grid_build = 0, grid_back = 0, grid_build_max = 0, grid_back_max = 0, launches = 0, prof_n = 0;
   double* cams_alt = nullptr;
   double* X_alt = nullptr;
   double* rcs_partial = nullptr;
@@ -1000,7 +1062,10 @@ struct SchurState {
   unsigned* polish_list[2] = {nullptr, nullptr};   // still-active points of the previous / this polish launch
   unsigned short* obs_lists = nullptr;     // [tile][8 + C*BT]
   unsigned short* pt_start = nullptr;      // [tile][BT] first observation of each point in its tile's list
-  unsigned short* pt_rank = nullptr;       // [tile][BT] rank of each point among the existing points of its tile
+  unsigned* pid = nullptr;                 // [E] scene index of the g-th existing point
+  uint8_t* cmask = nullptr;                // [E] its observation mask
+  unsigned* exist_blocks = nullptr;        // per-1024-point counts / offsets of the compaction
+  int64_t E = 0;                           // existing points of the current solve
   double2* uvc = nullptr;                  // [tile][C*BT] observations compacted in list order (built once per solve)
   double* stgN = nullptr;                  // [6][P*C] N rows per observation (tile list order), written by K4 for K6
   double* stgP = nullptr;                  // [15][P] V^-1, h, D, g per point, written by K4 for K6

@@ -169,12 +169,14 @@ static int schur_alloc(acino_sba* h) {
   const int bt = schur_bt(C), len = rcs_len(C);
   int64_t tiles = (h->P + bt - 1) / bt;
   { const int64_t cap = (int64_t)sms * schur_ctas_per_sm(C); s.grid_build = (int)(tiles < 1 ? 1 : (tiles < cap ? tiles : cap)); }
+  s.grid_build_max = s.grid_build;      // buffers are sized for all P slot groups existing; every solve launches what its E needs
   int occ = 1;     // resident CTAs per SM of the persistent back-substitution kernel
   DISPATCH_C(C, (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, schur_backsub_kernel<CC>, SCHUR_BACKSUB_TB, 0)));
   if (occ < 1) occ = 1;
   {
     const int64_t groups = (h->P + SCHUR_BACKSUB_TB - 1) / SCHUR_BACKSUB_TB;
     s.grid_back = (int)(groups < 1 ? 1 : (groups < (int64_t)sms * occ ? groups : (int64_t)sms * occ));
+    s.grid_back_max = s.grid_back;
   }
   size_t P = h->P ? (size_t)h->P : 1;
   ACINO_CUDA(cudaMalloc(&s.cams_alt, MAX_CAMS * CAM_STRIDE * sizeof(double)));
@@ -196,7 +198,9 @@ static int schur_alloc(acino_sba* h) {
     ACINO_CUDA(cudaMalloc(&s.unit_counts, nt * nup * sizeof(unsigned short)));
     ACINO_CUDA(cudaMalloc(&s.obs_lists, nt * (8 + (size_t)C * bt) * sizeof(unsigned short)));
     ACINO_CUDA(cudaMalloc(&s.pt_start, nt * bt * sizeof(unsigned short)));
-    ACINO_CUDA(cudaMalloc(&s.pt_rank, nt * bt * sizeof(unsigned short)));
+    ACINO_CUDA(cudaMalloc(&s.pid, nt * bt * sizeof(unsigned)));
+    ACINO_CUDA(cudaMalloc(&s.cmask, nt * bt * sizeof(uint8_t)));
+    ACINO_CUDA(cudaMalloc(&s.exist_blocks, ((P + EXIST_TB - 1) / EXIST_TB + 1) * sizeof(unsigned)));
     ACINO_CUDA(cudaMalloc(&s.uvc, nt * (size_t)C * bt * sizeof(double2)));
     // rows staged by K4 for K6 (6 doubles per slot, 15 per point): 1 GB per 119,490 frames at C = 6
     ACINO_CUDA(cudaMalloc(&s.stgN, 6 * nt * (size_t)C * bt * sizeof(double)));
@@ -216,7 +220,7 @@ static int schur_alloc(acino_sba* h) {
 static void schur_free(SchurState& s) {
   cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.max_partial); cudaFree(s.rcs);
   cudaFree(s.mx); cudaFree(s.delta_c); cudaFree(s.scal_partial); cudaFree(s.scal); cudaFree(s.lm);
-  cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.unit_lists); cudaFree(s.unit_counts); cudaFree(s.obs_lists); cudaFree(s.pt_start); cudaFree(s.pt_rank); cudaFree(s.uvc); cudaFree(s.stgN); cudaFree(s.stgP);
+  cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.unit_lists); cudaFree(s.unit_counts); cudaFree(s.obs_lists); cudaFree(s.pt_start); cudaFree(s.pid); cudaFree(s.cmask); cudaFree(s.exist_blocks); cudaFree(s.uvc); cudaFree(s.stgN); cudaFree(s.stgP);
   if (s.h_lm) cudaFreeHost(s.h_lm);
   for (cudaEvent_t e : s.prof_ev) if (e) cudaEventDestroy(e);
   s = SchurState();
@@ -243,8 +247,23 @@ static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
   // the camera-pair point lists of every tile follow from the masks alone: (re)built once per solve (the observation
   // mask may be a borrowed device buffer that changed since the last solve; it must not change during one)
   if (h->P > 0) {
-    DISPATCH_C(h->C, (schur_lists_kernel<CC><<<(unsigned)s.n_tiles, schur_bt(CC), 0, h->stream>>>(h->mask, h->P, s.unit_lists, s.unit_counts,
-                                                                                                  s.obs_lists, s.pt_start, s.pt_rank, h->uv, s.uvc)));
+    // existing points compacted (pid, cmask, E), then the per-tile lists over tiles of schur_bt existing points
+    const int nb = (int)((h->P + EXIST_TB - 1) / EXIST_TB);
+    exist_count_kernel<<<nb, EXIST_TB, 0, h->stream>>>(h->mask, h->P, s.exist_blocks);
+    exist_scan_kernel<<<1, EXIST_TB, 0, h->stream>>>(s.exist_blocks, nb, h->counters + 7);
+    exist_scatter_kernel<<<nb, EXIST_TB, 0, h->stream>>>(h->mask, h->P, s.exist_blocks, s.pid, s.cmask);
+    ACINO_CUDA(cudaGetLastError());
+    ACINO_CUDA(cudaMemcpyAsync(h->h_counters + 7, h->counters + 7, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    s.E = (int64_t)h->h_counters[7];
+    const int bt = schur_bt(h->C);
+    s.n_tiles = (s.E + bt - 1) / bt;
+    s.grid_build = (int)(s.n_tiles < 1 ? 1 : (s.n_tiles < s.grid_build_max ? s.n_tiles : s.grid_build_max));
+    const int64_t groups = (s.E + SCHUR_BACKSUB_TB - 1) / SCHUR_BACKSUB_TB;
+    s.grid_back = (int)(groups < 1 ? 1 : (groups < s.grid_back_max ? groups : s.grid_back_max));
+    if (s.n_tiles > 0)
+      DISPATCH_C(h->C, (schur_lists_kernel<CC><<<(unsigned)s.n_tiles, schur_bt(CC), 0, h->stream>>>(
+                           s.cmask, s.pid, s.E, s.unit_lists, s.unit_counts, s.obs_lists, s.pt_start, h->uv, s.uvc)));
     ACINO_CUDA(cudaGetLastError());
     int rc = ensure_point_order(h, true);      // K3 (refinement, polishing) visits the points by observation count
     if (rc) return rc;
@@ -263,8 +282,8 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   const bool prof = s.prof_on && s.prof_n < SchurState::PROF_MAX;
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n], st));
   DISPATCH_C(C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, st>>>(
-                    h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.rcs_partial, s.max_partial, s.unit_lists,
-                    s.unit_counts, s.obs_lists, s.stgN, s.stgP, s.pt_rank, s.uvc)));
+                    s.cmask, s.pid, s.E, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.rcs_partial, s.max_partial, s.unit_lists,
+                    s.unit_counts, s.obs_lists, s.stgN, s.stgP, s.uvc)));
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 1], st));
   ++s.launches;
@@ -299,8 +318,8 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 2], st));
   DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, SCHUR_BACKSUB_TB, 0, st>>>(
-                    h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, h->X, s.X_alt, s.lm, prm, s.delta_c, s.scal_partial,
-                    s.pt_start, s.stgN, s.stgP, s.pt_rank, s.uvc)));
+                    s.cmask, s.pid, s.E, h->P, h->cams, s.cams_alt, h->X, s.X_alt, h->X, s.X_alt, s.lm, prm, s.delta_c, s.scal_partial,
+                    s.pt_start, s.stgN, s.stgP, s.uvc)));
   ACINO_CUDA(cudaGetLastError());
   if (prof) { ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 3], st)); ++s.prof_n; }
   ++s.launches;
@@ -497,8 +516,8 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     pf.force = 1;
     const int len = rcs_len(h->C);
     DISPATCH_C(h->C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, h->stream>>>(
-                         h->uv, h->mask, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, pf, s.rcs_partial, s.max_partial,
-                         s.unit_lists, s.unit_counts, s.obs_lists, s.stgN, s.stgP, s.pt_rank, s.uvc)));
+                         s.cmask, s.pid, s.E, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, pf, s.rcs_partial, s.max_partial,
+                         s.unit_lists, s.unit_counts, s.obs_lists, s.stgN, s.stgP, s.uvc)));
     ACINO_CUDA(cudaGetLastError());
     fold_partials_kernel<<<(len + 31) / 32, 256, 0, h->stream>>>(s.rcs_partial, s.grid_build, len, s.rcs, s.max_partial,
                                                                  s.grid_build, 2, 2, 0, s.mx);
