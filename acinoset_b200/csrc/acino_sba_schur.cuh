@@ -270,15 +270,19 @@ schur_lists_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict
 }
 
 // ---- K4: residual + Jacobian + per-point blocks + Schur accumulation ------------------------------------
-// Persistent CTAs of BT threads loop over tiles of BT points.
-//   phase 1 (one thread per point): linearise the point's observations, build V, g, invert V + lam D, stage
-//            N (6 doubles) and e (2) per observation and X, V^-1, h = V^-1 g per point in shared memory, and
-//            append the point to the list of every camera pair (unit) it is observed by.
-//   phase 2 (one warp per unit, lanes over the unit's point list): accumulate the unit's 6x6 block (+ rhs, gradient
-//            and diag(U) for diagonal units) in registers, reduce-scatter over the warp, add into the CTA's
-//            shared RCS. Lists, unit order and the reduction tree are fixed, so the result is deterministic.
-// At the end every CTA writes its RCS partial; the solve kernel (or the reduce kernel before the NCCL
-// allreduce) sums the partials in a fixed order.
+// Persistent CTAs of BT threads loop over tiles of BT EXISTING points (compacted numbering, pid / cmask) with the
+// per-tile lists schur_lists_kernel built from the masks.
+//   phase 1a  the tile's points, observation list and mask arrived during the previous tile (cp.async, double
+//             buffered); this tile's camera-pair lists and the next tile's data are requested
+//   phase 1b  one thread per OBSERVATION of the tile's list: linearise it; N (6 doubles) and e (2) into the staging
+//             arrays in shared memory, N also to HBM for K6
+//   phase 1c  one thread per point: V, g from the staged rows, damped inverse, h = V^-1 g (record to HBM for K6)
+//   phase 2   one warp per camera pair (unit, claimed longest first), lanes over the unit's point list: accumulate the
+//             unit's 6x6 block (+ rhs, gradient and diag(U) for diagonal units) in registers, reduce-scatter over
+//             the warp, add into the CTA's shared RCS. Lists, unit order and the reduction tree are fixed, so the
+//             result is deterministic.
+// At the end every CTA writes its RCS partial; fold_partials_kernel sums the partials in a fixed order (and at more
+// than one rank the sums of all ranks meet in K5, acino_sba_xchg.cuh).
 template <int C>
 struct SchurSmem {
   static constexpr int BT = schur_bt(C);
