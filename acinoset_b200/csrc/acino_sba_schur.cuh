@@ -11,7 +11,7 @@
 // Reduced-camera-system vector ("RCS"), NU = C(C+1)/2 units of 40 doubles + 8 scalars:
 //   unit c   (c < C)      : [0..20] S_cc upper triangle, [21..26] rhs_c, [27..32] g_c, [33..38] diag(U_c)
 //   unit C+k (pair c<c')  : [0..35] S_cc' row-major
-//   scalars               : [0] robust cost at the current parameters
+//   scalars               : [0] robust cost at the current parameters, [1] sum over the points of g^T h
 #pragma once
 #include "acino_common.cuh"
 #include "acino_sba_xchg.cuh"
@@ -342,7 +342,7 @@ schur_build_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict
   }
   __syncthreads();
 
-  double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0;
+  double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0, gh_acc = 0.0;
   double cprod = 1.0;     // running product of (1+z_u)(1+z_v): sum of log1p(z) = log of the product
   // tiles of BT EXISTING points (compacted numbering g, pid[g] = the point's index in the scene)
   const int64_t n_tiles = skip ? 0 : (E + BT - 1) / BT;
@@ -458,8 +458,11 @@ schur_build_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict
         stgP[3 * PS + pp] = iv.i11; stgP[4 * PS + pp] = iv.i12; stgP[5 * PS + pp] = iv.i22;
         stgP[6 * PS + pp] = sH[tid]; stgP[7 * PS + pp] = sH[BS + tid]; stgP[8 * PS + pp] = sH[2 * BS + tid];
         stgP[9 * PS + pp] = iv.D0; stgP[10 * PS + pp] = iv.D1; stgP[11 * PS + pp] = iv.D2;
-        stgP[12 * PS + pp] = g0; stgP[13 * PS + pp] = g1; stgP[14 * PS + pp] = g2;
       }
+      // g^T h of the point block: with dX = -(h + V^-1 s) the gradient term of the predicted reduction is
+      // -g^T dX = g^T h + h^T s; the first part is summed here (RCS scalar [1]), the second in K6, so that g need not
+      // travel to K6 (24 B per point less written here and read there)
+      gh_acc += fma(g0, sH[tid], fma(g1, sH[BS + tid], g2 * sH[2 * BS + tid]));
       gmax_acc = fmax(gmax_acc, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
     }
     if (tid == 0) next_unit[0] = 0;
@@ -573,19 +576,21 @@ schur_build_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict
 
   // ---------------- CTA totals: cost (sum) and gradient / coordinate maxima
   cost_acc += prm.half_c2 * log(cprod);
-  __shared__ double red[3][32];
+  __shared__ double red[4][32];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     cost_acc += __shfl_xor_sync(0xffffffffu, cost_acc, o);
+    gh_acc += __shfl_xor_sync(0xffffffffu, gh_acc, o);
     gmax_acc = fmax(gmax_acc, __shfl_xor_sync(0xffffffffu, gmax_acc, o));
     xmax_acc = fmax(xmax_acc, __shfl_xor_sync(0xffffffffu, xmax_acc, o));
   }
-  if (lane == 0) { red[0][warp] = cost_acc; red[1][warp] = gmax_acc; red[2][warp] = xmax_acc; }
+  if (lane == 0) { red[0][warp] = cost_acc; red[1][warp] = gmax_acc; red[2][warp] = xmax_acc; red[3][warp] = gh_acc; }
   __syncthreads();
   if (tid == 0) {
-    double cs = 0, gm = 0, xm = 0;
-    for (int w = 0; w < NW; ++w) { cs += red[0][w]; gm = fmax(gm, red[1][w]); xm = fmax(xm, red[2][w]); }
+    double cs = 0, gm = 0, xm = 0, gh = 0;
+    for (int w = 0; w < NW; ++w) { cs += red[0][w]; gm = fmax(gm, red[1][w]); xm = fmax(xm, red[2][w]); gh += red[3][w]; }
     sS[NU * RCS_UNIT] = cs;
+    sS[NU * RCS_UNIT + 1] = gh;
     max_partial[2 * blockIdx.x] = gm;
     max_partial[2 * blockIdx.x + 1] = xm;
   }
@@ -762,7 +767,7 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
     }
     if (lane == 0) {
       if (bad) lm->chol_fail += 1;
-      lm->pred_cam = pc;
+      lm->pred_cam = pc + 0.5 * r[NU * RCS_UNIT + 1];      // + the points' g^T h (K4), see K6
       fail = bad;
     }
   }
@@ -872,12 +877,12 @@ schur_backsub_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restri
     const double i11 = stgP[3 * PS + pr], i12 = stgP[4 * PS + pr], i22 = stgP[5 * PS + pr];
     const double h0 = stgP[6 * PS + pr], h1 = stgP[7 * PS + pr], h2 = stgP[8 * PS + pr];
     const double D0 = stgP[9 * PS + pr], D1 = stgP[10 * PS + pr], D2 = stgP[11 * PS + pr];
-    const double g0 = stgP[12 * PS + pr], g1 = stgP[13 * PS + pr], g2 = stgP[14 * PS + pr];
     const double d0 = -(h0 + fma(i00, s0, fma(i01, s1, i02 * s2)));
     const double d1 = -(h1 + fma(i01, s0, fma(i11, s1, i12 * s2)));
     const double d2 = -(h2 + fma(i02, s0, fma(i12, s1, i22 * s2)));
-    // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta) with the undamped gradient g
-    pred_acc += 0.5 * (lam * (D0 * d0 * d0 + D1 * d1 * d1 + D2 * d2 * d2) - fma(g0, d0, fma(g1, d1, g2 * d2)));
+    // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta) with the undamped gradient g;
+    // for the point block -g^T dX = g^T h + h^T s, of which K4 has already summed g^T h (it reaches K7 through K5)
+    pred_acc += 0.5 * (lam * (D0 * d0 * d0 + D1 * d1 * d1 + D2 * d2 * d2) + fma(h0, s0, fma(h1, s1, h2 * s2)));
     const double xt = X + d0, yt = Y + d1, zt = Z + d2;
     Xt[3 * p] = xt; Xt[3 * p + 1] = yt; Xt[3 * p + 2] = zt;
     dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));

@@ -202,9 +202,9 @@ static int schur_alloc(acino_sba* h) {
     ACINO_CUDA(cudaMalloc(&s.cmask, nt * bt * sizeof(uint8_t)));
     ACINO_CUDA(cudaMalloc(&s.exist_blocks, ((P + EXIST_TB - 1) / EXIST_TB + 1) * sizeof(unsigned)));
     ACINO_CUDA(cudaMalloc(&s.uvc, nt * (size_t)C * bt * sizeof(double2)));
-    // rows staged by K4 for K6 (6 doubles per slot, 15 per point): 1 GB per 119,490 frames at C = 6
+    // rows staged by K4 for K6 (6 doubles per slot, 12 per point): 1 GB per 119,490 frames at C = 6
     ACINO_CUDA(cudaMalloc(&s.stgN, 6 * nt * (size_t)C * bt * sizeof(double)));
-    ACINO_CUDA(cudaMalloc(&s.stgP, 15 * nt * (size_t)bt * sizeof(double)));
+    ACINO_CUDA(cudaMalloc(&s.stgP, 12 * nt * (size_t)bt * sizeof(double)));
     s.n_tiles = (int64_t)nt;
   }
   ACINO_CUDA(cudaMemsetAsync(s.cams_alt, 0, MAX_CAMS * CAM_STRIDE * sizeof(double), h->stream));
