@@ -57,6 +57,7 @@ SIGNATURES = {
     'acino_ekf_measurement': (_I, [_P, _I, _I, _P, _I, _D, _I, _P, _P, _P]),
     'acino_manual_residuals': (_I, [_P, _I, _P, _I, _P, _I, _P, _I, _P, _I, _D, _D, _D, _P]),
     'acino_ring_critical': (_I, [_P, _I64, _I, _P]),
+    'acino_jacobian_list': (_I, [_P, _I64, _P, _P, _I64, _P, _I, _P]),
     'acino_rodrigues': (_I, [_P, _I, _P]),
     'acino_triangulate_pair': (_I, [_P, _P, _I64, _P, _P, _P]),
     'acino_triangulate_ring': (_I, [_P, _P, _D, _I64, _I, _P, _P, _P, _P]),
@@ -80,6 +81,7 @@ SIGNATURES = {
     'acino_sba_stream': (_P, [_P]),
     'acino_sba_profile': (_I, [_P, _I]),
     'acino_sba_profile_read': (_I, [_P, ct.POINTER(_D), ct.POINTER(_D), ct.POINTER(_I)]),
+    'acino_sba_profile_read_kernels': (_I, [_P, _P, ct.POINTER(_I)]),
     'acino_sba_lm_state': (_I, [_P, _P]),
     'acino_fp64_peak': (_I, [ct.POINTER(_D)]),
     'acino_nccl_unique_id': (_I, [_P]),

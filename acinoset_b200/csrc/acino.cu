@@ -133,6 +133,34 @@ int acino_residuals_list(const double* X, int64_t n_points, const int32_t* point
   return ACINO_OK;
 }
 
+int acino_jacobian_list(const double* X, int64_t n_points, const int32_t* point_idx, const int32_t* cam_idx, int64_t n_obs,
+                        const double* cams24, int n_cams, double* J) {
+  ARG_CHECK(n_points >= 0 && n_obs >= 0 && n_cams > 0 && n_cams <= 64 && cams24, "jacobian_list");
+  if (n_obs == 0) return ACINO_OK;
+  ARG_CHECK(X && point_idx && cam_idx && J, "jacobian_list null pointer");
+  for (int64_t o = 0; o < n_obs; ++o) {
+    if (point_idx[o] < 0 || point_idx[o] >= n_points || cam_idx[o] < 0 || cam_idx[o] >= n_cams) {
+      set_error("jacobian_list: observation %lld has point %d / camera %d out of range", (long long)o, point_idx[o], cam_idx[o]);
+      return ACINO_EINVAL;
+    }
+  }
+  DevBuf dX, dP, dC, dJ, dCam;
+  ACINO_CUDA(dX.alloc(n_points * 3 * sizeof(double)));
+  ACINO_CUDA(dP.alloc(n_obs * sizeof(int32_t)));
+  ACINO_CUDA(dC.alloc(n_obs * sizeof(int32_t)));
+  ACINO_CUDA(dJ.alloc(n_obs * 18 * sizeof(double)));
+  ACINO_CUDA(dCam.alloc(n_cams * CAM_STRIDE * sizeof(double)));
+  ACINO_CUDA(cudaMemcpy(dX.p, X, n_points * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dP.p, point_idx, n_obs * sizeof(int32_t), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dC.p, cam_idx, n_obs * sizeof(int32_t), cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaMemcpy(dCam.p, cams24, n_cams * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  jacobian_list_kernel<<<grid_for(n_obs, 256), 256, n_cams * CAM_STRIDE * sizeof(double)>>>(
+      dX.as<double>(), dP.as<int32_t>(), dC.as<int32_t>(), n_obs, dCam.as<double>(), n_cams, dJ.as<double>());
+  ACINO_CUDA(cudaGetLastError());
+  ACINO_CUDA(cudaMemcpy(J, dJ.p, n_obs * 18 * sizeof(double), cudaMemcpyDeviceToHost));
+  return ACINO_OK;
+}
+
 __global__ void rodrigues_kernel(const double* rv, int n, double* R) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) rodrigues(rv + 3 * i, R + 9 * i);

@@ -322,6 +322,33 @@ residuals_list_kernel(const double* __restrict__ Xp, const int32_t* __restrict__
   f[o] = make_double2(u - q.x, v - q.y);
 }
 
+// The analytic Jacobian the LM kernels are built from, for inspection (it is tested against central
+// differences of the reference's residual): per observation the 2x9 matrix d(u, v) / d(w, tau, X), w and tau the
+// world-frame twist of the camera (R <- R Exp(w), t <- t + R tau), X the point: rows [X x n | n | n] with n the rows of
+// N = d(u,v)/dX. Same device functions as K3 / K4a (fisheye_uv_jac, mul_R), without the robust weights.
+__global__ void __launch_bounds__(256)
+jacobian_list_kernel(const double* __restrict__ Xp, const int32_t* __restrict__ pidx, const int32_t* __restrict__ cidx,
+                     int64_t n_obs, const double* __restrict__ cams, int n_cams, double* __restrict__ J) {
+  extern __shared__ double sc[];
+  for (int i = threadIdx.x; i < n_cams * CAM_STRIDE; i += blockDim.x) sc[i] = cams[i];
+  __syncthreads();
+  int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= n_obs) return;
+  const int64_t p = pidx[o];
+  const double* cam = sc + cidx[o] * CAM_STRIDE;
+  const double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
+  double x, y, z, u, v, Ju[3], Jv[3], n0[3], n1[3];
+  to_camera(cam, X, Y, Z, x, y, z);
+  fisheye_uv_jac(cam, x, y, z, u, v, Ju, Jv);
+  mul_R(cam, Ju, n0);
+  mul_R(cam, Jv, n1);
+  double* r0 = J + 18 * o;
+  double* r1 = r0 + 9;
+  r0[0] = fma(Y, n0[2], -Z * n0[1]); r0[1] = fma(Z, n0[0], -X * n0[2]); r0[2] = fma(X, n0[1], -Y * n0[0]);
+  r1[0] = fma(Y, n1[2], -Z * n1[1]); r1[1] = fma(Z, n1[0], -X * n1[2]); r1[2] = fma(X, n1[1], -Y * n1[0]);
+  for (int i = 0; i < 3; ++i) { r0[3 + i] = n0[i]; r0[6 + i] = n0[i]; r1[3 + i] = n1[i]; r1[6 + i] = n1[i]; }
+}
+
 // K1 plain projection of N points into one camera (project_points_fisheye)
 __global__ void __launch_bounds__(256)
 project_kernel(const double* __restrict__ Xp, int64_t N, const double* __restrict__ cam, double2* __restrict__ uv) {

@@ -1,4 +1,4 @@
-// acino_sba_schur.cuh — K4/K5/K6: points+extrinsics Levenberg-Marquardt with Schur elimination.
+// acino_sba_schur.cuh — K4a/K4b/K5/K6/K7: points+extrinsics Levenberg-Marquardt with Schur elimination.
 // Replaces the scipy least_squares call of bundle_adjust_points_and_extrinsics (src/lib/sba.py:158-178):
 // same objective (Cauchy on every scalar residual), analytic Jacobian, per-point 3x3 blocks eliminated into
 // the 6C x 6C reduced camera system (SURVEY.md §8a "Schur structure").
@@ -21,8 +21,6 @@ namespace acino {
 #define RCS_UNIT 40
 __host__ __device__ constexpr int rcs_units(int C) { return C * (C + 1) / 2; }
 __host__ __device__ constexpr int rcs_len(int C) { return rcs_units(C) * RCS_UNIT + 8; }
-__host__ __device__ constexpr int schur_bt(int C) { return C <= 6 ? 384 : 256; }
-__host__ __device__ constexpr int schur_ctas_per_sm(int) { return 1; }   // 2 x 192 threads measured slower (0.74 vs 0.66 ms)
 
 // device-resident LM state: every decision is taken on the device from (all-reduced) sums, identically on all ranks
 struct SchurLm {
@@ -133,32 +131,57 @@ __device__ __forceinline__ void warp_reduce_scatter40(double (&a)[RCS_UNIT], int
   }
 }
 
-// ---- existing points, compacted ------------------------------------------------------------------------------
+// ---- the existing points, sorted by their observation mask ("class") ------------------------------------------
 // Only (frame, keypoint) slot groups with a non-empty observation mask are points of the problem (72 % of them at 50 %
-// masking). K4 / K6 tile the EXISTING points: pid[g] = index of the g-th existing point (increasing), cmask[g] its mask,
-// so that a tile of BT points is BT points of work: 28 % fewer tiles, barriers, unit claims and warp reductions at C4,
-// and longer camera-pair lists per tile (fuller last rounds). Three small kernels, once per solve: per-block counts,
-// a single-block scan of the counts, scatter.
-#define EXIST_TB 1024
-__global__ void __launch_bounds__(EXIST_TB)
-exist_count_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, unsigned* __restrict__ block_counts) {
-  const int64_t p = (int64_t)blockIdx.x * EXIST_TB + threadIdx.x;
-  const int n = __syncthreads_count(p < P && obs_mask[p] != 0);
-  if (threadIdx.x == 0) block_counts[blockIdx.x] = (unsigned)n;
+// masking). Once per solve they are sorted by the VALUE of the mask (stable: scene order within a class) and every
+// class is padded to whole rounds of 32 points. In that numbering a warp always holds 32 points seen by the SAME
+// cameras, so K4a / K4b / K6 have
+//   * warp-uniform control flow and camera parameters (no per-lane camera loops, no idle lanes for masked slots),
+//   * no per-tile lists at all: the points two cameras share are whole rounds of whole classes,
+//   * fully coalesced 16-byte accesses: all per-round data is laid out [row][lane] in rows of 32 double2 (512 B).
+// Layout of one round of a class with k cameras c_0 < ... < c_{k-1} in the staging array (4k + 6 rows):
+//   rows 3j .. 3j+2   (n0x n0y) (n0z n1x) (n1y n1z)      weighted point Jacobian of the observation by camera c_j
+//   row  3k + j       (e0 e1)                            its scaled residual
+//   rows 4k .. 4k+5   (X Y) (Z i00) (i01 i02) (i11 i12) (i22 h0) (h1 h2)      the point, (V + lam D)^-1, h = V^-1 g
+// and in the observation array (k rows): row j = (u v) of camera c_j. Padding lanes hold zeros in every row, which
+// contribute exactly zero to every sum, so no kernel needs a lane predicate in its inner loop.
+#define SCHUR_MAXCLS 256
+#define SCHUR_ROW 32                      // double2 per row
+struct SchurClasses {
+  unsigned round0[SCHUR_MAXCLS + 1];      // first round of class m (= mask value m); [2^C] = number of rounds
+  unsigned blk0[SCHUR_MAXCLS + 1];        // first staging row of class m
+  unsigned uv0[SCHUR_MAXCLS + 1];         // first observation row of class m
+  unsigned off0[SCHUR_MAXCLS + 1];        // exclusive scan value of the class's first histogram entry
+};
+__host__ __device__ constexpr int schur_rows(int k) { return 4 * k + 6; }
+
+#define CLS_TB 1024
+// histogram of the mask values per block of 1024 slot groups, bin-major: hist[m * n_blocks + block]
+template <int C>
+__global__ void __launch_bounds__(CLS_TB)
+cls_hist_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, int n_blocks, unsigned* __restrict__ hist) {
+  constexpr int NCLS = 1 << C;
+  __shared__ unsigned cnt[NCLS];
+  for (int i = threadIdx.x; i < NCLS; i += CLS_TB) cnt[i] = 0u;
+  __syncthreads();
+  const int64_t p = (int64_t)blockIdx.x * CLS_TB + threadIdx.x;
+  if (p < P) atomicAdd(&cnt[obs_mask[p] & (NCLS - 1)], 1u);      // integer counts: order-independent
+  __syncthreads();
+  for (int i = threadIdx.x; i < NCLS; i += CLS_TB) hist[(size_t)i * n_blocks + blockIdx.x] = cnt[i];
 }
 
-// in place: block_counts[i] <- sum of the counts before block i; total[0] <- number of existing points
-__global__ void __launch_bounds__(EXIST_TB)
-exist_scan_kernel(unsigned* __restrict__ block_counts, int n_blocks, unsigned long long* __restrict__ total) {
-  __shared__ unsigned wsum[EXIST_TB / 32];
+// in place: v[i] <- sum of the entries before i; total[0] <- sum of all n entries. One block.
+__global__ void __launch_bounds__(CLS_TB)
+exclusive_scan_kernel(unsigned* __restrict__ v, int64_t n, unsigned long long* __restrict__ total) {
+  __shared__ unsigned wsum[CLS_TB / 32];
   __shared__ unsigned long long carry;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) carry = 0ull;
   __syncthreads();
-  for (int base = 0; base < n_blocks; base += EXIST_TB) {
-    const int i = base + tid;
-    const unsigned v = i < n_blocks ? block_counts[i] : 0u;
-    unsigned incl = v;
+  for (int64_t base = 0; base < n; base += CLS_TB) {
+    const int64_t i = base + tid;
+    const unsigned x = i < n ? v[i] : 0u;
+    unsigned incl = x;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
@@ -169,414 +192,170 @@ exist_scan_kernel(unsigned* __restrict__ block_counts, int n_blocks, unsigned lo
     unsigned before = 0;
     for (int w = 0; w < warp; ++w) before += wsum[w];
     const unsigned long long c0 = carry;
-    if (i < n_blocks) block_counts[i] = (unsigned)(c0 + before + incl - v);
+    if (i < n) v[i] = (unsigned)(c0 + before + incl - x);
     __syncthreads();
-    if (tid == EXIST_TB - 1) carry = c0 + before + incl;
+    if (tid == CLS_TB - 1) carry = c0 + before + incl;
     __syncthreads();
   }
   if (tid == 0) total[0] = carry;
 }
 
-__global__ void __launch_bounds__(EXIST_TB)
-exist_scatter_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, const unsigned* __restrict__ block_offsets,
-                     unsigned* __restrict__ pid, uint8_t* __restrict__ cmask) {
-  __shared__ unsigned wsum[EXIST_TB / 32];
+// the scan value at the first block of every class, contiguous for the read-back: out[m] = hist[m * n_blocks]
+__global__ void cls_starts_kernel(const unsigned* __restrict__ hist, int n_blocks, int ncls, unsigned* __restrict__ out) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m < ncls) out[m] = hist[(size_t)m * n_blocks];
+}
+
+// pid[g] <- scene index of the point at sorted position g (stable within the class); padding keeps 0xFFFFFFFF
+template <int C>
+__global__ void __launch_bounds__(CLS_TB)
+cls_scatter_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, int n_blocks, const unsigned* __restrict__ hist,
+                   const SchurClasses* __restrict__ cls, unsigned* __restrict__ pid) {
+  constexpr int NCLS = 1 << C, NW = CLS_TB / 32;
+  __shared__ unsigned short wcnt[NW][NCLS];      // points of class m in warp w of this block
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int64_t p = (int64_t)blockIdx.x * EXIST_TB + tid;
-  const unsigned m = p < P ? obs_mask[p] : 0u;
-  const unsigned bal = __ballot_sync(0xffffffffu, m != 0);
-  if (lane == 0) wsum[warp] = __popc(bal);
+  for (int i = tid; i < NW * NCLS; i += CLS_TB) (&wcnt[0][0])[i] = 0;
+  __syncthreads();
+  const int64_t p = (int64_t)blockIdx.x * CLS_TB + tid;
+  const unsigned m = p < P ? (obs_mask[p] & (NCLS - 1)) : 0u;
+  const unsigned same = __match_any_sync(0xffffffffu, m);
+  const unsigned before = __popc(same & ((1u << lane) - 1u));
+  if (m && before == 0) wcnt[warp][m] = (unsigned short)__popc(same);
   __syncthreads();
   if (m) {
-    unsigned g = block_offsets[blockIdx.x] + __popc(bal & ((1u << lane) - 1u));
-    for (int w = 0; w < warp; ++w) g += wsum[w];
+    unsigned r = before;
+    for (int w = 0; w < warp; ++w) r += wcnt[w][m];
+    const size_t g = (size_t)cls->round0[m] * 32 + (hist[(size_t)m * n_blocks + blockIdx.x] - cls->off0[m]) + r;
     pid[g] = (unsigned)p;
-    cmask[g] = (uint8_t)m;
   }
 }
 
-// ---- unit lists: for every tile of BT points and every camera pair (unit), the tile-local indices of the points both
-// cameras observe, in point order. They depend on the masks only, so they are built once per solve and K4 streams
-// them in (cp.async) instead of compacting them again in every LM iteration. lists [tile][unit][BT] u16,
-// counts [tile][NUP] u16: [0, NU) the list lengths, [NU, 2 NU) the units sorted by length (longest first).
+__device__ __forceinline__ int schur_class_of_round(const unsigned* s_round0, int ncls, unsigned r) {
+  int lo = 0, hi = ncls;        // round0[lo] <= r < round0[hi]
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (s_round0[mid] <= r) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// the observations in the sorted layout: row j of a round = (u, v) of the class's j-th camera, zeros in padding lanes
 template <int C>
-__global__ void __launch_bounds__(schur_bt(C))
-schur_lists_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict__ pid, int64_t E,
-                   unsigned short* __restrict__ lists, unsigned short* __restrict__ counts,
-                   unsigned short* __restrict__ obs_lists, unsigned short* __restrict__ pt_start,
-                   const double2* __restrict__ uv, double2* __restrict__ uvc) {
-  constexpr int BT = schur_bt(C), NU = rcs_units(C), NW = BT / 32, NUP = (2 * NU + 7) & ~7, OB = 8 + C * BT;
-  __shared__ unsigned char sM[BT];
-  __shared__ int wtot[NW];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int64_t tile = blockIdx.x;
-  const int64_t g = tile * BT + tid;                 // existing point g of the compacted numbering (tile-local index tid)
-  const unsigned m = (g < E) ? cmask[g] : 0u;
-  const size_t p = (g < E) ? pid[g] : 0;
-  sM[tid] = (unsigned char)m;
-  {   // the tile's observations, point-major then camera: [0] = count, [8 + i] = q*8 + c
-    int k = __popc(m), incl = k;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      int v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    if (lane == 31) wtot[warp] = incl;
-    __syncthreads();
-    int base = incl - k;
-    for (int w = 0; w < warp; ++w) base += wtot[w];
-    pt_start[(size_t)tile * BT + tid] = (unsigned short)base;
-    unsigned short* ol = obs_lists + (size_t)tile * OB;
-    unsigned mm = m;
-    while (mm) {
-      int c = __ffs(mm) - 1;
-      mm &= mm - 1;
-      uvc[(size_t)tile * (C * BT) + base] = uv[p * C + c];     // observations compacted in list order
-      ol[8 + base++] = (unsigned short)(tid * 8 + c);
-    }
-    if (tid == BT - 1) ol[0] = (unsigned short)base;
-  }
-  __shared__ unsigned short scnt[NU];
-  for (int u = warp; u < NU; u += NW) {
-    int c, cp;
-    if (u < C) { c = u; cp = u; }
-    else {
-      int k = u - C; c = 0;
-      while (k >= C - 1 - c) { k -= C - 1 - c; ++c; }
-      cp = c + 1 + k;
-    }
-    unsigned short* lst = lists + ((size_t)tile * NU + u) * BT;
-    int n = 0;
-    for (int b0 = 0; b0 < BT; b0 += 32) {
-      const unsigned mq = sM[b0 + lane];
-      const bool in = (mq >> c & 1) && (mq >> cp & 1);
-      const unsigned b = __ballot_sync(0xffffffffu, in);
-      if (in) lst[n + __popc(b & ((1u << lane) - 1u))] = (unsigned short)(b0 + lane);
-      n += __popc(b);
-    }
-    if (lane == 0) { counts[tile * NUP + u] = (unsigned short)n; scnt[u] = (unsigned short)n; }
-  }
+__global__ void __launch_bounds__(256)
+cls_fill_obs_kernel(const SchurClasses* __restrict__ cls, const unsigned* __restrict__ pid, const double2* __restrict__ uv,
+                    double2* __restrict__ uvs) {
+  constexpr int NCLS = 1 << C;
+  __shared__ unsigned s_round0[NCLS + 1], s_uv0[NCLS + 1];
+  for (int i = threadIdx.x; i <= NCLS; i += 256) { s_round0[i] = cls->round0[i]; s_uv0[i] = cls->uv0[i]; }
   __syncthreads();
-  if (tid == 0) {   // claim order of phase 2: longest list first (ties: lower unit first), so the tail of the tile is short work
-    unsigned short ord[NU];
-    for (int u = 0; u < NU; ++u) {
-      int k = u;
-      while (k > 0 && scnt[ord[k - 1]] < scnt[u]) { ord[k] = ord[k - 1]; --k; }
-      ord[k] = (unsigned short)u;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned n_rounds = s_round0[NCLS];
+  for (unsigned r = blockIdx.x * 8 + warp; r < n_rounds; r += gridDim.x * 8) {
+    const int m = schur_class_of_round(s_round0, NCLS, r);
+    const int k = __popc(m);
+    const unsigned p = pid[(size_t)r * 32 + lane];
+    double2* dst = uvs + ((size_t)s_uv0[m] + (size_t)(r - s_round0[m]) * k) * SCHUR_ROW + lane;
+    int j = 0;
+    for (unsigned mm = m; mm; mm &= mm - 1, ++j) {
+      const int c = __ffs(mm) - 1;
+      dst[j * SCHUR_ROW] = (p != 0xFFFFFFFFu) ? uv[(size_t)p * C + c] : make_double2(0.0, 0.0);
     }
-    for (int u = 0; u < NU; ++u) counts[tile * NUP + NU + u] = ord[u];
-    for (int u = 2 * NU; u < NUP; ++u) counts[tile * NUP + u] = 0;
   }
 }
 
-// ---- K4: residual + Jacobian + per-point blocks + Schur accumulation ------------------------------------
-// Persistent CTAs of BT threads loop over tiles of BT EXISTING points (compacted numbering, pid / cmask) with the
-// per-tile lists schur_lists_kernel built from the masks.
-//   phase 1a  the tile's points, observation list and mask arrived during the previous tile (cp.async, double
-//             buffered); this tile's camera-pair lists and the next tile's data are requested
-//   phase 1b  one thread per OBSERVATION of the tile's list: linearise it; N (6 doubles) and e (2) into the staging
-//             arrays in shared memory, N also to HBM for K6
-//   phase 1c  one thread per point: V, g from the staged rows, damped inverse, h = V^-1 g (record to HBM for K6)
-//   phase 2   one warp per camera pair (unit, claimed longest first), lanes over the unit's point list: accumulate the
-//             unit's 6x6 block (+ rhs, gradient and diag(U) for diagonal units) in registers, reduce-scatter over
-//             the warp, add into the CTA's shared RCS. Lists, unit order and the reduction tree are fixed, so the
-//             result is deterministic.
-// At the end every CTA writes its RCS partial; fold_partials_kernel sums the partials in a fixed order (and at more
-// than one rank the sums of all ranks meet in K5, acino_sba_xchg.cuh).
+// ---- K4a: linearisation. One thread per point of the sorted numbering, one warp per round, 16 warps per SM ---------
+// residual + Jacobian of the point's k observations (the camera is the same for the whole warp: broadcast reads),
+// V = sum N^T N, g = sum N^T e, damped inverse, h = V^-1 g; everything K4b and K6 need goes to the round's staging
+// rows with coalesced 16-byte stores. Streaming: 140 MB read, 550 MB written at 119,490 frames; HBM bound.
+// Per CTA partials [cost, sum g^T h, max |g|, max |X|].
+#define SCHUR_LIN_TB 128
 template <int C>
-struct SchurSmem {
-  static constexpr int BT = schur_bt(C);
-  static constexpr int NU = rcs_units(C);
-  static constexpr int NW = BT / 32;
-  static constexpr int LEN = rcs_len(C);
-  static constexpr int BS = BT + 1;       // row stride of the staged arrays (odd: spreads the per-observation writes over banks)
-  static constexpr int NUP = (2 * NU + 7) & ~7;   // unit counts + claim order per tile, padded to a multiple of 16 bytes
-  static constexpr size_t n_doubles = ((size_t)C * CAM_STRIDE + (size_t)C * 8 * BS + 15 * BS + LEN + 1) & ~(size_t)1;   // sX is double-buffered; even: the lists start 16-byte aligned
-  static constexpr size_t list_bytes = (size_t)NU * BT * 2;     // one tile's unit lists (global layout = shared layout)
-  static constexpr int OB = 8 + C * BT;       // one tile's observation list in u16: [0] = count, [8..] = entries q*8 + c
-  static constexpr size_t bytes = n_doubles * 8 + list_bytes + NUP * 2 + (size_t)OB * 2 * 2 + 16 + NU * 2 + 16;
-};
-
-template <int C>
-__global__ void __launch_bounds__(schur_bt(C), schur_ctas_per_sm(C))
-schur_build_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict__ pid, int64_t E, int64_t P,
-                   const double* __restrict__ cams0, const double* __restrict__ cams1,
-                   const double* __restrict__ X0, const double* __restrict__ X1,
-                   const SchurLm* __restrict__ lm, SchurParams prm,
-                   double* __restrict__ rcs_partial, double* __restrict__ max_partial,
-                   const unsigned short* __restrict__ unit_lists, const unsigned short* __restrict__ unit_counts,
-                   const unsigned short* __restrict__ obs_lists, double* __restrict__ stgN, double* __restrict__ stgP,
-                   const double2* __restrict__ uvc) {
-  using L = SchurSmem<C>;
-  constexpr int BT = L::BT, BS = L::BS, NU = L::NU, NW = L::NW, LEN = L::LEN, NUP = L::NUP, OB = L::OB;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* sc = reinterpret_cast<double*>(smem_raw);
-  double* sN = sc + C * CAM_STRIDE;          // [(c*6+k)*BS + q]
-  double* sE = sN + (size_t)C * 6 * BS;      // [(c*2+k)*BS + q]
-  double* sXbuf = sE + (size_t)C * 2 * BS;   // two buffers of [k*BS + q], k<3: the next tile's points arrive by cp.async
-  double* sVi = sXbuf + 6 * BS;              // [k*BS + q], k<6: 00 01 02 11 12 22
-  double* sH = sVi + 6 * BS;                 // [k*BS + q], k<3
-  double* sS = sH + 3 * BS;                  // [LEN]
-  unsigned short* list = reinterpret_cast<unsigned short*>(sc + L::n_doubles);   // [u*BT + i] points of unit u (16-byte aligned)
-  unsigned short* ucnt = list + (size_t)NU * BT;                        // [u] points in unit u of this tile
-  unsigned short* olbuf = ucnt + NUP;                                   // two buffers of OB: the tile's observations (q*8 + c), point-major
-  int* next_unit = reinterpret_cast<int*>(olbuf + 2 * OB);              // [0] unit counter
-  unsigned char* u_c = reinterpret_cast<unsigned char*>(next_unit + 4); // [u] first camera
-  unsigned char* u_cp = u_c + NU;                                       // [u] second camera
-
+__global__ void __launch_bounds__(SCHUR_LIN_TB, 4)
+schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __restrict__ pid,
+                       const double2* __restrict__ uvs, const double* __restrict__ cams0, const double* __restrict__ cams1,
+                       const double* __restrict__ X0, const double* __restrict__ X1, const SchurLm* __restrict__ lm,
+                       SchurParams prm, double2* __restrict__ stg, double* __restrict__ lin_partial) {
+  constexpr int NCLS = 1 << C, NW = SCHUR_LIN_TB / 32;
+  __shared__ double sc[C * CAM_STRIDE];
+  __shared__ unsigned s_round0[NCLS + 1], s_blk0[NCLS + 1], s_uv0[NCLS + 1];
+  __shared__ double red[4][NW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
   const int cur = lm->cur;
   const double lam = lm->lambda;
-  const bool need_cost = (lm->iter == 0) || lm->need_cost;   // later iterations inherit the cost from the accepted trial evaluation (K6/K7)
+  const bool need_cost = (lm->iter == 0) || lm->need_cost;   // later iterations inherit the cost from the accepted trial (K6/K7)
   const double* __restrict__ cams = cur ? cams1 : cams0;
   const double* __restrict__ Xp = cur ? X1 : X0;
-
-  for (int i = tid; i < C * CAM_STRIDE; i += BT) sc[i] = cams[i];
-  for (int i = tid; i < LEN; i += BT) sS[i] = 0.0;
-  if (tid == 0) {
-    int u = C;
-    for (int c = 0; c < C; ++c) { u_c[c] = c; u_cp[c] = c; }
-    for (int c = 0; c < C; ++c)
-      for (int d = c + 1; d < C; ++d) { u_c[u] = c; u_cp[u] = d; ++u; }
-  }
+  for (int i = tid; i < C * CAM_STRIDE; i += SCHUR_LIN_TB) sc[i] = cams[i];
+  for (int i = tid; i <= NCLS; i += SCHUR_LIN_TB) { s_round0[i] = cls->round0[i]; s_blk0[i] = cls->blk0[i]; s_uv0[i] = cls->uv0[i]; }
   __syncthreads();
-
   double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0, gh_acc = 0.0;
   double cprod = 1.0;     // running product of (1+z_u)(1+z_v): sum of log1p(z) = log of the product
-  // tiles of BT EXISTING points (compacted numbering g, pid[g] = the point's index in the scene)
-  const int64_t n_tiles = skip ? 0 : (E + BT - 1) / BT;
-  // the first tile's points, mask and observation list; later tiles are fetched one tile ahead, and the scene index of
-  // this thread's point one tile further ahead still (pid_next: the copy of the point must not wait for its index)
-  unsigned m_next = 0u;
-  unsigned pid_next = 0u;
-  int buf = 0;
-  if ((int64_t)blockIdx.x < n_tiles) {
-    const int64_t g0 = (int64_t)blockIdx.x * BT + tid;
-    if (g0 < E) {
-      m_next = cmask[g0];
-      const size_t p0 = pid[g0];
-      cp_async8(sXbuf + tid, Xp + 3 * p0); cp_async8(sXbuf + BS + tid, Xp + 3 * p0 + 1); cp_async8(sXbuf + 2 * BS + tid, Xp + 3 * p0 + 2);
-    }
-    const int64_t g1 = g0 + (int64_t)gridDim.x * BT;
-    if (g1 < E) pid_next = pid[g1];
-    for (int i = tid; i < OB / 8; i += BT)
-      cp_async16(reinterpret_cast<char*>(olbuf) + 16 * i, reinterpret_cast<const char*>(obs_lists) + ((size_t)blockIdx.x * OB) * 2 + 16 * i);
-    cp_async_wait_all();
-    __syncthreads();
-  }
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    // ---------------- phase 1a: the tile's points and observation list are in shared memory and visible (they were waited
-    // for before the barrier that opened phase 2 of the previous tile): no barrier here. Issue the copies that phase 2
-    // will need: the next tile's points, list and mask (other buffers) and this tile's unit lists.
-    double* sX = sXbuf + buf * 3 * BS;
-    const unsigned short* olist = olbuf + buf * OB;
-    const unsigned m = m_next;
-    {
-      const int64_t gn = (tile + gridDim.x) * BT + tid;
-      m_next = 0u;
-      if (gn < E) {
-        double* sXn = sXbuf + (buf ^ 1) * 3 * BS;
-        m_next = cmask[gn];
-        const size_t pn = pid_next;
-        cp_async8(sXn + tid, Xp + 3 * pn); cp_async8(sXn + BS + tid, Xp + 3 * pn + 1); cp_async8(sXn + 2 * BS + tid, Xp + 3 * pn + 2);
-      }
-      const int64_t gnn = gn + (int64_t)gridDim.x * BT;
-      if (gnn < E) pid_next = pid[gnn];
-      if (tile + gridDim.x < n_tiles)
-        for (int i = tid; i < OB / 8; i += BT)
-          cp_async16(reinterpret_cast<char*>(olbuf + (buf ^ 1) * OB) + 16 * i,
-                     reinterpret_cast<const char*>(obs_lists) + ((size_t)(tile + gridDim.x) * OB) * 2 + 16 * i);
-    }
-    {   // this tile's unit lists (precomputed from the masks, schur_lists_kernel): in flight during phase 1
-      const char* src = reinterpret_cast<const char*>(unit_lists) + (size_t)tile * L::list_bytes;
-      char* dst = reinterpret_cast<char*>(list);
-      for (int i = tid; i < (int)(L::list_bytes / 16); i += BT) cp_async16(dst + 16 * i, src + 16 * i);
-      if (tid < NUP / 8) cp_async16(reinterpret_cast<char*>(ucnt) + 16 * tid,
-                                    reinterpret_cast<const char*>(unit_counts) + ((size_t)tile * NUP) * 2 + 16 * tid);
-      cp_async_commit();
-    }
-    if (m) {
-      double X = sX[tid], Y = sX[BS + tid], Z = sX[2 * BS + tid];
-      xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
-    }
-    // ---------------- phase 1b: one thread per observation: residual, Jacobian rows, robust weights
-    {
-      const int n_obs = olist[0];
-      for (int i = tid; i < n_obs; i += BT) {
-        const int e = olist[8 + i], q = e >> 3, c = e & 7;
-        const double2 ob = uvc[(size_t)tile * (C * BT) + i];
+  const unsigned n_rounds = skip ? 0u : s_round0[NCLS];
+  for (unsigned r = blockIdx.x * NW + warp; r < n_rounds; r += gridDim.x * NW) {
+    const int m = schur_class_of_round(s_round0, NCLS, r);
+    const int k = __popc(m);
+    const unsigned rr = r - s_round0[m];
+    double2* __restrict__ blk = stg + ((size_t)s_blk0[m] + (size_t)rr * schur_rows(k)) * SCHUR_ROW + lane;
+    const double2* __restrict__ ob = uvs + ((size_t)s_uv0[m] + (size_t)rr * k) * SCHUR_ROW + lane;
+    const unsigned p = pid[(size_t)r * 32 + lane];
+    const bool valid = p != 0xFFFFFFFFu;
+    double X = 0.0, Y = 0.0, Z = 0.0;
+    if (valid) { X = Xp[3 * (size_t)p]; Y = Xp[3 * (size_t)p + 1]; Z = Xp[3 * (size_t)p + 2]; }
+    double g0 = 0, g1 = 0, g2 = 0, v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0;
+    double2 o_next = ob[0];
+    int j = 0;
+#pragma unroll 1
+    for (unsigned mm = m; mm; mm &= mm - 1, ++j) {
+      const int c = __ffs(mm) - 1;
+      const double2 o = o_next;
+      if (mm & (mm - 1)) o_next = ob[(j + 1) * SCHUR_ROW];
+      double a0 = 0, a1 = 0, a2 = 0, b0 = 0, b1 = 0, b2 = 0, e0 = 0, e1 = 0;
+      if (valid) {
         double pm1 = 0.0;
-        ObsLin o = linearise_obs(sc + c * CAM_STRIDE, sX[q], sX[BS + q], sX[2 * BS + q], ob.x, ob.y, prm.inv_c2, prm.hfloor, pm1);
-        double* n = sN + (size_t)(c * 6) * BS + q;
-        n[0] = o.n0[0]; n[BS] = o.n0[1]; n[2 * BS] = o.n0[2];
-        n[3 * BS] = o.n1[0]; n[4 * BS] = o.n1[1]; n[5 * BS] = o.n1[2];
-        sE[(size_t)(c * 2) * BS + q] = o.e0;
-        sE[(size_t)(c * 2 + 1) * BS + q] = o.e1;
-        {   // the rows stay in HBM for the back-substitution kernel (K6), in the tile's list order: coalesced
-          const size_t gi = (size_t)tile * (C * BT) + i, PC = (size_t)P * C;
-          stgN[gi] = o.n0[0]; stgN[PC + gi] = o.n0[1]; stgN[2 * PC + gi] = o.n0[2];
-          stgN[3 * PC + gi] = o.n1[0]; stgN[4 * PC + gi] = o.n1[1]; stgN[5 * PC + gi] = o.n1[2];
-        }
+        const ObsLin L = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, o.x, o.y, prm.inv_c2, prm.hfloor, pm1);
+        a0 = L.n0[0]; a1 = L.n0[1]; a2 = L.n0[2]; b0 = L.n1[0]; b1 = L.n1[1]; b2 = L.n1[2]; e0 = L.e0; e1 = L.e1;
         if (need_cost) {
           cprod *= 1.0 + pm1;
           if (cprod > 1e200) { cost_acc += prm.half_c2 * log(cprod); cprod = 1.0; }
         }
+        g0 = fma(a0, e0, fma(b0, e1, g0));
+        g1 = fma(a1, e0, fma(b1, e1, g1));
+        g2 = fma(a2, e0, fma(b2, e1, g2));
+        v00 = fma(a0, a0, fma(b0, b0, v00));
+        v01 = fma(a0, a1, fma(b0, b1, v01));
+        v02 = fma(a0, a2, fma(b0, b2, v02));
+        v11 = fma(a1, a1, fma(b1, b1, v11));
+        v12 = fma(a1, a2, fma(b1, b2, v12));
+        v22 = fma(a2, a2, fma(b2, b2, v22));
       }
-      __syncthreads();
+      blk[(3 * j) * SCHUR_ROW] = make_double2(a0, a1);
+      blk[(3 * j + 1) * SCHUR_ROW] = make_double2(a2, b0);
+      blk[(3 * j + 2) * SCHUR_ROW] = make_double2(b1, b2);
+      blk[(3 * k + j) * SCHUR_ROW] = make_double2(e0, e1);
     }
-    // ---------------- phase 1c: one thread per point: V, g from the staged rows, damped inverse
-    if (m) {
-      double g0 = 0, g1 = 0, g2 = 0, v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0;
-#pragma unroll
-      for (int c = 0; c < C; ++c) {
-        if (m >> c & 1) {
-          const double* n = sN + (size_t)(c * 6) * BS + tid;
-          const double a0 = n[0], a1 = n[BS], a2 = n[2 * BS], b0 = n[3 * BS], b1 = n[4 * BS], b2 = n[5 * BS];
-          const double e0 = sE[(size_t)(c * 2) * BS + tid], e1 = sE[(size_t)(c * 2 + 1) * BS + tid];
-          g0 = fma(a0, e0, fma(b0, e1, g0));
-          g1 = fma(a1, e0, fma(b1, e1, g1));
-          g2 = fma(a2, e0, fma(b2, e1, g2));
-          v00 = fma(a0, a0, fma(b0, b0, v00));
-          v01 = fma(a0, a1, fma(b0, b1, v01));
-          v02 = fma(a0, a2, fma(b0, b2, v02));
-          v11 = fma(a1, a1, fma(b1, b1, v11));
-          v12 = fma(a1, a2, fma(b1, b2, v12));
-          v22 = fma(a2, a2, fma(b2, b2, v22));
-        }
-      }
-      Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
-      sVi[tid] = iv.i00; sVi[BS + tid] = iv.i01; sVi[2 * BS + tid] = iv.i02;
-      sVi[3 * BS + tid] = iv.i11; sVi[4 * BS + tid] = iv.i12; sVi[5 * BS + tid] = iv.i22;
-      sH[tid] = fma(iv.i00, g0, fma(iv.i01, g1, iv.i02 * g2));
-      sH[BS + tid] = fma(iv.i01, g0, fma(iv.i11, g1, iv.i12 * g2));
-      sH[2 * BS + tid] = fma(iv.i02, g0, fma(iv.i12, g1, iv.i22 * g2));
-      {   // per-point blocks for K6: V^-1, h, D, g
-        const int64_t pp = tile * BT + tid;           // = g: dense over the existing points
-        const size_t PS = (size_t)P;
-        stgP[pp] = iv.i00; stgP[PS + pp] = iv.i01; stgP[2 * PS + pp] = iv.i02;
-        stgP[3 * PS + pp] = iv.i11; stgP[4 * PS + pp] = iv.i12; stgP[5 * PS + pp] = iv.i22;
-        stgP[6 * PS + pp] = sH[tid]; stgP[7 * PS + pp] = sH[BS + tid]; stgP[8 * PS + pp] = sH[2 * BS + tid];
-        stgP[9 * PS + pp] = iv.D0; stgP[10 * PS + pp] = iv.D1; stgP[11 * PS + pp] = iv.D2;
-      }
+    double i00 = 0, i01 = 0, i02 = 0, i11 = 0, i12 = 0, i22 = 0, h0 = 0, h1 = 0, h2 = 0;
+    if (valid) {
+      const Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
+      i00 = iv.i00; i01 = iv.i01; i02 = iv.i02; i11 = iv.i11; i12 = iv.i12; i22 = iv.i22;
+      h0 = fma(i00, g0, fma(i01, g1, i02 * g2));
+      h1 = fma(i01, g0, fma(i11, g1, i12 * g2));
+      h2 = fma(i02, g0, fma(i12, g1, i22 * g2));
       // g^T h of the point block: with dX = -(h + V^-1 s) the gradient term of the predicted reduction is
-      // -g^T dX = g^T h + h^T s; the first part is summed here (RCS scalar [1]), the second in K6, so that g need not
-      // travel to K6 (24 B per point less written here and read there)
-      gh_acc += fma(g0, sH[tid], fma(g1, sH[BS + tid], g2 * sH[2 * BS + tid]));
+      // -g^T dX = g^T h + h^T s; the first part is summed here (RCS scalar [1]), the second in K6
+      gh_acc += fma(g0, h0, fma(g1, h1, g2 * h2));
       gmax_acc = fmax(gmax_acc, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+      xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
     }
-    if (tid == 0) next_unit[0] = 0;
-    cp_async_wait_all();        // the unit lists and the next tile's points / observation list have landed
-    __syncthreads();
-    if (tile + gridDim.x < n_tiles) {
-      // the next tile's observations towards L2 (its list has landed: the count is known), so that phase 1b of the next
-      // tile does not start with a full DRAM latency in every round
-      const int n_next = olbuf[(buf ^ 1) * OB];
-      const char* nx = reinterpret_cast<const char*>(uvc + (size_t)(tile + gridDim.x) * (C * BT));
-      for (int i = tid * 128; i < n_next * 16; i += BT * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + i));
-    }
-    // ---------------- phase 2: warps take units (longest first: diagonal units lead) until none is left
-    for (;;) {
-      int u = 0;
-      if (lane == 0) u = atomicAdd(next_unit, 1);
-      u = __shfl_sync(0xffffffffu, u, 0);
-      if (u >= NU) break;
-      u = ucnt[NU + u];            // claim order precomputed per tile: longest list first
-      const int c = u_c[u], cp = u_cp[u];
-      const bool diag = (c == cp);
-      // the unit's point list: tile points observed by both cameras, in point order (precomputed, copied in above)
-      const unsigned short* lst = list + (size_t)u * BT;
-      const int n = ucnt[u];
-      if (n == 0) continue;
-      double acc[RCS_UNIT];
-#pragma unroll
-      for (int i = 0; i < RCS_UNIT; ++i) acc[i] = 0.0;
-      const double* nc = sN + (size_t)(c * 6) * BS;
-      const double* ncp = sN + (size_t)(cp * 6) * BS;
-      const double* ec = sE + (size_t)(c * 2) * BS;
-#pragma unroll 1
-      for (int base = 0; base < n; base += 32) {
-        if (base + lane < n) {
-          const int q = lst[base + lane];
-          const double X = sX[q], Y = sX[BS + q], Z = sX[2 * BS + q];
-          const double n0x = nc[q], n0y = nc[BS + q], n0z = nc[2 * BS + q];
-          const double n1x = nc[3 * BS + q], n1y = nc[4 * BS + q], n1z = nc[5 * BS + q];
-          const double i00 = sVi[q], i01 = sVi[BS + q], i02 = sVi[2 * BS + q];
-          const double i11 = sVi[3 * BS + q], i12 = sVi[4 * BS + q], i22 = sVi[5 * BS + q];
-          double a0[6], a1[6];
-          a0[0] = fma(Y, n0z, -Z * n0y); a0[1] = fma(Z, n0x, -X * n0z); a0[2] = fma(X, n0y, -Y * n0x);
-          a0[3] = n0x; a0[4] = n0y; a0[5] = n0z;
-          a1[0] = fma(Y, n1z, -Z * n1y); a1[1] = fma(Z, n1x, -X * n1z); a1[2] = fma(X, n1y, -Y * n1x);
-          a1[3] = n1x; a1[4] = n1y; a1[5] = n1z;
-          // Q = N V^-1 (2x3)
-          const double q0x = fma(n0x, i00, fma(n0y, i01, n0z * i02));
-          const double q0y = fma(n0x, i01, fma(n0y, i11, n0z * i12));
-          const double q0z = fma(n0x, i02, fma(n0y, i12, n0z * i22));
-          const double q1x = fma(n1x, i00, fma(n1y, i01, n1z * i02));
-          const double q1y = fma(n1x, i01, fma(n1y, i11, n1z * i12));
-          const double q1z = fma(n1x, i02, fma(n1y, i12, n1z * i22));
-          if (diag) {
-            const double m00 = 1.0 - fma(q0x, n0x, fma(q0y, n0y, q0z * n0z));
-            const double m01 = -fma(q0x, n1x, fma(q0y, n1y, q0z * n1z));
-            const double m11 = 1.0 - fma(q1x, n1x, fma(q1y, n1y, q1z * n1z));
-            double t0[6], t1[6];
-#pragma unroll
-            for (int j = 0; j < 6; ++j) {
-              t0[j] = fma(m00, a0[j], m01 * a1[j]);
-              t1[j] = fma(m01, a0[j], m11 * a1[j]);
-            }
-            int k = 0;
-#pragma unroll
-            for (int i = 0; i < 6; ++i)
-#pragma unroll
-              for (int j = i; j < 6; ++j) { acc[k] = fma(a0[i], t0[j], fma(a1[i], t1[j], acc[k])); ++k; }
-            const double e0 = ec[q], e1 = ec[BS + q];
-            const double hx = sH[q], hy = sH[BS + q], hz = sH[2 * BS + q];
-            const double b0 = e0 - fma(n0x, hx, fma(n0y, hy, n0z * hz));
-            const double b1 = e1 - fma(n1x, hx, fma(n1y, hy, n1z * hz));
-#pragma unroll
-            for (int i = 0; i < 6; ++i) {
-              acc[21 + i] = fma(a0[i], b0, fma(a1[i], b1, acc[21 + i]));
-              acc[27 + i] = fma(a0[i], e0, fma(a1[i], e1, acc[27 + i]));
-              acc[33 + i] = fma(a0[i], a0[i], fma(a1[i], a1[i], acc[33 + i]));
-            }
-          } else {
-            const double p0x = ncp[q], p0y = ncp[BS + q], p0z = ncp[2 * BS + q];
-            const double p1x = ncp[3 * BS + q], p1y = ncp[4 * BS + q], p1z = ncp[5 * BS + q];
-            double b0[6], b1[6];
-            b0[0] = fma(Y, p0z, -Z * p0y); b0[1] = fma(Z, p0x, -X * p0z); b0[2] = fma(X, p0y, -Y * p0x);
-            b0[3] = p0x; b0[4] = p0y; b0[5] = p0z;
-            b1[0] = fma(Y, p1z, -Z * p1y); b1[1] = fma(Z, p1x, -X * p1z); b1[2] = fma(X, p1y, -Y * p1x);
-            b1[3] = p1x; b1[4] = p1y; b1[5] = p1z;
-            const double m00 = -fma(q0x, p0x, fma(q0y, p0y, q0z * p0z));
-            const double m01 = -fma(q0x, p1x, fma(q0y, p1y, q0z * p1z));
-            const double m10 = -fma(q1x, p0x, fma(q1y, p0y, q1z * p0z));
-            const double m11 = -fma(q1x, p1x, fma(q1y, p1y, q1z * p1z));
-#pragma unroll
-            for (int j = 0; j < 6; ++j) {
-              const double t0 = fma(m00, b0[j], m01 * b1[j]);
-              const double t1 = fma(m10, b0[j], m11 * b1[j]);
-#pragma unroll
-              for (int i = 0; i < 6; ++i) acc[i * 6 + j] = fma(a0[i], t0, fma(a1[i], t1, acc[i * 6 + j]));
-            }
-          }
-        }
-      }
-      warp_reduce_scatter40(acc, lane);
-      if ((lane & 3) == 0) {
-        const int e0 = 5 * ((lane >> 2) & 1) + 10 * ((lane >> 3) & 1) + 20 * ((lane >> 4) & 1);
-        double* dst = sS + u * RCS_UNIT + e0;
-#pragma unroll
-        for (int i = 0; i < 5; ++i) dst[i] += acc[i];
-      }
-    }
-    buf ^= 1;
-    __syncthreads();
+    double2* __restrict__ pt = blk + (size_t)(4 * k) * SCHUR_ROW;
+    pt[0] = make_double2(X, Y);
+    pt[SCHUR_ROW] = make_double2(Z, i00);
+    pt[2 * SCHUR_ROW] = make_double2(i01, i02);
+    pt[3 * SCHUR_ROW] = make_double2(i11, i12);
+    pt[4 * SCHUR_ROW] = make_double2(i22, h0);
+    pt[5 * SCHUR_ROW] = make_double2(h1, h2);
   }
-
-  // ---------------- CTA totals: cost (sum) and gradient / coordinate maxima
   cost_acc += prm.half_c2 * log(cprod);
-  __shared__ double red[4][32];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     cost_acc += __shfl_xor_sync(0xffffffffu, cost_acc, o);
@@ -584,18 +363,244 @@ schur_build_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict
     gmax_acc = fmax(gmax_acc, __shfl_xor_sync(0xffffffffu, gmax_acc, o));
     xmax_acc = fmax(xmax_acc, __shfl_xor_sync(0xffffffffu, xmax_acc, o));
   }
-  if (lane == 0) { red[0][warp] = cost_acc; red[1][warp] = gmax_acc; red[2][warp] = xmax_acc; red[3][warp] = gh_acc; }
+  if (lane == 0) { red[0][warp] = cost_acc; red[1][warp] = gh_acc; red[2][warp] = gmax_acc; red[3][warp] = xmax_acc; }
   __syncthreads();
   if (tid == 0) {
-    double cs = 0, gm = 0, xm = 0, gh = 0;
-    for (int w = 0; w < NW; ++w) { cs += red[0][w]; gm = fmax(gm, red[1][w]); xm = fmax(xm, red[2][w]); gh += red[3][w]; }
-    sS[NU * RCS_UNIT] = cs;
-    sS[NU * RCS_UNIT + 1] = gh;
-    max_partial[2 * blockIdx.x] = gm;
-    max_partial[2 * blockIdx.x + 1] = xm;
+    double cs = 0, gh = 0, gm = 0, xm = 0;
+    for (int w = 0; w < NW; ++w) { cs += red[0][w]; gh += red[1][w]; gm = fmax(gm, red[2][w]); xm = fmax(xm, red[3][w]); }
+    lin_partial[4 * blockIdx.x] = cs;
+    lin_partial[4 * blockIdx.x + 1] = gh;
+    lin_partial[4 * blockIdx.x + 2] = gm;
+    lin_partial[4 * blockIdx.x + 3] = xm;
   }
+}
+
+// ---- K4b: Schur accumulation --------------------------------------------------------------------------------------
+// Pure fp64 work on what K4a staged. One persistent CTA per SM walks a contiguous range of tiles (the host cuts the
+// sorted rounds into per-CTA ranges of equal work and the ranges into tiles of one class that fit a buffer); a tile is
+// one contiguous block of staging rows and arrives by cp.async into the other of two buffers while the current one is
+// used: one barrier per tile. A class with k cameras has k (k+1)/2 units (camera pairs incl. the diagonal), and EVERY
+// point of the tile belongs to every unit: the tile's unit x round grid is cut into SCHUR_NW equal contiguous pieces, one
+// per warp (static, no claims, no lists, full lanes). A warp keeps the 6x6 block of its current unit in 40 registers
+// ACROSS tiles - consecutive tiles of a class give it the same piece, and the order of its units alternates from tile
+// to tile so that it ends a tile on the unit it starts the next one with - and only when the unit changes does it
+// reduce-scatter the block over the warp (45 double shuffles) and add it to its own partial system in global memory
+// (L2 resident, touched by this warp only: deterministic). At the end the CTA folds its warps' partials in a fixed order.
+#ifndef SCHUR_NW
+#define SCHUR_NW 12
+#endif
+#define SCHUR_BUF_ROWS 220                 // staging rows (512 B) per tile buffer: 2 x 110 KB
+#define SCHUR_ACCUM_SMEM (2 * SCHUR_BUF_ROWS * SCHUR_ROW * sizeof(double2))
+// relative cost of one round of a class with k cameras in K4b (k (k+1)/2 units + the per-tile overheads): the weight the
+// host balances the per-CTA ranges with
+__host__ __device__ constexpr int schur_round_cost(int k) { return k * (k + 1) + 1; }
+struct SchurTile {
+  unsigned row0;             // first staging row
+  unsigned short rounds;     // rounds in the tile (<= SCHUR_BUF_ROWS / schur_rows(k))
+  unsigned char mask;        // the class
+  unsigned char pad;
+};
+
+__device__ __forceinline__ void schur_load_tile(double2* dst, const double2* __restrict__ stg, const SchurTile t, int tid) {
+  const int n16 = (int)t.rounds * schur_rows(__popc((unsigned)t.mask)) * SCHUR_ROW;
+  const double2* src = stg + (size_t)t.row0 * SCHUR_ROW;
+  for (int i = tid; i < n16; i += SCHUR_NW * 32) cp_async16(dst + i, src + i);
+}
+
+// rounds [ra, rb) of a diagonal unit (camera j of the class): S_cc, rhs_c, g_c, diag U_c
+__device__ __forceinline__ void schur_accum_diag(double (&acc)[RCS_UNIT], const double2* __restrict__ tb, int rows, int offN,
+                                                 int offE, int offP, int ra, int rb) {
+#pragma unroll 1
+  for (int r = ra; r < rb; ++r) {
+    const double2* __restrict__ pr = tb + (size_t)r * rows * SCHUR_ROW;
+    const double2 A0 = pr[offN], A1 = pr[offN + SCHUR_ROW], A2 = pr[offN + 2 * SCHUR_ROW];
+    const double2 P0 = pr[offP], P1 = pr[offP + SCHUR_ROW], P2 = pr[offP + 2 * SCHUR_ROW];
+    const double2 P3 = pr[offP + 3 * SCHUR_ROW], P4 = pr[offP + 4 * SCHUR_ROW], P5 = pr[offP + 5 * SCHUR_ROW];
+    const double2 E = pr[offE];
+    const double n0x = A0.x, n0y = A0.y, n0z = A1.x, n1x = A1.y, n1y = A2.x, n1z = A2.y;
+    const double X = P0.x, Y = P0.y, Z = P1.x;
+    const double i00 = P1.y, i01 = P2.x, i02 = P2.y, i11 = P3.x, i12 = P3.y, i22 = P4.x;
+    double a0[6], a1[6];
+    a0[0] = fma(Y, n0z, -Z * n0y); a0[1] = fma(Z, n0x, -X * n0z); a0[2] = fma(X, n0y, -Y * n0x);
+    a0[3] = n0x; a0[4] = n0y; a0[5] = n0z;
+    a1[0] = fma(Y, n1z, -Z * n1y); a1[1] = fma(Z, n1x, -X * n1z); a1[2] = fma(X, n1y, -Y * n1x);
+    a1[3] = n1x; a1[4] = n1y; a1[5] = n1z;
+    // Q = N V^-1 (2x3)
+    const double q0x = fma(n0x, i00, fma(n0y, i01, n0z * i02));
+    const double q0y = fma(n0x, i01, fma(n0y, i11, n0z * i12));
+    const double q0z = fma(n0x, i02, fma(n0y, i12, n0z * i22));
+    const double q1x = fma(n1x, i00, fma(n1y, i01, n1z * i02));
+    const double q1y = fma(n1x, i01, fma(n1y, i11, n1z * i12));
+    const double q1z = fma(n1x, i02, fma(n1y, i12, n1z * i22));
+    const double m00 = 1.0 - fma(q0x, n0x, fma(q0y, n0y, q0z * n0z));
+    const double m01 = -fma(q0x, n1x, fma(q0y, n1y, q0z * n1z));
+    const double m11 = 1.0 - fma(q1x, n1x, fma(q1y, n1y, q1z * n1z));
+    double t0[6], t1[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      t0[j] = fma(m00, a0[j], m01 * a1[j]);
+      t1[j] = fma(m01, a0[j], m11 * a1[j]);
+    }
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = i; j < 6; ++j) { acc[k] = fma(a0[i], t0[j], fma(a1[i], t1[j], acc[k])); ++k; }
+    const double e0 = E.x, e1 = E.y;
+    const double hx = P4.y, hy = P5.x, hz = P5.y;
+    const double b0 = e0 - fma(n0x, hx, fma(n0y, hy, n0z * hz));
+    const double b1 = e1 - fma(n1x, hx, fma(n1y, hy, n1z * hz));
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      acc[21 + i] = fma(a0[i], b0, fma(a1[i], b1, acc[21 + i]));
+      acc[27 + i] = fma(a0[i], e0, fma(a1[i], e1, acc[27 + i]));
+      acc[33 + i] = fma(a0[i], a0[i], fma(a1[i], a1[i], acc[33 + i]));
+    }
+  }
+}
+
+// rounds [ra, rb) of an off-diagonal unit (cameras j < j' of the class): S_cc' = - W_c V^-1 W_c'^T
+__device__ __forceinline__ void schur_accum_off(double (&acc)[RCS_UNIT], const double2* __restrict__ tb, int rows, int offN,
+                                                int offNp, int offP, int ra, int rb) {
+#pragma unroll 1
+  for (int r = ra; r < rb; ++r) {
+    const double2* __restrict__ pr = tb + (size_t)r * rows * SCHUR_ROW;
+    const double2 A0 = pr[offN], A1 = pr[offN + SCHUR_ROW], A2 = pr[offN + 2 * SCHUR_ROW];
+    const double2 B0 = pr[offNp], B1 = pr[offNp + SCHUR_ROW], B2 = pr[offNp + 2 * SCHUR_ROW];
+    const double2 P0 = pr[offP], P1 = pr[offP + SCHUR_ROW], P2 = pr[offP + 2 * SCHUR_ROW];
+    const double2 P3 = pr[offP + 3 * SCHUR_ROW], P4 = pr[offP + 4 * SCHUR_ROW];
+    const double n0x = A0.x, n0y = A0.y, n0z = A1.x, n1x = A1.y, n1y = A2.x, n1z = A2.y;
+    const double p0x = B0.x, p0y = B0.y, p0z = B1.x, p1x = B1.y, p1y = B2.x, p1z = B2.y;
+    const double X = P0.x, Y = P0.y, Z = P1.x;
+    const double i00 = P1.y, i01 = P2.x, i02 = P2.y, i11 = P3.x, i12 = P3.y, i22 = P4.x;
+    double a0[6], a1[6];
+    a0[0] = fma(Y, n0z, -Z * n0y); a0[1] = fma(Z, n0x, -X * n0z); a0[2] = fma(X, n0y, -Y * n0x);
+    a0[3] = n0x; a0[4] = n0y; a0[5] = n0z;
+    a1[0] = fma(Y, n1z, -Z * n1y); a1[1] = fma(Z, n1x, -X * n1z); a1[2] = fma(X, n1y, -Y * n1x);
+    a1[3] = n1x; a1[4] = n1y; a1[5] = n1z;
+    const double q0x = fma(n0x, i00, fma(n0y, i01, n0z * i02));
+    const double q0y = fma(n0x, i01, fma(n0y, i11, n0z * i12));
+    const double q0z = fma(n0x, i02, fma(n0y, i12, n0z * i22));
+    const double q1x = fma(n1x, i00, fma(n1y, i01, n1z * i02));
+    const double q1y = fma(n1x, i01, fma(n1y, i11, n1z * i12));
+    const double q1z = fma(n1x, i02, fma(n1y, i12, n1z * i22));
+    double b0[6], b1[6];
+    b0[0] = fma(Y, p0z, -Z * p0y); b0[1] = fma(Z, p0x, -X * p0z); b0[2] = fma(X, p0y, -Y * p0x);
+    b0[3] = p0x; b0[4] = p0y; b0[5] = p0z;
+    b1[0] = fma(Y, p1z, -Z * p1y); b1[1] = fma(Z, p1x, -X * p1z); b1[2] = fma(X, p1y, -Y * p1x);
+    b1[3] = p1x; b1[4] = p1y; b1[5] = p1z;
+    const double m00 = -fma(q0x, p0x, fma(q0y, p0y, q0z * p0z));
+    const double m01 = -fma(q0x, p1x, fma(q0y, p1y, q0z * p1z));
+    const double m10 = -fma(q1x, p0x, fma(q1y, p0y, q1z * p0z));
+    const double m11 = -fma(q1x, p1x, fma(q1y, p1y, q1z * p1z));
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const double t0 = fma(m00, b0[j], m01 * b1[j]);
+      const double t1 = fma(m10, b0[j], m11 * b1[j]);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) acc[i * 6 + j] = fma(a0[i], t0, fma(a1[i], t1, acc[i * 6 + j]));
+    }
+  }
+}
+
+// the warp's block goes to its own partial system: reduce-scatter over the lanes, then the 8 lanes that hold 5 entries
+// each add them (or store them, the first time the warp meets this unit) into the unit's 40 doubles
+__device__ __forceinline__ void schur_flush_unit(double (&acc)[RCS_UNIT], int lane, double* __restrict__ mypart, int gu,
+                                                 unsigned long long& touched) {
+  warp_reduce_scatter40(acc, lane);
+  if ((lane & 3) == 0) {
+    const int e0 = 5 * ((lane >> 2) & 1) + 10 * ((lane >> 3) & 1) + 20 * ((lane >> 4) & 1);
+    double* dst = mypart + gu * RCS_UNIT + e0;
+    if (touched >> gu & 1ull) {
+#pragma unroll
+      for (int i = 0; i < 5; ++i) dst[i] += acc[i];
+    } else {
+#pragma unroll
+      for (int i = 0; i < 5; ++i) dst[i] = acc[i];
+    }
+  }
+  touched |= 1ull << gu;
+#pragma unroll
+  for (int i = 0; i < RCS_UNIT; ++i) acc[i] = 0.0;
+}
+
+template <int C>
+__global__ void __launch_bounds__(SCHUR_NW * 32, 1)
+schur_accum_kernel(const SchurTile* __restrict__ tiles, const unsigned* __restrict__ tile_range,
+                   const double2* __restrict__ stg, const SchurLm* __restrict__ lm, SchurParams prm,
+                   double* __restrict__ wpart, double* __restrict__ rcs_partial) {
+  constexpr int NW = SCHUR_NW, NT = NW * 32, NU = rcs_units(C), LEN = rcs_len(C);
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double2* bufs = reinterpret_cast<double2*>(smem_raw);      // two buffers of SCHUR_BUF_ROWS rows
+  __shared__ unsigned long long s_touched[NW];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int skip = (lm->status != 0 && !prm.force);
+  const unsigned t_a = skip ? 0u : tile_range[blockIdx.x], t_b = skip ? 0u : tile_range[blockIdx.x + 1];
+  double* __restrict__ mypart = wpart + ((size_t)blockIdx.x * NW + warp) * LEN;
+  double acc[RCS_UNIT];
+#pragma unroll
+  for (int i = 0; i < RCS_UNIT; ++i) acc[i] = 0.0;
+  int cur_unit = -1;
+  unsigned long long touched = 0ull;
+  SchurTile tl = {0u, 0, 0, 0}, tn = {0u, 0, 0, 0};
+  if (t_a < t_b) {
+    tl = tiles[t_a];
+    schur_load_tile(bufs, stg, tl, tid);
+    if (t_a + 1 < t_b) tn = tiles[t_a + 1];
+  }
+  for (unsigned t = t_a; t < t_b; ++t) {
+    cp_async_wait_all();
+    __syncthreads();        // tile t has landed and is visible; every warp has left tile t-1, whose buffer is free again
+    const int par = (int)((t - t_a) & 1u);
+    const double2* __restrict__ tb = bufs + (size_t)par * SCHUR_BUF_ROWS * SCHUR_ROW;
+    const SchurTile tc = tl;
+    if (t + 1 < t_b) {
+      schur_load_tile(bufs + (size_t)(par ^ 1) * SCHUR_BUF_ROWS * SCHUR_ROW, stg, tn, tid);
+      tl = tn;
+      if (t + 2 < t_b) tn = tiles[t + 2];
+    }
+    const unsigned m = tc.mask;
+    const int k = __popc(m), rows = schur_rows(k), R = tc.rounds, U = k * (k + 1) / 2;
+    const int T = U * R, lo = warp * T / NW, hi = (warp + 1) * T / NW;
+    if (lo < hi) {
+      const int u0 = lo / R, u1 = (hi - 1) / R;
+      for (int s = 0; s <= u1 - u0; ++s) {
+        const int u = par ? u1 - s : u0 + s;
+        const int ra = (u == u0) ? lo - u0 * R : 0, rb = (u == u1) ? hi - u1 * R : R;
+        int j, jp;
+        if (u < k) { j = u; jp = u; }
+        else {
+          int q = u - k;
+          j = 0;
+          while (q >= k - 1 - j) { q -= k - 1 - j; ++j; }
+          jp = j + 1 + q;
+        }
+        const int c = __fns(m, 0, j + 1), cp = __fns(m, 0, jp + 1);
+        const int gu = (c == cp) ? c : C + c * C - c * (c + 1) / 2 + (cp - c - 1);
+        if (gu != cur_unit) {
+          if (cur_unit >= 0) schur_flush_unit(acc, lane, mypart, cur_unit, touched);
+          cur_unit = gu;
+        }
+        if (j == jp) schur_accum_diag(acc, tb + lane, rows, 3 * j * SCHUR_ROW, (3 * k + j) * SCHUR_ROW, 4 * k * SCHUR_ROW, ra, rb);
+        else schur_accum_off(acc, tb + lane, rows, 3 * j * SCHUR_ROW, 3 * jp * SCHUR_ROW, 4 * k * SCHUR_ROW, ra, rb);
+      }
+    }
+  }
+  if (cur_unit >= 0) schur_flush_unit(acc, lane, mypart, cur_unit, touched);
+  if (lane == 0) s_touched[warp] = touched;
   __syncthreads();
-  for (int i = tid; i < LEN; i += BT) rcs_partial[(size_t)blockIdx.x * LEN + i] = sS[i];
+  // the CTA's partial system: its warps' partials in warp order (fixed: deterministic)
+  const double* __restrict__ cpart = wpart + (size_t)blockIdx.x * NW * LEN;
+  for (int e = tid; e < LEN; e += NT) {
+    double s = 0.0;
+    if (e < NU * RCS_UNIT) {
+      const int u = e / RCS_UNIT;
+#pragma unroll 1
+      for (int w = 0; w < NW; ++w)
+        if (s_touched[w] >> u & 1ull) s += __ldcg(cpart + (size_t)w * LEN + e);
+    }
+    rcs_partial[(size_t)blockIdx.x * LEN + e] = s;
+  }
 }
 
 // ---- K5: reduced camera system: sum the partials, damp, Cholesky-solve in shared memory, trial cameras -----
@@ -791,75 +796,65 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
 }
 
 // ---- K6: back-substitution + trial evaluation --------------------------------------------------------------
-// Nothing is linearised twice: K4 leaves, per observation, the weighted point-Jacobian rows N (6 doubles, in the tile's
-// observation-list order) and, per point, V^-1 (6), h = V^-1 g (3), the damping diagonal D (3) and the gradient g (3).
-// One thread owns one point, without tiles, shared staging or barriers: it walks the point's own observations (they are
-// consecutive in the tile's list order, so the staged rows of a warp's points form one contiguous run per plane) for
-// s = sum N^T (N d_c), d_c = w_c x X + tau_c the camera step seen by the point; takes the step dX = -(h + V^-1 s); writes
-// the trial point; adds the predicted reduction of the point block 0.5 lam dX^T D dX - 0.5 g^T dX and max |dX|; and
-// projects the trial point with the trial cameras for the robust trial cost (a running product, one log per overflow).
-// Only the trial cameras and the camera steps sit in shared memory, so an SM holds 32 warps and the loads of different
-// points overlap: the kernel is HBM bound, and this form took it from 0.218 ms (tiles of 384 points staged in shared
-// memory, thread per observation, four barriers per tile) to 0.172 ms at 119,490 frames. The rows of the next
-// observation are requested before the current one is used. Points are visited from the last to the first (the rows
-// K4 staged last are still in the 126 MB L2). Sums per thread run in camera order; the per-CTA partials
+// Nothing is linearised twice: K4a leaves, per observation, the weighted point-Jacobian rows N and, per point, X,
+// (V + lam D)^-1 and h = V^-1 g in the round's staging rows. One thread owns one point of the sorted numbering, one warp
+// one round (32 points seen by the same k cameras: uniform trip counts, broadcast camera reads, every load a coalesced
+// 16-byte access): s = sum N^T (N d_c), d_c = w_c x X + tau_c the camera step seen by the point; the step
+// dX = -(h + V^-1 s); the trial point (scattered to its scene index); the predicted reduction of the point block
+// 0.5 lam dX^T D dX + 0.5 h^T s (D = the floored diagonal of V, rebuilt from the rows; the g^T h part was summed by
+// K4a) and max |dX|; then the trial point is projected with the trial cameras for the robust trial cost (a running
+// product, one log per overflow). Only the trial cameras and the camera steps sit in shared memory, so an SM holds 32
+// warps and the loads of different rounds overlap: HBM bound. The rows of the next observation are requested before
+// the current one is used. Sums per thread run in camera order; the per-CTA partials
 // [trial cost, predicted reduction, max |dX|, 0] are folded in a fixed order by K7: deterministic.
 #define SCHUR_BACKSUB_TB 256
-#define SCHUR_BACKSUB_MINB 4     // 64 registers: 32 warps per SM (3 CTAs of 80 registers measured 0.180 ms, 4 of 64: 0.172 ms)
+#define SCHUR_BACKSUB_MINB 4     // 64 registers: 32 warps per SM
 template <int C>
 __global__ void __launch_bounds__(SCHUR_BACKSUB_TB, SCHUR_BACKSUB_MINB)
-schur_backsub_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restrict__ pid, int64_t E, int64_t P,
-                            const double* __restrict__ cams0, const double* __restrict__ cams1,
-                            const double* __restrict__ X0, const double* __restrict__ X1, double* __restrict__ Xt0,
-                            double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
-                            const double* __restrict__ delta_c, double* __restrict__ scal_partial,
-                            const unsigned short* __restrict__ pt_start, const double* __restrict__ stgN,
-                            const double* __restrict__ stgP, const double2* __restrict__ uvc) {
-  constexpr int BT = schur_bt(C), CB = C * BT, TB = SCHUR_BACKSUB_TB, NW = TB / 32;
-  __shared__ double st[C * CAM_SMEM_STRIDE];   // trial cameras, odd stride: lanes on different cameras hit different banks
+schur_backsub_kernel(const SchurClasses* __restrict__ cls, const unsigned* __restrict__ pid,
+                     const double* __restrict__ cams0, const double* __restrict__ cams1, double* __restrict__ Xt0,
+                     double* __restrict__ Xt1, const SchurLm* __restrict__ lm, SchurParams prm,
+                     const double* __restrict__ delta_c, double* __restrict__ scal_partial,
+                     const double2* __restrict__ stg, const double2* __restrict__ uvs) {
+  constexpr int NCLS = 1 << C, TB = SCHUR_BACKSUB_TB, NW = TB / 32;
+  __shared__ double st[C * CAM_STRIDE];        // trial cameras (the camera is the same for the whole warp: broadcast)
   __shared__ double sd[6 * C + 2];             // camera steps (w, tau)
+  __shared__ unsigned s_round0[NCLS + 1], s_blk0[NCLS + 1], s_uv0[NCLS + 1];
   __shared__ double red[3][NW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
   const int cur = lm->cur;
   const double lam = lm->lambda;
   const double* __restrict__ camt = cur ? cams0 : cams1;
-  const double* __restrict__ Xp = cur ? X1 : X0;
   double* __restrict__ Xt = cur ? Xt0 : Xt1;
-  const size_t PC = (size_t)P * C, PS = (size_t)P;
-  for (int i = tid; i < C * CAM_STRIDE; i += TB) st[(i / CAM_STRIDE) * CAM_SMEM_STRIDE + i % CAM_STRIDE] = camt[i];
+  for (int i = tid; i < C * CAM_STRIDE; i += TB) st[i] = camt[i];
   if (tid < 6 * C) sd[tid] = delta_c[tid];
+  for (int i = tid; i <= NCLS; i += TB) { s_round0[i] = cls->round0[i]; s_blk0[i] = cls->blk0[i]; s_uv0[i] = cls->uv0[i]; }
   __syncthreads();
   double f_acc = 0.0, pred_acc = 0.0, dx_acc = 0.0;
   double prod = 1.0;
-  const int64_t n_groups = skip ? 0 : (E + TB - 1) / TB;
-  for (int64_t grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
-    const int64_t g = E - 1 - (grp * TB + tid);          // existing point g (compacted numbering), last to first
-    if (g < 0) continue;
-    const unsigned m = cmask[g];
-    const size_t p = pid[g];
-    const int64_t tile = g / BT;
-    const size_t gi0 = (size_t)tile * CB + pt_start[g];
-    const size_t pr = (size_t)g;
-    const double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+  const unsigned n_rounds = skip ? 0u : s_round0[NCLS];
+  for (unsigned r = blockIdx.x * NW + warp; r < n_rounds; r += gridDim.x * NW) {
+    const int m = schur_class_of_round(s_round0, NCLS, r);
     const int k = __popc(m);
-    double2 ob_n = uvc[gi0];                     // first observation of stage C: in flight during the sums
+    const unsigned rr = r - s_round0[m];
+    const double2* __restrict__ blk = stg + ((size_t)s_blk0[m] + (size_t)rr * schur_rows(k)) * SCHUR_ROW + lane;
+    const double2* __restrict__ ob = uvs + ((size_t)s_uv0[m] + (size_t)rr * k) * SCHUR_ROW + lane;
+    const unsigned p = pid[(size_t)r * 32 + lane];
+    const double2* __restrict__ pt = blk + (size_t)(4 * k) * SCHUR_ROW;
+    const double2 P0 = pt[0], P1 = pt[SCHUR_ROW];
+    const double X = P0.x, Y = P0.y, Z = P1.x;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, v00 = 0.0, v11 = 0.0, v22 = 0.0;
+    double2 ob_n = ob[0];                        // first observation of the trial evaluation: in flight during the sums
     {
-      unsigned mm = m;
-      size_t gi = gi0;
-      // the rows of the next observation are requested before the current one is used
-      double a0 = stgN[gi], a1 = stgN[PC + gi], a2 = stgN[2 * PC + gi];
-      double a3 = stgN[3 * PC + gi], a4 = stgN[4 * PC + gi], a5 = stgN[5 * PC + gi];
+      double2 A0 = blk[0], A1 = blk[SCHUR_ROW], A2 = blk[2 * SCHUR_ROW];
+      int j = 0;
 #pragma unroll 1
-      for (int j = 0; j < k; ++j) {
+      for (unsigned mm = m; mm; mm &= mm - 1, ++j) {
         const int c = __ffs(mm) - 1;
-        mm &= mm - 1;
-        const double n0x = a0, n0y = a1, n0z = a2, n1x = a3, n1y = a4, n1z = a5;
-        ++gi;
-        if (j + 1 < k) {
-          a0 = stgN[gi]; a1 = stgN[PC + gi]; a2 = stgN[2 * PC + gi];
-          a3 = stgN[3 * PC + gi]; a4 = stgN[4 * PC + gi]; a5 = stgN[5 * PC + gi];
+        const double n0x = A0.x, n0y = A0.y, n0z = A1.x, n1x = A1.y, n1y = A2.x, n1z = A2.y;
+        if (mm & (mm - 1)) {
+          A0 = blk[(3 * j + 3) * SCHUR_ROW]; A1 = blk[(3 * j + 4) * SCHUR_ROW]; A2 = blk[(3 * j + 5) * SCHUR_ROW];
         }
         const double* d = sd + 6 * c;
         const double dx = fma(d[1], Z, -d[2] * Y) + d[3];
@@ -870,36 +865,37 @@ schur_backsub_kernel(const uint8_t* __restrict__ cmask, const unsigned* __restri
         s0 += fma(n0x, y0, n1x * y1);
         s1 += fma(n0y, y0, n1y * y1);
         s2 += fma(n0z, y0, n1z * y1);
+        v00 = fma(n0x, n0x, fma(n1x, n1x, v00));      // diag V in K4a's summation order: the same D bit for bit
+        v11 = fma(n0y, n0y, fma(n1y, n1y, v11));
+        v22 = fma(n0z, n0z, fma(n1z, n1z, v22));
       }
     }
-    // the point's record is requested after the sums: 30 fewer live registers in the loop above
-    const double i00 = stgP[pr], i01 = stgP[PS + pr], i02 = stgP[2 * PS + pr];
-    const double i11 = stgP[3 * PS + pr], i12 = stgP[4 * PS + pr], i22 = stgP[5 * PS + pr];
-    const double h0 = stgP[6 * PS + pr], h1 = stgP[7 * PS + pr], h2 = stgP[8 * PS + pr];
-    const double D0 = stgP[9 * PS + pr], D1 = stgP[10 * PS + pr], D2 = stgP[11 * PS + pr];
+    // the rest of the point's record is requested after the sums: fewer live registers in the loop above
+    const double2 P2 = pt[2 * SCHUR_ROW], P3 = pt[3 * SCHUR_ROW], P4 = pt[4 * SCHUR_ROW], P5 = pt[5 * SCHUR_ROW];
+    const double i00 = P1.y, i01 = P2.x, i02 = P2.y, i11 = P3.x, i12 = P3.y, i22 = P4.x;
+    const double h0 = P4.y, h1 = P5.x, h2 = P5.y;
+    const double flo = fmax(1e-9 * fmax(v00, fmax(v11, v22)), 1e-300);
+    const double D0 = fmax(v00, flo), D1 = fmax(v11, flo), D2 = fmax(v22, flo);
     const double d0 = -(h0 + fma(i00, s0, fma(i01, s1, i02 * s2)));
     const double d1 = -(h1 + fma(i01, s0, fma(i11, s1, i12 * s2)));
     const double d2 = -(h2 + fma(i02, s0, fma(i12, s1, i22 * s2)));
-    // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta) with the undamped gradient g;
-    // for the point block -g^T dX = g^T h + h^T s, of which K4 has already summed g^T h (it reaches K7 through K5)
-    pred_acc += 0.5 * (lam * (D0 * d0 * d0 + D1 * d1 * d1 + D2 * d2 * d2) + fma(h0, s0, fma(h1, s1, h2 * s2)));
     const double xt = X + d0, yt = Y + d1, zt = Z + d2;
-    Xt[3 * p] = xt; Xt[3 * p + 1] = yt; Xt[3 * p + 2] = zt;
-    dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
-    {
-      unsigned mm = m;
-      size_t gi = gi0;
+    if (p != 0xFFFFFFFFu) {
+      // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta) with the undamped gradient g;
+      // for the point block -g^T dX = g^T h + h^T s, of which K4a has already summed g^T h (it reaches K7 through K5)
+      pred_acc += 0.5 * (lam * (D0 * d0 * d0 + D1 * d1 * d1 + D2 * d2 * d2) + fma(h0, s0, fma(h1, s1, h2 * s2)));
+      Xt[3 * (size_t)p] = xt; Xt[3 * (size_t)p + 1] = yt; Xt[3 * (size_t)p + 2] = zt;
+      dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
+      int j = 0;
 #pragma unroll 1
-      for (int j = 0; j < k; ++j) {
+      for (unsigned mm = m; mm; mm &= mm - 1, ++j) {
         const int c = __ffs(mm) - 1;
-        mm &= mm - 1;
-        const double2 ob = ob_n;
-        ++gi;
-        if (j + 1 < k) ob_n = uvc[gi];
+        const double2 o = ob_n;
+        if (mm & (mm - 1)) ob_n = ob[(j + 1) * SCHUR_ROW];
         double x, y, z, u, v;
-        to_camera(st + c * CAM_SMEM_STRIDE, xt, yt, zt, x, y, z);
-        fisheye_uv(st + c * CAM_SMEM_STRIDE, x, y, z, u, v);
-        const double fu = u - ob.x, fv = v - ob.y;
+        to_camera(st + c * CAM_STRIDE, xt, yt, zt, x, y, z);
+        fisheye_uv(st + c * CAM_STRIDE, x, y, z, u, v);
+        const double fu = u - o.x, fv = v - o.y;
         prod *= fma(fu * fu, prm.inv_c2, 1.0) * fma(fv * fv, prm.inv_c2, 1.0);
         if (prod > 1e200) { f_acc += log(prod); prod = 1.0; }      // sum of log1p(z) = log of the product; rare
       }
@@ -998,11 +994,13 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
 // fold the per-CTA partials (fixed order: deterministic): block = 8 warps x 32 entries; warp w sums the partials
 // b = w, w+8, ... of its 32 entries with two chains in flight, warp 0 combines the eight sums. One pass over
 // [n_partial][len] with len/32 CTAs instead of one CTA chasing n_partial dependent loads per entry. Block 0 also
-// folds the maxima rows (max_w columns at stride max_stride, offset max_off).
+// folds the maxima rows (max_w columns at stride max_stride, offset max_off) and, when `lin` is given, K4a's per-CTA
+// rows [cost, sum g^T h, max |g|, max |X|]: the two sums go to out_sum[scal_off], out_sum[scal_off + 1] (the RCS
+// scalars), the two maxima to out_max[0..1].
 __global__ void __launch_bounds__(256)
 fold_partials_kernel(const double* __restrict__ partial, int n_partial, int len, double* __restrict__ out_sum,
                      const double* __restrict__ maxp, int n_max, int max_w, int max_stride, int max_off,
-                     double* __restrict__ out_max) {
+                     double* __restrict__ out_max, const double* __restrict__ lin, int n_lin, int scal_off) {
   __shared__ double sm[8][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int i = blockIdx.x * 32 + lane;
@@ -1017,7 +1015,7 @@ fold_partials_kernel(const double* __restrict__ partial, int n_partial, int len,
   }
   sm[warp][lane] = s0 + s1;
   __syncthreads();
-  if (warp == 0 && i < len) {
+  if (warp == 0 && i < len && !(lin && (i == scal_off || i == scal_off + 1))) {
     double t = 0.0;
 #pragma unroll
     for (int w = 0; w < 8; ++w) t += sm[w][lane];
@@ -1030,6 +1028,23 @@ fold_partials_kernel(const double* __restrict__ partial, int n_partial, int len,
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
       if (lane == 0) out_max[c] = m;
+    }
+  }
+  if (lin && blockIdx.x == 0 && warp >= 2 && warp < 6) {
+    const int col = warp - 2;          // 0 cost, 1 g^T h (sums); 2 max |g|, 3 max |X|
+    double v = 0.0;
+    for (int b = lane; b < n_lin; b += 32) {
+      const double x = lin[4 * (size_t)b + col];
+      v = col < 2 ? v + x : fmax(v, x);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double x = __shfl_xor_sync(0xffffffffu, v, o);
+      v = col < 2 ? v + x : fmax(v, x);
+    }
+    if (lane == 0) {
+      if (col < 2) out_sum[scal_off + col] = v;
+      else out_max[col - 2] = v;
     }
   }
 }
@@ -1051,13 +1066,15 @@ __global__ void schur_init_kernel(SchurLm* lm, double lambda0) {
 
 // host-side state of the points+extrinsics solver (owned by the handle)
 struct SchurState {
-  static constexpr int PROF_MAX = 256;
+  static constexpr int PROF_MAX = 256, PROF_EV = 6;
   bool ready = false, inited = false, prof_on = false;
-  int grid_build = 0, grid_back = 0, grid_build_max = 0, grid_back_max = 0, launches = 0, prof_n = 0;
+  int sms = 148;
+  int grid_lin = 0, grid_build = 0, grid_back = 0, grid_back_max = 0, launches = 0, prof_n = 0;
   double* cams_alt = nullptr;
   double* X_alt = nullptr;
-  double* rcs_partial = nullptr;
-  double* max_partial = nullptr;
+  double* rcs_partial = nullptr;           // [sms][LEN] per-CTA partial systems of K4b
+  double* wpart = nullptr;                 // [sms * SCHUR_NW][LEN] per-warp partial systems of K4b (L2 resident)
+  double* lin_partial = nullptr;           // [4 sms][4] per-CTA rows of K4a
   double* rcs = nullptr;
   double* mx = nullptr;
   double* delta_c = nullptr;
@@ -1065,21 +1082,22 @@ struct SchurState {
   double* scal = nullptr;
   SchurLm* lm = nullptr;
   SchurLm* h_lm = nullptr;
-  unsigned short* unit_lists = nullptr;    // [tile][unit][BT]
-  unsigned short* unit_counts = nullptr;   // [tile][NUP]
   static constexpr int POLISH_CAP = 1 << 18;
   unsigned* polish_list[2] = {nullptr, nullptr};   // still-active points of the previous / this polish launch
-  unsigned short* obs_lists = nullptr;     // [tile][8 + C*BT]
-  unsigned short* pt_start = nullptr;      // [tile][BT] first observation of each point in its tile's list
-  unsigned* pid = nullptr;                 // [E] scene index of the g-th existing point
-  uint8_t* cmask = nullptr;                // [E] its observation mask
-  unsigned* exist_blocks = nullptr;        // per-1024-point counts / offsets of the compaction
+  // the sorted numbering (rebuilt by every solve from the masks)
+  unsigned* hist = nullptr;                // [2^C][n_blocks] mask histogram -> exclusive scan
+  unsigned* cls_starts = nullptr;          // [2^C] device, scan value at the first block of every class
+  unsigned* h_cls_starts = nullptr;        // pinned copy
+  SchurClasses* cls = nullptr;             // device
+  unsigned* pid = nullptr;                 // [32 n_rounds] scene index of the sorted point (0xFFFFFFFF: padding)
+  double2* uvs = nullptr;                  // observation rows
+  double2* stg = nullptr;                  // staging rows written by K4a, read by K4b and K6
+  SchurTile* tiles = nullptr;
+  unsigned* tile_range = nullptr;          // [grid_build + 1]
+  size_t cap_pid = 0, cap_uvs = 0, cap_stg = 0, cap_tiles = 0;     // capacities (grow only)
   int64_t E = 0;                           // existing points of the current solve
-  double2* uvc = nullptr;                  // [tile][C*BT] observations compacted in list order (built once per solve)
-  double* stgN = nullptr;                  // [6][P*C] N rows per observation (tile list order), written by K4 for K6
-  double* stgP = nullptr;                  // [15][P] V^-1, h, D, g per point, written by K4 for K6
-  int64_t n_tiles = 0;
-  cudaEvent_t prof_ev[4 * PROF_MAX] = {};
+  int64_t n_rounds = 0, n_tiles = 0, n_obs_rows = 0, n_stg_rows = 0;
+  cudaEvent_t prof_ev[PROF_EV * PROF_MAX] = {};
 };
 
 }  // namespace acino

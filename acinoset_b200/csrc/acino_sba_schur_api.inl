@@ -165,52 +165,37 @@ static int schur_alloc(acino_sba* h) {
   int dev = 0, sms = 148;
   ACINO_CUDA(cudaGetDevice(&dev));
   ACINO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  s.sms = sms;
   const int C = h->C;
-  const int bt = schur_bt(C), len = rcs_len(C);
-  int64_t tiles = (h->P + bt - 1) / bt;
-  { const int64_t cap = (int64_t)sms * schur_ctas_per_sm(C); s.grid_build = (int)(tiles < 1 ? 1 : (tiles < cap ? tiles : cap)); }
-  s.grid_build_max = s.grid_build;      // buffers are sized for all P slot groups existing; every solve launches what its E needs
-  int occ = 1;     // resident CTAs per SM of the persistent back-substitution kernel
+  const int len = rcs_len(C), ncls = 1 << C;
+  int occ = 1;     // resident CTAs per SM of the back-substitution kernel
   DISPATCH_C(C, (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, schur_backsub_kernel<CC>, SCHUR_BACKSUB_TB, 0)));
   if (occ < 1) occ = 1;
-  {
-    const int64_t groups = (h->P + SCHUR_BACKSUB_TB - 1) / SCHUR_BACKSUB_TB;
-    s.grid_back = (int)(groups < 1 ? 1 : (groups < (int64_t)sms * occ ? groups : (int64_t)sms * occ));
-    s.grid_back_max = s.grid_back;
-  }
+  s.grid_back_max = sms * occ;
   size_t P = h->P ? (size_t)h->P : 1;
+  const size_t nb = (P + CLS_TB - 1) / CLS_TB;
   ACINO_CUDA(cudaMalloc(&s.cams_alt, MAX_CAMS * CAM_STRIDE * sizeof(double)));
   ACINO_CUDA(cudaMalloc(&s.X_alt, P * 3 * sizeof(double)));
-  ACINO_CUDA(cudaMalloc(&s.rcs_partial, (size_t)s.grid_build * len * sizeof(double)));
-  ACINO_CUDA(cudaMalloc(&s.max_partial, (size_t)s.grid_build * 2 * sizeof(double)));
+  ACINO_CUDA(cudaMalloc(&s.rcs_partial, (size_t)sms * len * sizeof(double)));
+  ACINO_CUDA(cudaMalloc(&s.wpart, (size_t)sms * SCHUR_NW * len * sizeof(double)));
+  ACINO_CUDA(cudaMalloc(&s.lin_partial, (size_t)sms * 4 * 4 * sizeof(double)));
   ACINO_CUDA(cudaMalloc(&s.rcs, (size_t)len * sizeof(double)));
   ACINO_CUDA(cudaMalloc(&s.mx, 8 * sizeof(double)));
   ACINO_CUDA(cudaMalloc(&s.delta_c, (6 * MAX_CAMS + 8) * sizeof(double)));
-  ACINO_CUDA(cudaMalloc(&s.scal_partial, (size_t)s.grid_back * 4 * sizeof(double)));
+  ACINO_CUDA(cudaMalloc(&s.scal_partial, (size_t)s.grid_back_max * 4 * sizeof(double)));
   ACINO_CUDA(cudaMalloc(&s.scal, 8 * sizeof(double)));
   ACINO_CUDA(cudaMalloc(&s.lm, sizeof(SchurLm)));
   ACINO_CUDA(cudaMalloc(&s.polish_list[0], (size_t)SchurState::POLISH_CAP * sizeof(unsigned)));
   ACINO_CUDA(cudaMalloc(&s.polish_list[1], (size_t)SchurState::POLISH_CAP * sizeof(unsigned)));
   ACINO_CUDA(cudaMallocHost(&s.h_lm, sizeof(SchurLm)));
-  {
-    const size_t nt = tiles < 1 ? 1 : (size_t)tiles, nu = rcs_units(C), nup = (2 * nu + 7) & ~(size_t)7;
-    ACINO_CUDA(cudaMalloc(&s.unit_lists, nt * nu * bt * sizeof(unsigned short)));
-    ACINO_CUDA(cudaMalloc(&s.unit_counts, nt * nup * sizeof(unsigned short)));
-    ACINO_CUDA(cudaMalloc(&s.obs_lists, nt * (8 + (size_t)C * bt) * sizeof(unsigned short)));
-    ACINO_CUDA(cudaMalloc(&s.pt_start, nt * bt * sizeof(unsigned short)));
-    ACINO_CUDA(cudaMalloc(&s.pid, nt * bt * sizeof(unsigned)));
-    ACINO_CUDA(cudaMalloc(&s.cmask, nt * bt * sizeof(uint8_t)));
-    ACINO_CUDA(cudaMalloc(&s.exist_blocks, ((P + EXIST_TB - 1) / EXIST_TB + 1) * sizeof(unsigned)));
-    ACINO_CUDA(cudaMalloc(&s.uvc, nt * (size_t)C * bt * sizeof(double2)));
-    // rows staged by K4 for K6 (6 doubles per slot, 12 per point): 1 GB per 119,490 frames at C = 6
-    ACINO_CUDA(cudaMalloc(&s.stgN, 6 * nt * (size_t)C * bt * sizeof(double)));
-    ACINO_CUDA(cudaMalloc(&s.stgP, 12 * nt * (size_t)bt * sizeof(double)));
-    s.n_tiles = (int64_t)nt;
-  }
+  ACINO_CUDA(cudaMalloc(&s.hist, (size_t)ncls * nb * sizeof(unsigned)));
+  ACINO_CUDA(cudaMalloc(&s.cls_starts, (size_t)ncls * sizeof(unsigned)));
+  ACINO_CUDA(cudaMallocHost(&s.h_cls_starts, (size_t)ncls * sizeof(unsigned)));
+  ACINO_CUDA(cudaMalloc(&s.cls, sizeof(SchurClasses)));
+  ACINO_CUDA(cudaMalloc(&s.tile_range, (size_t)(sms + 1) * sizeof(unsigned)));
   ACINO_CUDA(cudaMemsetAsync(s.cams_alt, 0, MAX_CAMS * CAM_STRIDE * sizeof(double), h->stream));
-  ACINO_CUDA(cudaMemsetAsync(s.X_alt, 0, P * 3 * sizeof(double), h->stream));
-  DISPATCH_C(C, (cudaFuncSetAttribute(schur_build_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)SchurSmem<CC>::bytes)));
+  DISPATCH_C(C, (cudaFuncSetAttribute(schur_accum_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)SCHUR_ACCUM_SMEM)));
   ACINO_CUDA(cudaGetLastError());
   s.ready = true;
   s.inited = false;
@@ -218,10 +203,12 @@ static int schur_alloc(acino_sba* h) {
 }
 
 static void schur_free(SchurState& s) {
-  cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.max_partial); cudaFree(s.rcs);
+  cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.wpart); cudaFree(s.lin_partial); cudaFree(s.rcs);
   cudaFree(s.mx); cudaFree(s.delta_c); cudaFree(s.scal_partial); cudaFree(s.scal); cudaFree(s.lm);
-  cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.unit_lists); cudaFree(s.unit_counts); cudaFree(s.obs_lists); cudaFree(s.pt_start); cudaFree(s.pid); cudaFree(s.cmask); cudaFree(s.exist_blocks); cudaFree(s.uvc); cudaFree(s.stgN); cudaFree(s.stgP);
+  cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.hist); cudaFree(s.cls_starts); cudaFree(s.cls);
+  cudaFree(s.pid); cudaFree(s.uvs); cudaFree(s.stg); cudaFree(s.tiles); cudaFree(s.tile_range);
   if (s.h_lm) cudaFreeHost(s.h_lm);
+  if (s.h_cls_starts) cudaFreeHost(s.h_cls_starts);
   for (cudaEvent_t e : s.prof_ev) if (e) cudaEventDestroy(e);
   s = SchurState();
 }
@@ -240,37 +227,165 @@ static SchurParams make_schur_params(const acino_sba_opts* o) {
   return p;
 }
 
+// a device buffer that only grows (the sorted layout depends on the masks of the current solve)
+template <class T>
+static int schur_grow(T*& p, size_t& cap, size_t need) {
+  if (need <= cap && p) return ACINO_OK;
+  if (p) ACINO_CUDA(cudaFree(p));
+  p = nullptr;
+  cap = 0;
+  const size_t n = need + need / 16 + 64;
+  ACINO_CUDA(cudaMalloc(&p, n * sizeof(T)));
+  cap = n;
+  return ACINO_OK;
+}
+
+// Once per solve: the existing points sorted by observation mask (SchurClasses, pid), the observations in that
+// layout (uvs), and K4b's tiles and per-CTA tile ranges. The class sizes are read back (one synchronisation, 1 KB) and
+// the small tables are built on the host.
+static int schur_build_layout(acino_sba* h) {
+  SchurState& s = h->schur;
+  const int C = h->C, ncls = 1 << C;
+  const int nb = (int)((h->P + CLS_TB - 1) / CLS_TB);
+  SchurClasses hc;
+  memset(&hc, 0, sizeof(hc));
+  std::vector<unsigned long long> cnt((size_t)ncls, 0ull);
+  if (h->P > 0) {
+    DISPATCH_C(C, (cls_hist_kernel<CC><<<nb, CLS_TB, 0, h->stream>>>(h->mask, h->P, nb, s.hist)));
+    exclusive_scan_kernel<<<1, CLS_TB, 0, h->stream>>>(s.hist, (int64_t)ncls * nb, h->counters + 7);
+    cls_starts_kernel<<<(ncls + 255) / 256, 256, 0, h->stream>>>(s.hist, nb, ncls, s.cls_starts);
+    ACINO_CUDA(cudaGetLastError());
+    ACINO_CUDA(cudaMemcpyAsync(s.h_cls_starts, s.cls_starts, (size_t)ncls * sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream));
+    ACINO_CUDA(cudaMemcpyAsync(h->h_counters + 7, h->counters + 7, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    for (int m = 0; m < ncls; ++m) {
+      const unsigned long long end = (m + 1 < ncls) ? s.h_cls_starts[m + 1] : h->h_counters[7];
+      cnt[m] = end - s.h_cls_starts[m];
+      hc.off0[m] = s.h_cls_starts[m];
+    }
+  }
+  // class tables: rounds of 32 points, staging rows, observation rows (class 0 = slot groups without observations)
+  unsigned long long rounds = 0, rows = 0, orows = 0, E = 0;
+  std::vector<unsigned long long> cost0((size_t)ncls + 1, 0ull);     // work before class m, in units of schur_round_cost
+  for (int m = 0; m < ncls; ++m) {
+    const int k = __builtin_popcount((unsigned)m);
+    const unsigned long long nr = m == 0 ? 0ull : (cnt[m] + 31) / 32;
+    hc.round0[m] = (unsigned)rounds; hc.blk0[m] = (unsigned)rows; hc.uv0[m] = (unsigned)orows;
+    if (m) E += cnt[m];
+    rounds += nr; rows += nr * schur_rows(k); orows += nr * k;
+    cost0[m + 1] = cost0[m] + nr * (unsigned long long)schur_round_cost(k);
+  }
+  if (rows >= 0xFFFFFFFFull || rounds * 32 >= 0xFFFFFFFFull) { set_error("scene too large for the 32-bit row index of the staging layout"); return ACINO_EINVAL; }
+  for (int m = ncls; m <= SCHUR_MAXCLS; ++m) { hc.round0[m] = (unsigned)rounds; hc.blk0[m] = (unsigned)rows; hc.uv0[m] = (unsigned)orows; }
+  s.E = (int64_t)E; s.n_rounds = (int64_t)rounds; s.n_stg_rows = (int64_t)rows; s.n_obs_rows = (int64_t)orows;
+  // K4b: per-CTA ranges of rounds of equal work, cut into tiles of one class that fit a buffer
+  const int G = (int)(rounds < 1 ? 1 : (rounds < (unsigned long long)s.sms ? rounds : (unsigned long long)s.sms));
+  std::vector<SchurTile> tiles;
+  std::vector<unsigned> range((size_t)G + 1, 0u);
+  {
+    const unsigned long long W = cost0[ncls];
+    auto cut = [&](int b) -> unsigned long long {        // first round of CTA b
+      if (b <= 0) return 0ull;
+      if (b >= G) return rounds;
+      const unsigned long long target = (unsigned long long)(((unsigned __int128)W * (unsigned)b) / (unsigned)G);
+      int m = 0;
+      while (m + 1 < ncls && cost0[m + 1] <= target) ++m;
+      const int k = __builtin_popcount((unsigned)m);
+      unsigned long long r = hc.round0[m] + (target - cost0[m]) / (unsigned long long)schur_round_cost(k);
+      const unsigned long long rend = (m + 1 <= ncls) ? hc.round0[m + 1] : rounds;
+      return r < rend ? r : rend;
+    };
+    int m = 0;
+    for (int b = 0; b < G; ++b) {
+      range[b] = (unsigned)tiles.size();
+      unsigned long long r = cut(b);
+      const unsigned long long r_end = cut(b + 1);
+      while (r < r_end) {
+        while (hc.round0[m + 1] <= r) ++m;              // class of round r
+        const int k = __builtin_popcount((unsigned)m);
+        const unsigned long long seg_end = hc.round0[m + 1] < r_end ? hc.round0[m + 1] : r_end;
+        const unsigned long long n = seg_end - r, cap = SCHUR_BUF_ROWS / schur_rows(k);
+        const unsigned long long nt = (n + cap - 1) / cap, base = n / nt, rem = n % nt;
+        for (unsigned long long t = 0; t < nt; ++t) {
+          const unsigned long long R = base + (t < rem ? 1 : 0);
+          SchurTile tl;
+          tl.row0 = (unsigned)(hc.blk0[m] + (r - hc.round0[m]) * schur_rows(k));
+          tl.rounds = (unsigned short)R; tl.mask = (unsigned char)m; tl.pad = 0;
+          tiles.push_back(tl);
+          r += R;
+        }
+      }
+    }
+    range[G] = (unsigned)tiles.size();
+  }
+  s.n_tiles = (int64_t)tiles.size();
+  s.grid_build = G;
+  { const int64_t g = (s.n_rounds + 3) / 4; s.grid_lin = (int)(g < 1 ? 1 : (g < 4 * (int64_t)s.sms ? g : 4 * (int64_t)s.sms)); }
+  { const int64_t g = (s.n_rounds + 7) / 8; s.grid_back = (int)(g < 1 ? 1 : (g < s.grid_back_max ? g : s.grid_back_max)); }
+  int rc;
+  if ((rc = schur_grow(s.pid, s.cap_pid, (size_t)rounds * 32 + 32))) return rc;
+  if ((rc = schur_grow(s.uvs, s.cap_uvs, (size_t)orows * SCHUR_ROW + SCHUR_ROW))) return rc;
+  if ((rc = schur_grow(s.stg, s.cap_stg, (size_t)rows * SCHUR_ROW + SCHUR_ROW))) return rc;
+  if ((rc = schur_grow(s.tiles, s.cap_tiles, tiles.size() + 1))) return rc;
+  ACINO_CUDA(cudaMemcpyAsync(s.cls, &hc, sizeof(hc), cudaMemcpyHostToDevice, h->stream));
+  if (!tiles.empty()) ACINO_CUDA(cudaMemcpyAsync(s.tiles, tiles.data(), tiles.size() * sizeof(SchurTile), cudaMemcpyHostToDevice, h->stream));
+  ACINO_CUDA(cudaMemcpyAsync(s.tile_range, range.data(), range.size() * sizeof(unsigned), cudaMemcpyHostToDevice, h->stream));
+  if (rounds > 0) {
+    ACINO_CUDA(cudaMemsetAsync(s.pid, 0xFF, (size_t)rounds * 32 * sizeof(unsigned), h->stream));
+    DISPATCH_C(C, (cls_scatter_kernel<CC><<<nb, CLS_TB, 0, h->stream>>>(h->mask, h->P, nb, s.hist, s.cls, s.pid)));
+    const int64_t gf = (s.n_rounds + 7) / 8;
+    DISPATCH_C(C, (cls_fill_obs_kernel<CC><<<(unsigned)(gf < 4096 ? gf : 4096), 256, 0, h->stream>>>(s.cls, s.pid, h->uv, s.uvs)));
+    ACINO_CUDA(cudaGetLastError());
+  }
+  ACINO_CUDA(cudaStreamSynchronize(h->stream));      // the host tables above are pageable: copied before they go out of scope
+  return ACINO_OK;
+}
+
 static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
   SchurState& s = h->schur;
   schur_init_kernel<<<1, 1, 0, h->stream>>>(s.lm, o->lambda0);
   ACINO_CUDA(cudaGetLastError());
-  // the camera-pair point lists of every tile follow from the masks alone: (re)built once per solve (the observation
-  // mask may be a borrowed device buffer that changed since the last solve; it must not change during one)
+  // The alternate point buffer starts as a copy of the points: K6 writes trial rows for existing points only, so the
+  // rows of points without observations must already hold what the caller set (they are never touched by the solve,
+  // as in the reference, where scipy leaves parameters without residuals unchanged), whatever the number of accepted steps.
+  if (h->P) ACINO_CUDA(cudaMemcpyAsync(s.X_alt, h->X, (size_t)h->P * 3 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  // the sorted layout follows from the masks alone: (re)built once per solve (the observation mask may be a borrowed
+  // device buffer that changed since the last solve; it must not change during one)
+  int rc = schur_build_layout(h);
+  if (rc) return rc;
   if (h->P > 0) {
-    // existing points compacted (pid, cmask, E), then the per-tile lists over tiles of schur_bt existing points
-    const int nb = (int)((h->P + EXIST_TB - 1) / EXIST_TB);
-    exist_count_kernel<<<nb, EXIST_TB, 0, h->stream>>>(h->mask, h->P, s.exist_blocks);
-    exist_scan_kernel<<<1, EXIST_TB, 0, h->stream>>>(s.exist_blocks, nb, h->counters + 7);
-    exist_scatter_kernel<<<nb, EXIST_TB, 0, h->stream>>>(h->mask, h->P, s.exist_blocks, s.pid, s.cmask);
-    ACINO_CUDA(cudaGetLastError());
-    ACINO_CUDA(cudaMemcpyAsync(h->h_counters + 7, h->counters + 7, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
-    ACINO_CUDA(cudaStreamSynchronize(h->stream));
-    s.E = (int64_t)h->h_counters[7];
-    const int bt = schur_bt(h->C);
-    s.n_tiles = (s.E + bt - 1) / bt;
-    s.grid_build = (int)(s.n_tiles < 1 ? 1 : (s.n_tiles < s.grid_build_max ? s.n_tiles : s.grid_build_max));
-    const int64_t groups = (s.E + SCHUR_BACKSUB_TB - 1) / SCHUR_BACKSUB_TB;
-    s.grid_back = (int)(groups < 1 ? 1 : (groups < s.grid_back_max ? groups : s.grid_back_max));
-    if (s.n_tiles > 0)
-      DISPATCH_C(h->C, (schur_lists_kernel<CC><<<(unsigned)s.n_tiles, schur_bt(CC), 0, h->stream>>>(
-                           s.cmask, s.pid, s.E, s.unit_lists, s.unit_counts, s.obs_lists, s.pt_start, h->uv, s.uvc)));
-    ACINO_CUDA(cudaGetLastError());
-    int rc = ensure_point_order(h, true);      // K3 (refinement, polishing) visits the points by observation count
+    rc = ensure_point_order(h, true);      // K3 (refinement, polishing) visits the points by observation count
     if (rc) return rc;
   }
   s.inited = true;
   s.launches = 0;
   s.prof_n = 0;
+  return ACINO_OK;
+}
+
+// K4a + K4b + fold: linearisation at the current parameters and the rank's reduced camera system in s.rcs / s.mx
+static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumulate, bool prof) {
+  SchurState& s = h->schur;
+  const int C = h->C, len = rcs_len(C);
+  cudaStream_t st = h->stream;
+  cudaEvent_t* ev = s.prof_ev + SchurState::PROF_EV * s.prof_n;
+  if (prof) ACINO_CUDA(cudaEventRecord(ev[0], st));
+  DISPATCH_C(C, (schur_linearise_kernel<CC><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
+                    s.cls, s.pid, s.uvs, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.stg, s.lin_partial)));
+  ACINO_CUDA(cudaGetLastError());
+  if (prof) ACINO_CUDA(cudaEventRecord(ev[1], st));
+  ++s.launches;
+  if (accumulate) {
+    DISPATCH_C(C, (schur_accum_kernel<CC><<<s.grid_build, SCHUR_NW * 32, SCHUR_ACCUM_SMEM, st>>>(
+                      s.tiles, s.tile_range, s.stg, s.lm, prm, s.wpart, s.rcs_partial)));
+    ACINO_CUDA(cudaGetLastError());
+    ++s.launches;
+  }
+  if (prof) ACINO_CUDA(cudaEventRecord(ev[2], st));
+  fold_partials_kernel<<<(len + 31) / 32, 256, 0, st>>>(s.rcs_partial, accumulate ? s.grid_build : 0, len, s.rcs, nullptr, 0, 0, 0, 0,
+                                                        s.mx, s.lin_partial, s.grid_lin, rcs_units(C) * RCS_UNIT);
+  ACINO_CUDA(cudaGetLastError());
+  ++s.launches;
   return ACINO_OK;
 }
 
@@ -280,17 +395,9 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   const int C = h->C, len = rcs_len(C);
   cudaStream_t st = h->stream;
   const bool prof = s.prof_on && s.prof_n < SchurState::PROF_MAX;
-  if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n], st));
-  DISPATCH_C(C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, st>>>(
-                    s.cmask, s.pid, s.E, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.rcs_partial, s.max_partial, s.unit_lists,
-                    s.unit_counts, s.obs_lists, s.stgN, s.stgP, s.uvc)));
-  ACINO_CUDA(cudaGetLastError());
-  if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 1], st));
-  ++s.launches;
-  fold_partials_kernel<<<(len + 31) / 32, 256, 0, st>>>(s.rcs_partial, s.grid_build, len, s.rcs, s.max_partial, s.grid_build,
-                                                        2, 2, 0, s.mx);
-  ACINO_CUDA(cudaGetLastError());
-  ++s.launches;
+  cudaEvent_t* ev = s.prof_ev + SchurState::PROF_EV * s.prof_n;
+  int rc = schur_launch_build(h, prm, true, prof);
+  if (rc) return rc;
   PeerXchg& px = h->xchg;
   if (h->nranks > 1 && px.enabled) {
     // peer exchange: push this rank's folded system into every rank's slot; K5 waits for all ranks and adds the rows
@@ -316,12 +423,11 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   }
   ++s.launches;
   ACINO_CUDA(cudaGetLastError());
-  if (prof) ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 2], st));
+  if (prof) ACINO_CUDA(cudaEventRecord(ev[3], st));
   DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, SCHUR_BACKSUB_TB, 0, st>>>(
-                    s.cmask, s.pid, s.E, h->P, h->cams, s.cams_alt, h->X, s.X_alt, h->X, s.X_alt, s.lm, prm, s.delta_c, s.scal_partial,
-                    s.pt_start, s.stgN, s.stgP, s.uvc)));
+                    s.cls, s.pid, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.delta_c, s.scal_partial, s.stg, s.uvs)));
   ACINO_CUDA(cudaGetLastError());
-  if (prof) { ACINO_CUDA(cudaEventRecord(s.prof_ev[4 * s.prof_n + 3], st)); ++s.prof_n; }
+  if (prof) { ACINO_CUDA(cudaEventRecord(ev[4], st)); ++s.prof_n; }
   ++s.launches;
   if (h->nranks > 1 && px.enabled) {
     const unsigned long long seq = ++px.seq_b;
@@ -333,7 +439,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
     s.launches += 2;
   } else if (h->nranks > 1) {
     fold_partials_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, 4, s.scal, s.scal_partial, s.grid_back, 1, 4, 2,
-                                            s.scal + 4);
+                                            s.scal + 4, nullptr, 0, 0);
     ACINO_CUDA(cudaGetLastError());
     ACINO_NCCL(g_nccl.GroupStart());
     ACINO_NCCL(g_nccl.AllReduce(s.scal, s.scal, 4, kNcclDouble, kNcclSum, h->nccl_comm, st));
@@ -515,17 +621,12 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     SchurParams pf = prm;
     pf.force = 1;
     const int len = rcs_len(h->C);
-    DISPATCH_C(h->C, (schur_build_kernel<CC><<<s.grid_build, schur_bt(CC), SchurSmem<CC>::bytes, h->stream>>>(
-                         s.cmask, s.pid, s.E, h->P, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, pf, s.rcs_partial, s.max_partial,
-                         s.unit_lists, s.unit_counts, s.obs_lists, s.stgN, s.stgP, s.uvc)));
-    ACINO_CUDA(cudaGetLastError());
-    fold_partials_kernel<<<(len + 31) / 32, 256, 0, h->stream>>>(s.rcs_partial, s.grid_build, len, s.rcs, s.max_partial,
-                                                                 s.grid_build, 2, 2, 0, s.mx);
-    ACINO_CUDA(cudaGetLastError());
+    rc = schur_launch_build(h, pf, false, false);      // K4a alone: the cost is its sum
+    if (rc) return rc;
     if (h->nranks > 1) ACINO_NCCL(g_nccl.AllReduce(s.rcs, s.rcs, (size_t)len, kNcclDouble, kNcclSum, h->nccl_comm, h->stream));
     schur_refresh_cost_kernel<<<1, 1, 0, h->stream>>>(s.lm, s.rcs, rcs_units(h->C) * RCS_UNIT);
     ACINO_CUDA(cudaGetLastError());
-    s.launches += 3;
+    ++s.launches;
   }
   rc = schur_sync_current(h);
   if (rc) return rc;
@@ -622,7 +723,7 @@ int acino_sba_profile(acino_sba_t* h, int enable) {
   H_CHECK(h);
   SchurState& s = h->schur;
   if (enable) {
-    for (int i = 0; i < 4 * SchurState::PROF_MAX; ++i)
+    for (int i = 0; i < SchurState::PROF_EV * SchurState::PROF_MAX; ++i)
       if (!s.prof_ev[i]) ACINO_CUDA(cudaEventCreate(&s.prof_ev[i]));
   }
   s.prof_on = enable != 0;
@@ -630,21 +731,32 @@ int acino_sba_profile(acino_sba_t* h, int enable) {
   return ACINO_OK;
 }
 
-int acino_sba_profile_read(acino_sba_t* h, double* build_ms, double* backsub_ms, int* n_iterations) {
+int acino_sba_profile_read_kernels(acino_sba_t* h, double* ms4, int* n_iterations) {
   H_CHECK(h);
+  ARG_CHECK(ms4, "profile_read_kernels");
   SchurState& s = h->schur;
   ACINO_CUDA(cudaStreamSynchronize(h->stream));
-  double b = 0, k = 0;
+  double acc[4] = {0, 0, 0, 0};
   for (int i = 0; i < s.prof_n; ++i) {
-    float ms = 0;
-    ACINO_CUDA(cudaEventElapsedTime(&ms, s.prof_ev[4 * i], s.prof_ev[4 * i + 1]));
-    b += ms;
-    ACINO_CUDA(cudaEventElapsedTime(&ms, s.prof_ev[4 * i + 2], s.prof_ev[4 * i + 3]));
-    k += ms;
+    cudaEvent_t* ev = s.prof_ev + SchurState::PROF_EV * i;
+    const int a[4] = {0, 1, 2, 3}, b[4] = {1, 2, 3, 4};      // K4a | K4b | fold + exchange + K5 | K6
+    for (int k = 0; k < 4; ++k) {
+      float ms = 0;
+      ACINO_CUDA(cudaEventElapsedTime(&ms, ev[a[k]], ev[b[k]]));
+      acc[k] += ms;
+    }
   }
-  if (build_ms) *build_ms = s.prof_n ? b / s.prof_n : 0.0;
-  if (backsub_ms) *backsub_ms = s.prof_n ? k / s.prof_n : 0.0;
+  for (int k = 0; k < 4; ++k) ms4[k] = s.prof_n ? acc[k] / s.prof_n : 0.0;
   if (n_iterations) *n_iterations = s.prof_n;
+  return ACINO_OK;
+}
+
+int acino_sba_profile_read(acino_sba_t* h, double* build_ms, double* backsub_ms, int* n_iterations) {
+  double ms4[4];
+  int rc = acino_sba_profile_read_kernels(h, ms4, n_iterations);
+  if (rc) return rc;
+  if (build_ms) *build_ms = ms4[0] + ms4[1];
+  if (backsub_ms) *backsub_ms = ms4[3];
   return ACINO_OK;
 }
 

@@ -164,7 +164,10 @@ class SbaSolver:
         """Average device ms of the build (K4) and back-substitution (K6) kernels over the profiled iterations."""
         b, k, n = ct.c_double(), ct.c_double(), ct.c_int()
         _capi.check(_capi.lib().acino_sba_profile_read(self._h, ct.byref(b), ct.byref(k), ct.byref(n)))
-        return dict(build_ms=b.value, backsub_ms=k.value, iterations=n.value)
+        ms4 = np.zeros(4)
+        _capi.check(_capi.lib().acino_sba_profile_read_kernels(self._h, _capi.ptr(ms4), ct.byref(n)))
+        return dict(build_ms=b.value, backsub_ms=k.value, iterations=n.value, linearise_ms=float(ms4[0]),
+                    accumulate_ms=float(ms4[1]), solve_ms=float(ms4[2]))
 
     def lm_state(self):
         out = np.empty(16)

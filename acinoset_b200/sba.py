@@ -83,6 +83,21 @@ def cost_func_points_only(params, n_points, point_3d_indices, camera_indices, k_
     return f
 
 
+def jacobian_points_extrinsics(points_3d, point_3d_indices, camera_indices, k_arr, d_arr, r_arr, t_arr):
+    """The analytic Jacobian behind bundle_adjust_points_and_extrinsics (the reference differentiates
+    cost_func_points_extrinsics, src/lib/sba.py:142-146, numerically): (n_obs, 2, 9) = d(u, v)/d(w, tau, X) per observation,
+    (w, tau) the world-frame twist of the observing camera (R <- R Exp(w), t <- t + R tau), X the observed point."""
+    _capi.require_gpu()
+    X = _capi.f64(points_3d).reshape(-1, 3)
+    pidx = np.ascontiguousarray(point_3d_indices, dtype=np.int32).ravel()
+    cidx = np.ascontiguousarray(camera_indices, dtype=np.int32).ravel()
+    cams = _capi.pack_cams(k_arr, d_arr, r_arr, t_arr)
+    J = np.empty((len(pidx), 2, 9))
+    _capi.check(_capi.lib().acino_jacobian_list(_capi.ptr(X), len(X), _capi.ptr(pidx), _capi.ptr(cidx), len(pidx),
+                                                _capi.ptr(cams), len(cams), _capi.ptr(J)))
+    return J
+
+
 def params_to_points_extrinsics(params, n_cams, n_points):
     """src/lib/sba.py:25-32; the Rodrigues conversion runs in the CUDA library."""
     params = _capi.f64(params)
@@ -257,10 +272,25 @@ def bundle_adjust_board_points_only(img_pts_arr, fnames_arr, board_shape, k_arr,
 
 # ==========  BACK-END FUNCTION MANAGERS (src/lib/sba.py:211-313) ==========
 
+def merge_board_and_manual_points(board, manual, reference_ids=False):
+    """The merge of src/lib/sba.py:254-258: board = (points_2d, points_3d, point_3d_indices, camera_indices) of the
+    checkerboard corners, manual = the same of the manually labelled points; returns the four merged arrays.
+
+    reference_ids=True reproduces the reference bit for bit: the manual ids are offset by ``point_3d_indices.max()``
+    (sba.py:257), so the first manual point shares its id - i.e. its 3-D parameter - with the last board corner and
+    the last manual row of points_3d is referenced by nothing. reference_ids=False (the default of this package) offsets
+    by ``max() + 1``: no two physical points are merged. With no manual points both agree."""
+    p2d, p3d, pidx, pcam = board
+    m2d, m3d, midx, mcam = manual
+    offset = (pidx.max() + (0 if reference_ids else 1)) if len(pidx) else 0
+    return (np.append(p2d, m2d, axis=0), np.append(p3d, m3d, axis=0), np.append(pidx, midx + offset, axis=0),
+            np.append(pcam, mcam, axis=0))
+
+
 def _sba_board_points(scene_fpath, points_fpaths, manual_points_fpath, out_fpath, triangulate_func, project_func,
-                      camera_indices=None, manual_points_only=False):
+                      camera_indices=None, manual_points_only=False, reference_ids=False):
     """src/lib/sba.py:211-282: extrinsic calibration refinement from checkerboard (and optional manual) points;
-    writes the refined scene JSON and returns the residual dict."""
+    writes the refined scene JSON and returns the residual dict. ``reference_ids``: see merge_board_and_manual_points."""
     from .utils import load_points, load_manual_points
     img_pts_arr, fnames_arr, board_shape = [], [], None
     if camera_indices is None:
@@ -273,23 +303,16 @@ def _sba_board_points(scene_fpath, points_fpaths, manual_points_fpath, out_fpath
     assert len(k_arr) == len(img_pts_arr)
     if manual_points_fpath is not None:
         manual_points, _manual_fnames, *_ = load_manual_points(manual_points_fpath)
-        m2d, m3d, midx, mcam = prepare_manual_points_for_bundle_adjustment(manual_points, k_arr, d_arr, r_arr, t_arr,
-                                                                           triangulate_func)
+        manual = prepare_manual_points_for_bundle_adjustment(manual_points, k_arr, d_arr, r_arr, t_arr, triangulate_func)
         if manual_points_only:
             print('bundle_adjust_board_points_and_extrinsics (with manual points only)')
-            obj_pts, r_arr, t_arr, res = bundle_adjust_points_and_extrinsics(m2d, m3d, midx, mcam, k_arr, d_arr, r_arr, t_arr,
-                                                                             project_func)
+            obj_pts, r_arr, t_arr, res = bundle_adjust_points_and_extrinsics(*manual, k_arr, d_arr, r_arr, t_arr, project_func)
         else:
             print('bundle_adjust_board_points_and_extrinsics (with manual points)')
-            p2d, p3d, pidx, pcam = prepare_calib_board_data_for_bundle_adjustment(img_pts_arr, fnames_arr, board_shape, k_arr,
-                                                                                  d_arr, r_arr, t_arr, triangulate_func)
-            # The reference offsets the manual ids by point_3d_indices.max() (sba.py:257), which makes the first manual
-            # point share an id with the last board corner. The ids here start one past it, so no two physical points
-            # are merged; with no manual points both agree.
-            offset = (pidx.max() + 1) if len(pidx) else 0
+            board = prepare_calib_board_data_for_bundle_adjustment(img_pts_arr, fnames_arr, board_shape, k_arr, d_arr, r_arr,
+                                                                   t_arr, triangulate_func)
             obj_pts, r_arr, t_arr, res = bundle_adjust_points_and_extrinsics(
-                np.append(p2d, m2d, axis=0), np.append(p3d, m3d, axis=0), np.append(pidx, midx + offset, axis=0),
-                np.append(pcam, mcam, axis=0), k_arr, d_arr, r_arr, t_arr, project_func)
+                *merge_board_and_manual_points(board, manual, reference_ids), k_arr, d_arr, r_arr, t_arr, project_func)
     else:
         print('bundle_adjust_board_points_and_extrinsics')
         p2d, p3d, pidx, pcam = prepare_calib_board_data_for_bundle_adjustment(img_pts_arr, fnames_arr, board_shape, k_arr,

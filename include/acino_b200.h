@@ -56,6 +56,13 @@ int acino_project_all(const double* X, int64_t N, const double* cams24, int n_ca
 int acino_residuals_list(const double* X, int64_t n_points, const int32_t* point_idx, const int32_t* cam_idx,
                          const double* points_2d, int64_t n_obs, const double* cams24, int n_cams, double* f);
 
+/* The analytic Jacobian of that residual (the reference has none: scipy differentiates cost_func_points_extrinsics,
+ * src/lib/sba.py:142-146, by forward differences), for inspection and tests: per observation J double[2][9] =
+ * d(u, v) / d(w, tau, X), (w, tau) the world-frame twist of the camera (R <- R Exp(w), t <- t + R tau) the solver
+ * steps in, X the point. Host pointers. */
+int acino_jacobian_list(const double* X, int64_t n_points, const int32_t* point_idx, const int32_t* cam_idx, int64_t n_obs,
+                        const double* cams24, int n_cams, double* J);
+
 /* N3 — the residual vector of adjust_extrinsics_manual_points, src/lib/calib.py:224-256, for n_batch candidate
  * corrections at once (the current (rvec, t) and scipy's forward differences). img_pts double[n_points][n_cams][2];
  * cameras in correct_cams take (r R^T, t - r t_corr); every pair (a, b) of cam_pairs triangulates all points (K2), every
@@ -160,9 +167,11 @@ int acino_sba_reset_state(acino_sba_t* h);
 void* acino_sba_stream(acino_sba_t* h);
 
 /* per-kernel device times of acino_sba_iterate in points+extrinsics mode (CUDA events on the handle's stream):
- * enable, run <=256 iterations, read the averages in ms (build = K4 residual+Jacobian+Schur, backsub = K6). */
+ * enable, run <=256 iterations, read the averages in ms (build = K4a linearisation + K4b Schur accumulation,
+ * backsub = K6). profile_read_kernels: ms4 = [K4a, K4b, fold + exchange + K5, K6]. */
 int acino_sba_profile(acino_sba_t* h, int enable);
 int acino_sba_profile_read(acino_sba_t* h, double* build_ms, double* backsub_ms, int* n_iterations);
+int acino_sba_profile_read_kernels(acino_sba_t* h, double* ms4, int* n_iterations);
 /* LM state after iterate / solve: out[0]=cost, [1]=lambda, [2]=gmax, [3]=iterations, [4]=accepted, [5]=status,
  * [6]=trial cost, [7]=predicted reduction, [8]=gain ratio, [9]=max |dx|, [10]=max |x|, [11]=nu, [12]=relative decrease of
  * the last accepted step, [13]=rejected, [14]=Cholesky failures, [15]=cost at the first linearisation */

@@ -198,3 +198,62 @@ def test_oracle_ekf_measurement_vs_reference_golden(golden_dir):
         assert np.abs(H - g[f'{mode}_f64_H']).max() < 1e-6          # differences of ~1e3 px numbers divided by 1e-3
         # the reference's in-loop float32 pose gives the same Jacobian up to its own rounding noise
         assert np.abs(H - g[f'{mode}_f32_H']).max() < 2.0
+
+
+def test_block_oracle_equals_dense_oracle():
+    """oracle/sba_lm_np.BlockProblem (block-sparse, used at > 1000 points) states the same normal equations, reduced
+    camera system and step as the dense Problem."""
+    import numpy as np
+    from oracle import sba_lm_np as lm, fisheye_np as fe
+    from acinoset_b200 import synth
+    k, d, r, t, _ = synth.load_rig()
+    rng = np.random.default_rng(0)
+    P = 14
+    Xg = np.stack([rng.uniform(-1, 5, P), rng.uniform(5, 8, P), rng.uniform(0, 1, P)], 1)
+    pidx, cidx, obs = [], [], []
+    for p in range(P):
+        cams = [c for c in range(6) if rng.uniform() < 0.6]
+        if len(cams) < 2:
+            cams = [0, 1]
+        for c in cams:
+            pidx.append(p); cidx.append(c)
+            obs.append(fe.project_points_fisheye(Xg[p], k[c], d[c], r[c], t[c])[0] + rng.normal(0, 2.0, 2))
+    obs, pidx, cidx = np.array(obs), np.array(pidx), np.array(cidx)
+    X0 = Xg + rng.normal(0, 0.01, Xg.shape)
+    tt = np.asarray(t).reshape(6, 3)
+    dense_p = lm.Problem(obs, pidx, cidx, k, d, P, 1.0)
+    block_p = lm.BlockProblem(obs, pidx, cidx, k, d, P, 1.0, hess_floor=0.1)
+    H, g, F = dense_p.linearise(r, tt, X0)
+    L = block_p.linearise(r, tt, X0)
+    assert abs(F - L['F']) <= 1e-13 * F
+    assert np.abs(dense_p.residuals(r, tt, X0) - block_p.residuals(r, tt, X0)).max() < 1e-10
+    for lam in (1e-2, 1.0):
+        dc, dp, pred = dense_p.step(H, g, lam)
+        s = block_p.step(L, lam)
+        S_dense = dense_p.reduced_system(H, g, lam)[0]
+        assert np.abs(S_dense - s['S']).max() <= 1e-10 * np.abs(S_dense).max()
+        assert np.abs(dc - s['dc']).max() < 1e-11 and np.abs(dp - s['dp'].ravel()).max() < 1e-11
+        assert abs(pred - s['pred']) <= 1e-11 * abs(pred)
+
+
+def test_board_manual_merge_ids_vs_reference_golden(golden_dir):
+    """src/lib/sba.py:254-258 through the real _sba_board_points (oracle/make_golden_merge.py records what its two
+    prepare_* calls returned and what it passed to the solver): reference_ids=True reproduces the merged arrays bit for
+    bit, including the id the first manual point shares with the last board corner; the default keeps them apart."""
+    import os
+    import numpy as np
+    from acinoset_b200 import sba
+    g = np.load(os.path.join(golden_dir, 'golden_board_merge.npz'))
+    board = tuple(g[f'board_{n}'] for n in ('points_2d', 'points_3d', 'point_indices', 'camera_indices'))
+    manual = tuple(g[f'manual_{n}'] for n in ('points_2d', 'points_3d', 'point_indices', 'camera_indices'))
+    ref = sba.merge_board_and_manual_points(board, manual, reference_ids=True)
+    for a, n in zip(ref, ('points_2d', 'points_3d', 'point_indices', 'camera_indices')):
+        assert a.dtype == g[f'merged_{n}'].dtype or n.endswith('indices')
+        assert np.array_equal(a, g[f'merged_{n}'])
+    assert ref[2][len(board[2])] == board[2].max()                       # the collision of the reference
+    own = sba.merge_board_and_manual_points(board, manual)
+    assert np.array_equal(own[2][:len(board[2])], board[2])
+    assert np.array_equal(own[2][len(board[2]):], manual[2] + board[2].max() + 1)
+    assert own[2].max() == len(own[1]) - 1                               # every row of points_3d is a point of the problem
+    for a, b in zip(own[:2] + own[3:], ref[:2] + ref[3:]):
+        assert np.array_equal(a, b)
