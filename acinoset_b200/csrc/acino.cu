@@ -56,7 +56,13 @@ int acino_dev_alloc(void** out, int64_t bytes) {
   return ACINO_OK;
 }
 int acino_dev_free(void* p) { ACINO_CUDA(cudaFree(p)); return ACINO_OK; }
-int acino_h2d(void* d, const void* s, int64_t bytes) { ACINO_CUDA(cudaMemcpy(d, s, (size_t)bytes, cudaMemcpyHostToDevice)); return ACINO_OK; }
+int acino_h2d(void* d, const void* s, int64_t bytes) {
+  // a pageable source may still be in flight on the legacy stream when cudaMemcpy returns; the solver's streams are
+  // non-blocking (not ordered after it), so wait for the copy itself
+  ACINO_CUDA(cudaMemcpy(d, s, (size_t)bytes, cudaMemcpyHostToDevice));
+  ACINO_CUDA(cudaStreamSynchronize(cudaStreamLegacy));
+  return ACINO_OK;
+}
 int acino_d2h(void* d, const void* s, int64_t bytes) { ACINO_CUDA(cudaMemcpy(d, s, (size_t)bytes, cudaMemcpyDeviceToHost)); return ACINO_OK; }
 int acino_sync(void) { ACINO_CUDA(cudaDeviceSynchronize()); return ACINO_OK; }
 

@@ -269,8 +269,11 @@ cls_fill_obs_kernel(const SchurClasses* __restrict__ cls, const unsigned* __rest
 // rows with coalesced 16-byte stores. Streaming: 140 MB read, 550 MB written at 119,490 frames; HBM bound.
 // Per CTA partials [cost, sum g^T h, max |g|, max |X|].
 #define SCHUR_LIN_TB 128
+#ifndef SCHUR_LIN_MINB
+#define SCHUR_LIN_MINB 4       // 5 CTAs (96 registers, spills) measured slower: 0.179 vs 0.172 ms
+#endif
 template <int C>
-__global__ void __launch_bounds__(SCHUR_LIN_TB, 4)
+__global__ void __launch_bounds__(SCHUR_LIN_TB, SCHUR_LIN_MINB)
 schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __restrict__ pid,
                        const double2* __restrict__ uvs, const double* __restrict__ cams0, const double* __restrict__ cams1,
                        const double* __restrict__ X0, const double* __restrict__ X1, const SchurLm* __restrict__ lm,
@@ -401,18 +404,48 @@ struct SchurTile {
   unsigned char pad;
 };
 
-__device__ __forceinline__ void schur_load_tile(double2* dst, const double2* __restrict__ stg, const SchurTile t, int tid) {
-  const int n16 = (int)t.rounds * schur_rows(__popc((unsigned)t.mask)) * SCHUR_ROW;
-  const double2* src = stg + (size_t)t.row0 * SCHUR_ROW;
-  for (int i = tid; i < n16; i += SCHUR_NW * 32) cp_async16(dst + i, src + i);
+// ---- tile loads: TMA bulk copies (cp.async.bulk, UBLKCP) completing on an mbarrier -------------------------------
+// A tile is one contiguous run of staging rows: warp 0 posts the byte count on the buffer's mbarrier and its lanes issue
+// one bulk copy per round block. No thread spends issue slots or registers on the copy, and nothing queues in the LSU.
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+// waits for the completion of the phase with the given parity; a wait that never ends (a bug, never the data) traps
+// instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+  unsigned done = 0;
+  for (unsigned spin = 0; !done; ++spin) {
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    if (spin > (1u << 26)) __trap();
+  }
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src), "r"(bytes),
+                 "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+// called by warp 0 (all lanes)
+__device__ __forceinline__ void schur_load_tile(double2* dst, const double2* __restrict__ stg, const SchurTile t, int lane,
+                                                unsigned long long* bar) {
+  const unsigned blk_bytes = (unsigned)schur_rows(__popc((unsigned)t.mask)) * SCHUR_ROW * (unsigned)sizeof(double2);
+  if (lane == 0) mbar_expect_tx(bar, blk_bytes * t.rounds);
+  __syncwarp();
+  const char* src = reinterpret_cast<const char*>(stg + (size_t)t.row0 * SCHUR_ROW);
+  for (int r = lane; r < (int)t.rounds; r += 32)
+    bulk_g2s(reinterpret_cast<char*>(dst) + (size_t)r * blk_bytes, src + (size_t)r * blk_bytes, blk_bytes, bar);
 }
 
 // rounds [ra, rb) of a diagonal unit (camera j of the class): S_cc, rhs_c, g_c, diag U_c
 __device__ __forceinline__ void schur_accum_diag(double (&acc)[RCS_UNIT], const double2* __restrict__ tb, int rows, int offN,
                                                  int offE, int offP, int ra, int rb) {
+  const double2* __restrict__ pr = tb + (size_t)ra * rows * SCHUR_ROW;
 #pragma unroll 1
-  for (int r = ra; r < rb; ++r) {
-    const double2* __restrict__ pr = tb + (size_t)r * rows * SCHUR_ROW;
+  for (int r = ra; r < rb; ++r, pr += rows * SCHUR_ROW) {
     const double2 A0 = pr[offN], A1 = pr[offN + SCHUR_ROW], A2 = pr[offN + 2 * SCHUR_ROW];
     const double2 P0 = pr[offP], P1 = pr[offP + SCHUR_ROW], P2 = pr[offP + 2 * SCHUR_ROW];
     const double2 P3 = pr[offP + 3 * SCHUR_ROW], P4 = pr[offP + 4 * SCHUR_ROW], P5 = pr[offP + 5 * SCHUR_ROW];
@@ -462,9 +495,9 @@ __device__ __forceinline__ void schur_accum_diag(double (&acc)[RCS_UNIT], const 
 // rounds [ra, rb) of an off-diagonal unit (cameras j < j' of the class): S_cc' = - W_c V^-1 W_c'^T
 __device__ __forceinline__ void schur_accum_off(double (&acc)[RCS_UNIT], const double2* __restrict__ tb, int rows, int offN,
                                                 int offNp, int offP, int ra, int rb) {
+  const double2* __restrict__ pr = tb + (size_t)ra * rows * SCHUR_ROW;
 #pragma unroll 1
-  for (int r = ra; r < rb; ++r) {
-    const double2* __restrict__ pr = tb + (size_t)r * rows * SCHUR_ROW;
+  for (int r = ra; r < rb; ++r, pr += rows * SCHUR_ROW) {
     const double2 A0 = pr[offN], A1 = pr[offN + SCHUR_ROW], A2 = pr[offN + 2 * SCHUR_ROW];
     const double2 B0 = pr[offNp], B1 = pr[offNp + SCHUR_ROW], B2 = pr[offNp + 2 * SCHUR_ROW];
     const double2 P0 = pr[offP], P1 = pr[offP + SCHUR_ROW], P2 = pr[offP + 2 * SCHUR_ROW];
@@ -524,15 +557,22 @@ __device__ __forceinline__ void schur_flush_unit(double (&acc)[RCS_UNIT], int la
   for (int i = 0; i < RCS_UNIT; ++i) acc[i] = 0.0;
 }
 
+// the warp's piece of a tile, decoded: at most SCHUR_MAXSEG segments (unit, rounds [ra, rb)) in increasing unit order
+#define SCHUR_MAXSEG 8       // >= ceil(36 / SCHUR_NW) + 1 units per warp at C = 8
+struct SchurSeg { int gu_diag; int offN; int offX; int ra_rb; };      // global unit | diag << 8; row offsets; ra | rb << 16
+
 template <int C>
 __global__ void __launch_bounds__(SCHUR_NW * 32, 1)
 schur_accum_kernel(const SchurTile* __restrict__ tiles, const unsigned* __restrict__ tile_range,
                    const double2* __restrict__ stg, const SchurLm* __restrict__ lm, SchurParams prm,
                    double* __restrict__ wpart, double* __restrict__ rcs_partial) {
   constexpr int NW = SCHUR_NW, NT = NW * 32, NU = rcs_units(C), LEN = rcs_len(C);
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  static_assert((NU + NW - 1) / NW + 1 <= SCHUR_MAXSEG, "a warp's piece of a tile spans more units than s_seg holds");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   double2* bufs = reinterpret_cast<double2*>(smem_raw);      // two buffers of SCHUR_BUF_ROWS rows
   __shared__ unsigned long long s_touched[NW];
+  __shared__ __align__(8) unsigned long long s_full[2];       // mbarriers: "the tile in buffer b has landed"
+  __shared__ SchurSeg s_seg[NW][SCHUR_MAXSEG];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int skip = (lm->status != 0 && !prm.force);
   const unsigned t_a = skip ? 0u : tile_range[blockIdx.x], t_b = skip ? 0u : tile_range[blockIdx.x + 1];
@@ -542,48 +582,76 @@ schur_accum_kernel(const SchurTile* __restrict__ tiles, const unsigned* __restri
   for (int i = 0; i < RCS_UNIT; ++i) acc[i] = 0.0;
   int cur_unit = -1;
   unsigned long long touched = 0ull;
+  if (tid == 0) {
+    mbar_init(&s_full[0], 1);
+    mbar_init(&s_full[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
   SchurTile tl = {0u, 0, 0, 0}, tn = {0u, 0, 0, 0};
   if (t_a < t_b) {
     tl = tiles[t_a];
-    schur_load_tile(bufs, stg, tl, tid);
+    if (warp == 0) schur_load_tile(bufs, stg, tl, lane, &s_full[0]);
     if (t_a + 1 < t_b) tn = tiles[t_a + 1];
   }
+  unsigned sched_key = 0xFFFFFFFFu;      // (mask, rounds) the warp's decoded piece in s_seg belongs to
+  int nseg = 0;
   for (unsigned t = t_a; t < t_b; ++t) {
-    cp_async_wait_all();
-    __syncthreads();        // tile t has landed and is visible; every warp has left tile t-1, whose buffer is free again
+    __syncthreads();        // every warp has left tile t-1: its buffer is free for tile t+1
     const int par = (int)((t - t_a) & 1u);
     const double2* __restrict__ tb = bufs + (size_t)par * SCHUR_BUF_ROWS * SCHUR_ROW;
     const SchurTile tc = tl;
     if (t + 1 < t_b) {
-      schur_load_tile(bufs + (size_t)(par ^ 1) * SCHUR_BUF_ROWS * SCHUR_ROW, stg, tn, tid);
+      if (warp == 0) schur_load_tile(bufs + (size_t)(par ^ 1) * SCHUR_BUF_ROWS * SCHUR_ROW, stg, tn, lane, &s_full[par ^ 1]);
       tl = tn;
       if (t + 2 < t_b) tn = tiles[t + 2];
     }
     const unsigned m = tc.mask;
-    const int k = __popc(m), rows = schur_rows(k), R = tc.rounds, U = k * (k + 1) / 2;
-    const int T = U * R, lo = warp * T / NW, hi = (warp + 1) * T / NW;
-    if (lo < hi) {
-      const int u0 = lo / R, u1 = (hi - 1) / R;
-      for (int s = 0; s <= u1 - u0; ++s) {
-        const int u = par ? u1 - s : u0 + s;
-        const int ra = (u == u0) ? lo - u0 * R : 0, rb = (u == u1) ? hi - u1 * R : R;
-        int j, jp;
-        if (u < k) { j = u; jp = u; }
-        else {
-          int q = u - k;
-          j = 0;
-          while (q >= k - 1 - j) { q -= k - 1 - j; ++j; }
-          jp = j + 1 + q;
+    const int k = __popc(m), rows = schur_rows(k), R = tc.rounds;
+    const unsigned key = (m << 16) | (unsigned)R;
+    if (key != sched_key) {
+      // decode the warp's piece of a (class, rounds) tile once; consecutive tiles of a class reuse it
+      sched_key = key;
+      const int U = k * (k + 1) / 2, T = U * R, lo = warp * T / NW, hi = (warp + 1) * T / NW;
+      nseg = 0;
+      if (lo < hi) {
+        const int u0 = lo / R, u1 = (hi - 1) / R;
+        nseg = u1 - u0 + 1;
+        if (lane < nseg) {
+          const int u = u0 + lane;
+          const int ra = (u == u0) ? lo - u0 * R : 0, rb = (u == u1) ? hi - u1 * R : R;
+          int j, jp;
+          if (u < k) { j = u; jp = u; }
+          else {
+            int q = u - k;
+            j = 0;
+            while (q >= k - 1 - j) { q -= k - 1 - j; ++j; }
+            jp = j + 1 + q;
+          }
+          const int c = __fns(m, 0, j + 1), cp = __fns(m, 0, jp + 1);
+          const int gu = (c == cp) ? c : C + c * C - c * (c + 1) / 2 + (cp - c - 1);
+          SchurSeg sg;
+          sg.gu_diag = gu | ((j == jp) << 8);
+          sg.offN = 3 * j * SCHUR_ROW;
+          sg.offX = (j == jp) ? (3 * k + j) * SCHUR_ROW : 3 * jp * SCHUR_ROW;
+          sg.ra_rb = ra | (rb << 16);
+          s_seg[warp][lane] = sg;
         }
-        const int c = __fns(m, 0, j + 1), cp = __fns(m, 0, jp + 1);
-        const int gu = (c == cp) ? c : C + c * C - c * (c + 1) / 2 + (cp - c - 1);
-        if (gu != cur_unit) {
-          if (cur_unit >= 0) schur_flush_unit(acc, lane, mypart, cur_unit, touched);
-          cur_unit = gu;
-        }
-        if (j == jp) schur_accum_diag(acc, tb + lane, rows, 3 * j * SCHUR_ROW, (3 * k + j) * SCHUR_ROW, 4 * k * SCHUR_ROW, ra, rb);
-        else schur_accum_off(acc, tb + lane, rows, 3 * j * SCHUR_ROW, 3 * jp * SCHUR_ROW, 4 * k * SCHUR_ROW, ra, rb);
       }
+      __syncwarp();
+    }
+    mbar_wait(&s_full[par], ((t - t_a) >> 1) & 1u);      // tile t has landed (the async proxy's writes are visible after the wait)
+#pragma unroll 1
+    for (int s = 0; s < nseg; ++s) {
+      const SchurSeg sg = s_seg[warp][par ? nseg - 1 - s : s];
+      const int gu = sg.gu_diag & 0xFF;
+      if (gu != cur_unit) {
+        if (cur_unit >= 0) schur_flush_unit(acc, lane, mypart, cur_unit, touched);
+        cur_unit = gu;
+      }
+      const int ra = sg.ra_rb & 0xFFFF, rb = sg.ra_rb >> 16;
+      if (sg.gu_diag >> 8) schur_accum_diag(acc, tb + lane, rows, sg.offN, sg.offX, 4 * k * SCHUR_ROW, ra, rb);
+      else schur_accum_off(acc, tb + lane, rows, sg.offN, sg.offX, 4 * k * SCHUR_ROW, ra, rb);
     }
   }
   if (cur_unit >= 0) schur_flush_unit(acc, lane, mypart, cur_unit, touched);
@@ -808,7 +876,9 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
 // the current one is used. Sums per thread run in camera order; the per-CTA partials
 // [trial cost, predicted reduction, max |dX|, 0] are folded in a fixed order by K7: deterministic.
 #define SCHUR_BACKSUB_TB 256
-#define SCHUR_BACKSUB_MINB 4     // 64 registers: 32 warps per SM
+#ifndef SCHUR_BACKSUB_MINB
+#define SCHUR_BACKSUB_MINB 3     // 80 registers, 24 warps per SM: 0.159 ms; 4 CTAs of 64 registers (spills): 0.165 ms
+#endif
 template <int C>
 __global__ void __launch_bounds__(SCHUR_BACKSUB_TB, SCHUR_BACKSUB_MINB)
 schur_backsub_kernel(const SchurClasses* __restrict__ cls, const unsigned* __restrict__ pid,

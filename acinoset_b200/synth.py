@@ -132,6 +132,39 @@ def make_dlc_tables(n_frames, markers, n_cams, seed=0, first_frame=0, nan_frac=0
     return out
 
 
+def make_dlc_xy_tables(n_frames, markers, n_cams, seed=0, nan_frac=0.15):
+    """Hand-labelled style tables without a likelihood column (index = image file names ending in NNN.png); cells are NaN
+    in x only, in y only, or in both. Returns (tables, paths)."""
+    import pandas as pd
+    out = []
+    for c in range(n_cams):
+        rng = np.random.default_rng(seed * 100 + c)
+        cols = pd.MultiIndex.from_product([['labeller'], markers, ['x', 'y']], names=['scorer', 'bodyparts', 'coords'])
+        a = rng.uniform(0, 1, (n_frames, len(markers) * 2))
+        a[:, 0::2] *= 2704; a[:, 1::2] *= 1520
+        a[rng.uniform(size=a.shape) < nan_frac] = np.nan
+        index = [f'labeled-data/cam{c + 1}/img{f:03d}.png' for f in range(4, 4 + n_frames)]
+        out.append(pd.DataFrame(a, columns=cols, index=index))
+    return out, [f'/data/labels/cam{i + 1}.h5' for i in range(n_cams)]
+
+
+def make_dlc_head_tables(n_frames, n_cams, seed=0, nan_frac=0.15):
+    """The reference's head dataset layout (src/lib/utils.py:84-103): scorer '2019-03-09_lily_run', bodyparts
+    bodypart1..3 + objectA, x / y only, paths containing 'dlc_head'. Returns (tables, paths)."""
+    import pandas as pd
+    out = []
+    for c in range(n_cams):
+        rng = np.random.default_rng(seed * 100 + c)
+        cols = pd.MultiIndex.from_product([['2019-03-09_lily_run'], ['bodypart1', 'bodypart2', 'bodypart3', 'objectA'], ['x', 'y']],
+                                          names=['scorer', 'bodyparts', 'coords'])
+        a = rng.uniform(0, 1, (n_frames, 8))
+        a[:, 0::2] *= 2704; a[:, 1::2] *= 1520
+        a[rng.uniform(size=a.shape) < nan_frac] = np.nan
+        index = [f'labeled-data/cam{c + 1}/img{f:03d}.png' for f in range(10, 10 + n_frames)]
+        out.append(pd.DataFrame(a, columns=cols, index=index))
+    return out, [f'/data/dlc_head/cam{i + 1}.h5' for i in range(n_cams)]
+
+
 def dense_to_df(uv, lik, n_kpts, first_frame=0, markers=None):
     """Dense slots -> DataFrame[frame, camera, marker, x, y, likelihood], rows camera-major then
     frame then marker, like load_dlc_points_as_df (src/lib/utils.py:139-147)."""

@@ -187,21 +187,25 @@ def save_3d_cheetah_as_2d(position3d_arr, out_dir, scene_fpath, bodyparts, proje
 
 def _read_dlc_table(path, dlc_head=False):
     """One DeepLabCut .h5 -> (frames (F,), bodyparts in alphabetical order, values (F, K, 3) = x, y, likelihood).
-    Mirrors the per-file part of load_dlc_points_as_df: tables without a likelihood column get 1 where x is present and 0
-    elsewhere and their index (image file names) becomes int(name[-7:-4]); the 'dlc_head' tables of the reference's head
-    dataset are renamed the same way (utils.py:84-103)."""
+    Mirrors the per-file part of load_dlc_points_as_df: tables without a likelihood column get 1 where y is present and 0
+    elsewhere (utils.py:104-118) and their index (image file names) becomes int(name[-7:-4]); the 'dlc_head' tables of the
+    reference's head dataset are renamed, reduced to nose / r_eye / l_eye and get their likelihood from x
+    (utils.py:84-103)."""
     df = pd.read_hdf(path)                    # needs PyTables, like the reference
     if dlc_head:
         df = df.rename(columns={'bodypart1': 'r_eye', 'bodypart2': 'l_eye', 'bodypart3': 'nose'}, level=1)
         df = df.drop(columns=['objectA'], level=1)
     parts = list(dict.fromkeys(df.columns.get_level_values(1)))
+    if dlc_head:
+        parts = [p_ for p_ in parts if p_ in ('nose', 'r_eye', 'l_eye')]       # the reference's reindex keeps these three
     coords = set(df.columns.get_level_values(2))
     scorer = df.columns.get_level_values(0)[0]
     frames = np.asarray(df.index)
     has_lik = 'likelihood' in coords and not dlc_head
     if not has_lik:
         frames = np.array([int(str(s_)[-7:-4]) for s_ in frames])
-    parts_sorted = sorted(parts)
+    # bodyparts come out alphabetical from the reference's unstack; the head tables keep the order of its reindex
+    parts_sorted = [p_ for p_ in ('nose', 'r_eye', 'l_eye') if p_ in parts] if dlc_head else sorted(parts)
     vals = np.empty((len(df), len(parts_sorted), 3))
     for j, bp in enumerate(parts_sorted):
         vals[:, j, 0] = df[(scorer, bp, 'x')].to_numpy(dtype=np.float64)
@@ -209,7 +213,7 @@ def _read_dlc_table(path, dlc_head=False):
         if has_lik:
             vals[:, j, 2] = df[(scorer, bp, 'likelihood')].to_numpy(dtype=np.float64)
         else:
-            vals[:, j, 2] = (~np.isnan(vals[:, j, 0])).astype(np.float64)
+            vals[:, j, 2] = (~np.isnan(vals[:, j, 0 if dlc_head else 1])).astype(np.float64)
     return frames, parts_sorted, vals
 
 

@@ -103,6 +103,19 @@ def gen_dlc_load():
             out[f'{name}_marker'] = df['marker'].to_numpy().astype(str)
             for col in ('x', 'y', 'likelihood'):
                 out[f'{name}_{col}'] = df[col].to_numpy().astype(np.float64)
+        # tables without a likelihood column (utils.py:104-118: likelihood from y) and the 'dlc_head' tables
+        # (utils.py:84-103: likelihood from x, three markers kept); cells that are NaN in x only / in y only
+        for name, tabs2, paths2 in (('nolik',) + synth.make_dlc_xy_tables(9, ['nose', 'r_eye', 'spine'], 3, seed=11),
+                                    ('head',) + synth.make_dlc_head_tables(7, 2, seed=12)):
+            store.clear()
+            store.update(dict(zip(paths2, tabs2)))
+            with ref_shim.quiet():
+                df = utils.load_dlc_points_as_df(paths2)
+            out[f'{name}_frame'] = df['frame'].to_numpy().astype(np.int64)
+            out[f'{name}_camera'] = df['camera'].to_numpy().astype(np.int64)
+            out[f'{name}_marker'] = df['marker'].to_numpy().astype(str)
+            for col in ('x', 'y', 'likelihood'):
+                out[f'{name}_{col}'] = df[col].to_numpy().astype(np.float64)
     finally:
         pd.read_hdf = real
     np.savez_compressed(os.path.join(GOLD, 'golden_dlc_load.npz'), versions=_versions(), **out)

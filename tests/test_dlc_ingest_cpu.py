@@ -52,3 +52,24 @@ def test_dense_loader_equals_table_path(dlc_files):
 def test_frame_shift_assert(dlc_files):
     with pytest.raises(AssertionError):
         utils.load_dlc_points_as_df(dlc_files, frame_shifts=[0, 1])
+
+
+@pytest.mark.parametrize('name', ['nolik', 'head'])
+def test_tables_without_likelihood_match_reference(monkeypatch, golden_dir, name):
+    """tables without a likelihood column take it from the y column (src/lib/utils.py:104-118); the 'dlc_head'
+    tables take it from x and keep nose / r_eye / l_eye only (utils.py:84-103). The synthetic tables hold cells that are
+    NaN in x only and in y only, so the two rules give different tables."""
+    g = np.load(os.path.join(golden_dir, 'golden_dlc_load.npz'))
+    tabs, paths = (synth.make_dlc_xy_tables(9, ['nose', 'r_eye', 'spine'], 3, seed=11) if name == 'nolik'
+                   else synth.make_dlc_head_tables(7, 2, seed=12))
+    store = dict(zip(paths, tabs))
+    monkeypatch.setattr(pd, 'read_hdf', lambda p, *a, **k: store[p].copy())
+    df = utils.load_dlc_points_as_df(paths)
+    assert np.array_equal(df['frame'].to_numpy(), g[f'{name}_frame'])
+    assert np.array_equal(df['camera'].to_numpy(), g[f'{name}_camera'])
+    assert np.array_equal(df['marker'].to_numpy().astype(str), g[f'{name}_marker'])
+    for col in ('x', 'y', 'likelihood'):
+        assert np.array_equal(df[col].to_numpy(), g[f'{name}_{col}'], equal_nan=True), col
+    x_only = np.isnan(df['x'].to_numpy()) & ~np.isnan(df['y'].to_numpy())
+    y_only = ~np.isnan(df['x'].to_numpy()) & np.isnan(df['y'].to_numpy())
+    assert x_only.any() and y_only.any()

@@ -65,7 +65,7 @@ def test_ring_triangulation_other_camera_counts(rig, cams):
     assert np.array_equal(ex, eo)
     want_mask = (mo * (1 << np.arange(len(cams)))).sum(axis=1) * eo
     assert np.array_equal(mask.astype(np.int64), want_mask)
-    assert np.abs(xyz[ex] - xo[eo]).max() < 1e-8        # 2- and 3-camera rigs have near-degenerate pairs: 1e-8 m
+    assert np.abs(xyz[ex] - xo[eo]).max() < 1e-9
 
 
 def test_eight_cameras_schur_vs_numpy_lm(rig):
