@@ -57,6 +57,7 @@ SIGNATURES = {
     'acino_ekf_measurement': (_I, [_P, _I, _I, _P, _I, _D, _I, _P, _P, _P]),
     'acino_manual_residuals': (_I, [_P, _I, _P, _I, _P, _I, _P, _I, _P, _I, _D, _D, _D, _P]),
     'acino_ring_critical': (_I, [_P, _I64, _I, _P]),
+    'acino_residual_cost_noalloc': (_I, [_P, _I64, _P, _P, _P, _I64, _P, _I, _D, _P, _P, _P]),
     'acino_jacobian_list': (_I, [_P, _I64, _P, _P, _I64, _P, _I, _P]),
     'acino_rodrigues': (_I, [_P, _I, _P]),
     'acino_triangulate_pair': (_I, [_P, _P, _I64, _P, _P, _P]),

@@ -339,3 +339,135 @@ int acino_ekf_measurement(const double* x, int n_pose, int mode, const double* c
 }
 
 #include "acino_sba_api.inl"
+
+// ================================================================ allocation-free entry point
+// acino_residual_cost_noalloc: residual vector + robust (Cauchy) cost of an observation list with NO allocation of any
+// kind: not here, not in a library routine. It is the two-stage deterministic cost sum of the points-only solver
+// (sum_kernel + the handle's `partial` scratch, acino_sba_api.inl: scene_cost) fused with residuals_list_kernel; the
+// per-block partial sums live in a file-scope device array of a stated maximum size instead of a cudaMalloc'ed buffer.
+// Every GPU that loads the library holds the array (128.25 KB) until the process exits. All calls share it and it keeps
+// the last call's contents: the ticket counter is cleared on the caller's stream before every launch, and calls that
+// overlap on one GPU (different streams, threads or processes sharing the context) RACE on it - serialise them.
+#define NOALLOC_TB 256
+#define NOALLOC_MAX_BLOCKS 16384
+#define NOALLOC_MAX_OBS ((int64_t)NOALLOC_MAX_BLOCKS * NOALLOC_TB)      /* 4,194,304 observations per call */
+static __device__ __align__(256) unsigned char g_noalloc_scratch[256 + NOALLOC_MAX_BLOCKS * sizeof(double)];
+// layout: [0, 8) ticket counter (u32 used), [256, ...) one partial cost sum per block
+
+struct NoAllocCams { double c[MAX_CAMS * CAM_STRIDE]; };      // by value in the launch parameters: no device copy to own
+
+__global__ void __launch_bounds__(NOALLOC_TB)
+residual_cost_noalloc_kernel(const double* __restrict__ Xp, int64_t n_points, const int32_t* __restrict__ pidx,
+                             const int32_t* __restrict__ cidx, const double2* __restrict__ obs, int64_t n_obs,
+                             const __grid_constant__ NoAllocCams cams, int n_cams, double inv_c2, double half_c2,
+                             double2* __restrict__ f, double* __restrict__ cost_out, unsigned char* __restrict__ scratch) {
+  __shared__ double sc[MAX_CAMS * CAM_STRIDE];
+  __shared__ double red[NOALLOC_TB / 32];
+  __shared__ unsigned s_ticket;
+  unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+  double* partial = reinterpret_cast<double*>(scratch + 256);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < n_cams * CAM_STRIDE; i += NOALLOC_TB) sc[i] = cams.c[i];
+  __syncthreads();
+  const int64_t o = (int64_t)blockIdx.x * NOALLOC_TB + tid;
+  double c = 0.0;
+  if (o < n_obs) {
+    const int64_t p = pidx[o];
+    const int ci = cidx[o];
+    double2 r;
+    if (p < 0 || p >= n_points || ci < 0 || ci >= n_cams) {
+      // indices cannot be checked on the host without a copy: an out-of-range observation reads nothing and poisons
+      // its residual and the cost with NaN
+      r.x = r.y = __longlong_as_double(0x7ff8000000000000LL);
+    } else {
+      const double* cam = sc + ci * CAM_STRIDE;
+      double x, y, z, u, v;
+      to_camera(cam, Xp[3 * p], Xp[3 * p + 1], Xp[3 * p + 2], x, y, z);
+      fisheye_uv(cam, x, y, z, u, v);
+      const double2 q = obs[o];
+      r = make_double2(u - q.x, v - q.y);
+    }
+    if (f) f[o] = r;
+    c = log1p(r.x * r.x * inv_c2) + log1p(r.y * r.y * inv_c2);
+  }
+  // block sum in a fixed order
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) c += __shfl_xor_sync(0xffffffffu, c, s);
+  if (lane == 0) red[warp] = c;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0.0;
+    for (int w = 0; w < NOALLOC_TB / 32; ++w) t += red[w];
+    partial[blockIdx.x] = t;
+    __threadfence();
+    s_ticket = atomicAdd(ticket, 1u);
+  }
+  __syncthreads();
+  if (s_ticket != gridDim.x - 1) return;
+  // the last block to finish folds the partials: thread t sums entries t, t + 256, ... then the block sum as above,
+  // so the result does not depend on which block came last
+  __threadfence();
+  double t = 0.0;
+  for (unsigned b = tid; b < gridDim.x; b += NOALLOC_TB) t += __ldcg(partial + b);
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) t += __shfl_xor_sync(0xffffffffu, t, s);
+  __syncthreads();
+  if (lane == 0) red[warp] = t;
+  __syncthreads();
+  if (tid == 0) {
+    double a = 0.0;
+    for (int w = 0; w < NOALLOC_TB / 32; ++w) a += red[w];
+    cost_out[0] = half_c2 * a;
+    *ticket = 0u;
+  }
+}
+
+#define NOALLOC_MAX_DEVICES 64
+static unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};      // device address of g_noalloc_scratch, per device
+
+extern "C" int acino_residual_cost_noalloc(const double* X_dev, int64_t n_points, const int32_t* point_idx_dev,
+                                           const int32_t* cam_idx_dev, const double* points_2d_dev, int64_t n_obs,
+                                           const double* cams24_host, int n_cams, double f_scale, double* f_dev,
+                                           double* cost_dev, void* stream) {
+  ARG_CHECK(n_points >= 0 && n_obs >= 0 && cams24_host && cost_dev && f_scale > 0.0, "residual_cost_noalloc");
+  if (n_cams < 1 || n_cams > MAX_CAMS) {
+    set_error("residual_cost_noalloc: n_cams = %d, the allocation-free entry point takes 1..%d cameras (they travel in the launch parameters)",
+              n_cams, MAX_CAMS);
+    return ACINO_EINVAL;
+  }
+  if (n_obs > NOALLOC_MAX_OBS) {
+    set_error("residual_cost_noalloc: n_obs = %lld exceeds the fixed scratch of the allocation-free entry point (at most %lld observations per call); "
+              "split the list or use acino_residuals_list",
+              (long long)n_obs, (long long)NOALLOC_MAX_OBS);
+    return ACINO_EINVAL;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_obs == 0) {
+    ACINO_CUDA(cudaMemsetAsync(cost_dev, 0, sizeof(double), st));      // 0.0
+    return ACINO_OK;
+  }
+  ARG_CHECK(X_dev && point_idx_dev && cam_idx_dev && points_2d_dev, "residual_cost_noalloc null pointer");
+  int dev = 0;
+  ACINO_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) { set_error("residual_cost_noalloc: device ordinal %d not supported", dev); return ACINO_EINVAL; }
+  if (!g_noalloc_ptr[dev]) {
+    // once per device, with that device current: the symbol's name is a host-side stand-in, not a device address
+    unsigned char* p = nullptr;
+    ACINO_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    if (!p) { set_error("residual_cost_noalloc: cudaGetSymbolAddress returned a null address"); return ACINO_ECUDA; }
+    g_noalloc_ptr[dev] = p;
+  }
+  unsigned char* scratch = g_noalloc_ptr[dev];
+  // the array keeps the last call's contents: the ticket counter must start at zero (the partials are all overwritten)
+  ACINO_CUDA(cudaMemsetAsync(scratch, 0, 256, st));
+  NoAllocCams cams;
+  memset(&cams, 0, sizeof(cams));
+  memcpy(cams.c, cams24_host, (size_t)n_cams * CAM_STRIDE * sizeof(double));
+  const unsigned blocks = (unsigned)((n_obs + NOALLOC_TB - 1) / NOALLOC_TB);
+  residual_cost_noalloc_kernel<<<blocks, NOALLOC_TB, 0, st>>>(X_dev, n_points, point_idx_dev, cam_idx_dev,
+                                                             (const double2*)points_2d_dev, n_obs, cams, n_cams,
+                                                             1.0 / (f_scale * f_scale), 0.5 * f_scale * f_scale, (double2*)f_dev,
+                                                             cost_dev, scratch);
+  ACINO_CUDA(cudaGetLastError());
+  return ACINO_OK;
+}

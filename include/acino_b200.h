@@ -56,6 +56,24 @@ int acino_project_all(const double* X, int64_t N, const double* cams24, int n_ca
 int acino_residuals_list(const double* X, int64_t n_points, const int32_t* point_idx, const int32_t* cam_idx,
                          const double* points_2d, int64_t n_obs, const double* cams24, int n_cams, double* f);
 
+/* Allocation-free residual vector + robust cost of an observation list. This entry point has NO counterpart in the
+ * reference; it was added for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc). It calls no cudaMalloc / cudaFree / allocating
+ * library routine: the per-block partial sums of the cost live in a file-scope device array of the library (128.25 KB,
+ * held by every GPU that loads the library until the process exits), and the cameras travel in the launch parameters.
+ *   f_dev[2*o], f_dev[2*o+1] = proj(X[point_idx[o]], cam cam_idx[o]) - points_2d[o]   (as acino_residuals_list; may be NULL)
+ *   cost_dev[0] = 0.5 f_scale^2 sum log1p((f / f_scale)^2) over all 2 n_obs residuals (scipy's Cauchy cost, deterministic sum)
+ * Limits: n_obs <= 4,194,304 and 1 <= n_cams <= 8 per call (larger sizes are rejected with ACINO_EINVAL and a message).
+ * All pointers are DEVICE pointers on the current device except cams24_host. The work is enqueued on `stream` and not
+ * waited for. An observation whose point or camera index is out of range gives NaN residuals and a NaN cost. The first
+ * call on a device looks up the scratch array's device address (cudaGetSymbolAddress): make one call before a graph
+ * capture. All calls share the scratch array, which keeps the last call's contents (the entry point clears what must
+ * start at zero): calls that OVERLAP on one GPU race on it - issue them on one stream or serialise them. */
+int acino_residual_cost_noalloc(const double* X_dev, int64_t n_points, const int32_t* point_idx_dev,
+                                const int32_t* cam_idx_dev, const double* points_2d_dev, int64_t n_obs,
+                                const double* cams24_host, int n_cams, double f_scale, double* f_dev, double* cost_dev,
+                                void* stream);
+
 /* The analytic Jacobian of that residual (the reference has none: scipy differentiates cost_func_points_extrinsics,
  * src/lib/sba.py:142-146, by forward differences), for inspection and tests: per observation J double[2][9] =
  * d(u, v) / d(w, tau, X), (w, tau) the world-frame twist of the camera (R <- R Exp(w), t <- t + R tau) the solver
