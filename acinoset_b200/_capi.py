@@ -28,7 +28,8 @@ class SbaStats(ct.Structure):
     _fields_ = [('n_points', ct.c_int64), ('n_obs', ct.c_int64), ('n_unconverged', ct.c_int64),
                 ('iterations', ct.c_int32), ('launches', ct.c_int32),
                 ('cost_initial', ct.c_double), ('cost_final', ct.c_double), ('solve_ms', ct.c_double),
-                ('status', ct.c_double), ('n_accept', ct.c_double), ('lambda_final', ct.c_double), ('gmax', ct.c_double)]
+                ('status', ct.c_double), ('n_accept', ct.c_double), ('lambda_final', ct.c_double), ('gmax', ct.c_double),
+                ('init_ms', ct.c_double), ('polish_ms', ct.c_double), ('syncs', ct.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != 'reserved'}

@@ -176,7 +176,8 @@ void acino_sba_default_opts(acino_sba_opts* o, int mode) {
     o->ftol = 1e-14;
     o->hess_floor = 0.3;
     o->point_refine_iters = 3;
-    o->point_refine_skip = 1e-11;
+    o->point_refine_skip = 1e-8;      // scripts/refine_sweep.py: 1e-11 refines every point in every iteration for nothing (24 iterations / 26.8 ms
+                                      // at C4 against 21 / 21.6 ms), 1e-6 lets the joint steps creep (37 / 31.6 ms)
     o->polish_tol = 3e-4;
     o->lambda0 = 1.0;            // cautious first steps: a small start lets the first accepted step throw points into worse basins of the robust cost
   } else {

@@ -263,21 +263,87 @@ cls_fill_obs_kernel(const SchurClasses* __restrict__ cls, const unsigned* __rest
   }
 }
 
-// ---- K4a: linearisation. One thread per point of the sorted numbering, one warp per round, 16 warps per SM ---------
-// residual + Jacobian of the point's k observations (the camera is the same for the whole warp: broadcast reads),
-// V = sum N^T N, g = sum N^T e, damped inverse, h = V^-1 g; everything K4b and K6 need goes to the round's staging
-// rows with coalesced 16-byte stores. Streaming: 140 MB read, 550 MB written at 119,490 frames; HBM bound.
+// one point of a class with k cameras (mask m) linearised at (X, Y, Z): g = N^T e, V = N^T N, the robust cost as
+// prod(1 + z) - 1; with EMIT the rows of its observations go to the round's staging block (zeros for a padding lane)
+struct PointLin { double g0, g1, g2, v00, v01, v02, v11, v12, v22, pm1; };
+template <bool EMIT>
+__device__ __forceinline__ PointLin schur_lin_point(const double* __restrict__ sc, unsigned m, int k, const double2* __restrict__ ob,
+                                                    double2* __restrict__ blk, double X, double Y, double Z, bool valid,
+                                                    double inv_c2, double hfloor) {
+  PointLin L = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  double2 o_next = ob[0];
+  int j = 0;
+#pragma unroll 1
+  for (unsigned mm = m; mm; mm &= mm - 1, ++j) {
+    const int c = __ffs(mm) - 1;
+    const double2 o = o_next;
+    if (mm & (mm - 1)) o_next = ob[(j + 1) * SCHUR_ROW];
+    double a0 = 0, a1 = 0, a2 = 0, b0 = 0, b1 = 0, b2 = 0, e0 = 0, e1 = 0;
+    if (valid) {
+      const ObsLin Q = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, o.x, o.y, inv_c2, hfloor, L.pm1);
+      a0 = Q.n0[0]; a1 = Q.n0[1]; a2 = Q.n0[2]; b0 = Q.n1[0]; b1 = Q.n1[1]; b2 = Q.n1[2]; e0 = Q.e0; e1 = Q.e1;
+      L.g0 = fma(a0, e0, fma(b0, e1, L.g0));
+      L.g1 = fma(a1, e0, fma(b1, e1, L.g1));
+      L.g2 = fma(a2, e0, fma(b2, e1, L.g2));
+      L.v00 = fma(a0, a0, fma(b0, b0, L.v00));
+      L.v01 = fma(a0, a1, fma(b0, b1, L.v01));
+      L.v02 = fma(a0, a2, fma(b0, b2, L.v02));
+      L.v11 = fma(a1, a1, fma(b1, b1, L.v11));
+      L.v12 = fma(a1, a2, fma(b1, b2, L.v12));
+      L.v22 = fma(a2, a2, fma(b2, b2, L.v22));
+    }
+    if (EMIT) {
+      blk[(3 * j) * SCHUR_ROW] = make_double2(a0, a1);
+      blk[(3 * j + 1) * SCHUR_ROW] = make_double2(a2, b0);
+      blk[(3 * j + 2) * SCHUR_ROW] = make_double2(b1, b2);
+      blk[(3 * k + j) * SCHUR_ROW] = make_double2(e0, e1);
+    }
+  }
+  return L;
+}
+
+// robust cost of one point at (X, Y, Z) as prod(1 + z) - 1 (no derivatives): the last trial of the embedded refinement
+__device__ __forceinline__ double schur_cost_point(const double* __restrict__ sc, unsigned m, const double2* __restrict__ ob,
+                                                   double X, double Y, double Z, double inv_c2) {
+  double pm1 = 0.0;
+  int j = 0;
+#pragma unroll 1
+  for (unsigned mm = m; mm; mm &= mm - 1, ++j) {
+    const int c = __ffs(mm) - 1;
+    const double2 o = ob[j * SCHUR_ROW];
+    double x, y, z, u, v;
+    to_camera(sc + c * CAM_STRIDE, X, Y, Z, x, y, z);
+    fisheye_uv(sc + c * CAM_STRIDE, x, y, z, u, v);
+    cauchy_accum(u - o.x, v - o.y, inv_c2, pm1);
+  }
+  return pm1;
+}
+
+// ---- K4a: linearisation (+ embedded per-point refinement). One thread per point of the sorted numbering, one warp per
+// round, 16 warps per SM. Residual + Jacobian of the point's k observations (the camera is the same for the whole warp:
+// broadcast reads), V = sum N^T N, g = sum N^T e, damped inverse, h = V^-1 g; everything K4b and K6 need goes to the
+// round's staging rows with coalesced 16-byte stores. Streaming: 140 MB read, 550 MB written at 119,490 frames.
+//
+// Embedded refinement (prm.refine > 0, from the second linearisation of a solve on): a joint Gauss-Newton step with
+// floored robust curvature leaves individual points off their own minima (cameras fixed), and the solve converges in a
+// fraction of the iterations when they are put back first. This used to be a separate launch of the points-only LM
+// kernel after every accepted step, which re-read and re-linearised every point to find most of them converged. Here
+// the linearisation the build needs anyway doubles as the first evaluation: a point whose own model predicts a decrease
+// <= refine_skip x its cost (or whose gradient is below gtol) is done; any other point takes up to prm.refine LM steps
+// with its own damping (kept in lamS across iterations), writes its new position to the current point buffer and is
+// linearised once more for the rows. The cost K5 takes as the current cost is the cost after refinement.
 // Per CTA partials [cost, sum g^T h, max |g|, max |X|].
 #define SCHUR_LIN_TB 128
 #ifndef SCHUR_LIN_MINB
 #define SCHUR_LIN_MINB 4       // 5 CTAs (96 registers, spills) measured slower: 0.179 vs 0.172 ms
 #endif
-template <int C>
+template <int C, bool REFINE>
 __global__ void __launch_bounds__(SCHUR_LIN_TB, SCHUR_LIN_MINB)
 schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __restrict__ pid,
                        const double2* __restrict__ uvs, const double* __restrict__ cams0, const double* __restrict__ cams1,
-                       const double* __restrict__ X0, const double* __restrict__ X1, const SchurLm* __restrict__ lm,
-                       SchurParams prm, double2* __restrict__ stg, double* __restrict__ lin_partial) {
+                       double* __restrict__ X0, double* __restrict__ X1, const SchurLm* __restrict__ lm,
+                       SchurParams prm, double2* __restrict__ stg, double* __restrict__ lin_partial,
+                       double* __restrict__ lamS) {
   constexpr int NCLS = 1 << C, NW = SCHUR_LIN_TB / 32;
   __shared__ double sc[C * CAM_STRIDE];
   __shared__ unsigned s_round0[NCLS + 1], s_blk0[NCLS + 1], s_uv0[NCLS + 1];
@@ -286,9 +352,12 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
   const int skip = (lm->status != 0 && !prm.force);
   const int cur = lm->cur;
   const double lam = lm->lambda;
-  const bool need_cost = (lm->iter == 0) || lm->need_cost;   // later iterations inherit the cost from the accepted trial (K6/K7)
+  // REFINE = false is the plain linearisation (its own instantiation: 124 registers without spills)
+  const int refine = (REFINE && lm->iter > 0) ? prm.refine : 0;       // the first linearisation reports the cost of the caller's parameters
+  // later iterations inherit the cost from the accepted trial (K6/K7) unless the points move here
+  const bool need_cost = (lm->iter == 0) || lm->need_cost || refine > 0;
   const double* __restrict__ cams = cur ? cams1 : cams0;
-  const double* __restrict__ Xp = cur ? X1 : X0;
+  double* __restrict__ Xp = cur ? X1 : X0;
   for (int i = tid; i < C * CAM_STRIDE; i += SCHUR_LIN_TB) sc[i] = cams[i];
   for (int i = tid; i <= NCLS; i += SCHUR_LIN_TB) { s_round0[i] = cls->round0[i]; s_blk0[i] = cls->blk0[i]; s_uv0[i] = cls->uv0[i]; }
   __syncthreads();
@@ -301,53 +370,72 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
     const unsigned rr = r - s_round0[m];
     double2* __restrict__ blk = stg + ((size_t)s_blk0[m] + (size_t)rr * schur_rows(k)) * SCHUR_ROW + lane;
     const double2* __restrict__ ob = uvs + ((size_t)s_uv0[m] + (size_t)rr * k) * SCHUR_ROW + lane;
-    const unsigned p = pid[(size_t)r * 32 + lane];
+    const size_t gs = (size_t)r * 32 + lane;
+    const unsigned p = pid[gs];
     const bool valid = p != 0xFFFFFFFFu;
     double X = 0.0, Y = 0.0, Z = 0.0;
     if (valid) { X = Xp[3 * (size_t)p]; Y = Xp[3 * (size_t)p + 1]; Z = Xp[3 * (size_t)p + 2]; }
-    double g0 = 0, g1 = 0, g2 = 0, v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0;
-    double2 o_next = ob[0];
-    int j = 0;
+    PointLin L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, valid, prm.inv_c2, prm.hfloor);
+    if (REFINE && refine > 0 && valid) {
+      // ---- the point's own LM with the cameras fixed, from the linearisation just taken
+      double lp = lamS[gs];
+      if (!(lp > 0.0)) lp = 1e-4;
+      double nu = 2.0;
+      bool moved = false;
 #pragma unroll 1
-    for (unsigned mm = m; mm; mm &= mm - 1, ++j) {
-      const int c = __ffs(mm) - 1;
-      const double2 o = o_next;
-      if (mm & (mm - 1)) o_next = ob[(j + 1) * SCHUR_ROW];
-      double a0 = 0, a1 = 0, a2 = 0, b0 = 0, b1 = 0, b2 = 0, e0 = 0, e1 = 0;
-      if (valid) {
-        double pm1 = 0.0;
-        const ObsLin L = linearise_obs(sc + c * CAM_STRIDE, X, Y, Z, o.x, o.y, prm.inv_c2, prm.hfloor, pm1);
-        a0 = L.n0[0]; a1 = L.n0[1]; a2 = L.n0[2]; b0 = L.n1[0]; b1 = L.n1[1]; b2 = L.n1[2]; e0 = L.e0; e1 = L.e1;
-        if (need_cost) {
-          cprod *= 1.0 + pm1;
-          if (cprod > 1e200) { cost_acc += prm.half_c2 * log(cprod); cprod = 1.0; }
+      for (int it = 0; it < refine; ++it) {
+        const double gm = fmax(fabs(L.g0), fmax(fabs(L.g1), fabs(L.g2)));
+        if (!(gm > prm.gtol)) break;
+        const Sym3Inv iv = damped_inverse3(L.v00, L.v01, L.v02, L.v11, L.v12, L.v22, lp);
+        const double d0 = -fma(iv.i00, L.g0, fma(iv.i01, L.g1, iv.i02 * L.g2));
+        const double d1 = -fma(iv.i01, L.g0, fma(iv.i11, L.g1, iv.i12 * L.g2));
+        const double d2 = -fma(iv.i02, L.g0, fma(iv.i12, L.g1, iv.i22 * L.g2));
+        const double pred = 0.5 * (lp * (iv.D0 * d0 * d0 + iv.D1 * d1 * d1 + iv.D2 * d2 * d2) - (L.g0 * d0 + L.g1 * d1 + L.g2 * d2));
+        const double F = prm.half_c2 * log1p(L.pm1);
+        if (pred <= prm.refine_skip * fmax(F, prm.half_c2)) break;        // nothing to gain
+        const bool last = (it + 1 == refine);       // no further step in this launch: the trial's cost is enough
+        PointLin T;
+        if (last) T.pm1 = schur_cost_point(sc, m, ob, X + d0, Y + d1, Z + d2, prm.inv_c2);
+        else T = schur_lin_point<false>(sc, m, k, ob, blk, X + d0, Y + d1, Z + d2, true, prm.inv_c2, prm.hfloor);
+        const double act = F - prm.half_c2 * log1p(T.pm1);
+        if (act > 0.0 && pred > 0.0) {          // NaN-safe: comparisons fail on a non-finite trial cost
+          const double q = 2.0 * (act / pred) - 1.0;
+          lp = fmax(lp * fmax(1.0 / 3.0, 1.0 - q * q * q), 1e-12);
+          nu = 2.0;
+          const double dmax = fmax(fabs(d0), fmax(fabs(d1), fabs(d2)));
+          const double xmax = fmax(fabs(X), fmax(fabs(Y), fabs(Z)));
+          X += d0; Y += d1; Z += d2;
+          moved = true;
+          if (last) break;
+          L = T;
+          if (dmax <= prm.xtol * (xmax + prm.xtol)) break;
+        } else {
+          lp *= nu;
+          nu *= 2.0;
+          if (lp > 1e16) { lp = 1e16; break; }
         }
-        g0 = fma(a0, e0, fma(b0, e1, g0));
-        g1 = fma(a1, e0, fma(b1, e1, g1));
-        g2 = fma(a2, e0, fma(b2, e1, g2));
-        v00 = fma(a0, a0, fma(b0, b0, v00));
-        v01 = fma(a0, a1, fma(b0, b1, v01));
-        v02 = fma(a0, a2, fma(b0, b2, v02));
-        v11 = fma(a1, a1, fma(b1, b1, v11));
-        v12 = fma(a1, a2, fma(b1, b2, v12));
-        v22 = fma(a2, a2, fma(b2, b2, v22));
       }
-      blk[(3 * j) * SCHUR_ROW] = make_double2(a0, a1);
-      blk[(3 * j + 1) * SCHUR_ROW] = make_double2(a2, b0);
-      blk[(3 * j + 2) * SCHUR_ROW] = make_double2(b1, b2);
-      blk[(3 * k + j) * SCHUR_ROW] = make_double2(e0, e1);
+      lamS[gs] = lp;
+      if (moved) {
+        Xp[3 * (size_t)p] = X; Xp[3 * (size_t)p + 1] = Y; Xp[3 * (size_t)p + 2] = Z;
+        L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, true, prm.inv_c2, prm.hfloor);      // the rows at the refined point
+      }
     }
     double i00 = 0, i01 = 0, i02 = 0, i11 = 0, i12 = 0, i22 = 0, h0 = 0, h1 = 0, h2 = 0;
     if (valid) {
-      const Sym3Inv iv = damped_inverse3(v00, v01, v02, v11, v12, v22, lam);
+      if (need_cost) {
+        cprod *= 1.0 + L.pm1;
+        if (cprod > 1e150) { cost_acc += prm.half_c2 * log(cprod); cprod = 1.0; }      // a point contributes up to ~1e100
+      }
+      const Sym3Inv iv = damped_inverse3(L.v00, L.v01, L.v02, L.v11, L.v12, L.v22, lam);
       i00 = iv.i00; i01 = iv.i01; i02 = iv.i02; i11 = iv.i11; i12 = iv.i12; i22 = iv.i22;
-      h0 = fma(i00, g0, fma(i01, g1, i02 * g2));
-      h1 = fma(i01, g0, fma(i11, g1, i12 * g2));
-      h2 = fma(i02, g0, fma(i12, g1, i22 * g2));
+      h0 = fma(i00, L.g0, fma(i01, L.g1, i02 * L.g2));
+      h1 = fma(i01, L.g0, fma(i11, L.g1, i12 * L.g2));
+      h2 = fma(i02, L.g0, fma(i12, L.g1, i22 * L.g2));
       // g^T h of the point block: with dX = -(h + V^-1 s) the gradient term of the predicted reduction is
       // -g^T dX = g^T h + h^T s; the first part is summed here (RCS scalar [1]), the second in K6
-      gh_acc += fma(g0, h0, fma(g1, h1, g2 * h2));
-      gmax_acc = fmax(gmax_acc, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+      gh_acc += fma(L.g0, h0, fma(L.g1, h1, L.g2 * h2));
+      gmax_acc = fmax(gmax_acc, fmax(fabs(L.g0), fmax(fabs(L.g1), fabs(L.g2))));
       xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
     }
     double2* __restrict__ pt = blk + (size_t)(4 * k) * SCHUR_ROW;
@@ -392,6 +480,10 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
 #ifndef SCHUR_NW
 #define SCHUR_NW 12
 #endif
+#ifndef SCHUR_UNROLL
+#define SCHUR_UNROLL 1           // rounds per trip of the accumulation loops
+#endif
+constexpr int kSchurUnroll = SCHUR_UNROLL;
 #define SCHUR_BUF_ROWS 220                 // staging rows (512 B) per tile buffer: 2 x 110 KB
 #define SCHUR_ACCUM_SMEM (2 * SCHUR_BUF_ROWS * SCHUR_ROW * sizeof(double2))
 // relative cost of one round of a class with k cameras in K4b (k (k+1)/2 units + the per-tile overheads): the weight the
@@ -444,7 +536,7 @@ __device__ __forceinline__ void schur_load_tile(double2* dst, const double2* __r
 __device__ __forceinline__ void schur_accum_diag(double (&acc)[RCS_UNIT], const double2* __restrict__ tb, int rows, int offN,
                                                  int offE, int offP, int ra, int rb) {
   const double2* __restrict__ pr = tb + (size_t)ra * rows * SCHUR_ROW;
-#pragma unroll 1
+#pragma unroll kSchurUnroll
   for (int r = ra; r < rb; ++r, pr += rows * SCHUR_ROW) {
     const double2 A0 = pr[offN], A1 = pr[offN + SCHUR_ROW], A2 = pr[offN + 2 * SCHUR_ROW];
     const double2 P0 = pr[offP], P1 = pr[offP + SCHUR_ROW], P2 = pr[offP + 2 * SCHUR_ROW];
@@ -496,7 +588,7 @@ __device__ __forceinline__ void schur_accum_diag(double (&acc)[RCS_UNIT], const 
 __device__ __forceinline__ void schur_accum_off(double (&acc)[RCS_UNIT], const double2* __restrict__ tb, int rows, int offN,
                                                 int offNp, int offP, int ra, int rb) {
   const double2* __restrict__ pr = tb + (size_t)ra * rows * SCHUR_ROW;
-#pragma unroll 1
+#pragma unroll kSchurUnroll
   for (int r = ra; r < rb; ++r, pr += rows * SCHUR_ROW) {
     const double2 A0 = pr[offN], A1 = pr[offN + SCHUR_ROW], A2 = pr[offN + 2 * SCHUR_ROW];
     const double2 B0 = pr[offNp], B1 = pr[offNp + SCHUR_ROW], B2 = pr[offNp + 2 * SCHUR_ROW];
@@ -749,7 +841,7 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
     for (int i = 0; i < n; ++i) { dmax = fmax(dmax, D[i]); gm = fmax(gm, fabs(gbar[i])); }
     double flo = fmax(1e-12 * dmax, 1e-300);
     for (int i = 0; i < n; ++i) D[i] = fmax(D[i], flo);
-    if (lm->iter == 0 || lm->need_cost) {      // K4 evaluates the cost only then
+    if (lm->iter == 0 || lm->need_cost || prm.refine > 0) {      // K4a evaluates the cost only then (with refinement: always)
       lm->F = r[NU * RCS_UNIT];
       if (lm->iter == 0) lm->F0 = r[NU * RCS_UNIT];
       lm->need_cost = 0;
@@ -1039,7 +1131,7 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
     lm->F = Ft;
     lm->n_accept += 1;
     lm->last_accept = 1;
-    lm->need_cost = prm.refine > 0;
+    lm->need_cost = 0;          // the trial cost is the cost of the new parameters (the refinement is part of the next K4a)
     lm->last_rel_dec = act / F;
     if (!prm.force) {
       if (act <= prm.ftol * F && rho > 0.25) lm->status = 2;      // scipy trf check_termination: dF < ftol*F and ratio > 0.25
@@ -1160,11 +1252,12 @@ struct SchurState {
   unsigned* h_cls_starts = nullptr;        // pinned copy
   SchurClasses* cls = nullptr;             // device
   unsigned* pid = nullptr;                 // [32 n_rounds] scene index of the sorted point (0xFFFFFFFF: padding)
+  double* lamS = nullptr;                  // [32 n_rounds] the points' own damping of the embedded refinement (sorted numbering)
   double2* uvs = nullptr;                  // observation rows
   double2* stg = nullptr;                  // staging rows written by K4a, read by K4b and K6
   SchurTile* tiles = nullptr;
   unsigned* tile_range = nullptr;          // [grid_build + 1]
-  size_t cap_pid = 0, cap_uvs = 0, cap_stg = 0, cap_tiles = 0;     // capacities (grow only)
+  size_t cap_pid = 0, cap_lam = 0, cap_uvs = 0, cap_stg = 0, cap_tiles = 0;     // capacities (grow only)
   int64_t E = 0;                           // existing points of the current solve
   int64_t n_rounds = 0, n_tiles = 0, n_obs_rows = 0, n_stg_rows = 0;
   cudaEvent_t prof_ev[PROF_EV * PROF_MAX] = {};

@@ -206,7 +206,7 @@ static void schur_free(SchurState& s) {
   cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.wpart); cudaFree(s.lin_partial); cudaFree(s.rcs);
   cudaFree(s.mx); cudaFree(s.delta_c); cudaFree(s.scal_partial); cudaFree(s.scal); cudaFree(s.lm);
   cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.hist); cudaFree(s.cls_starts); cudaFree(s.cls);
-  cudaFree(s.pid); cudaFree(s.uvs); cudaFree(s.stg); cudaFree(s.tiles); cudaFree(s.tile_range);
+  cudaFree(s.pid); cudaFree(s.lamS); cudaFree(s.uvs); cudaFree(s.stg); cudaFree(s.tiles); cudaFree(s.tile_range);
   if (s.h_lm) cudaFreeHost(s.h_lm);
   if (s.h_cls_starts) cudaFreeHost(s.h_cls_starts);
   for (cudaEvent_t e : s.prof_ev) if (e) cudaEventDestroy(e);
@@ -324,6 +324,8 @@ static int schur_build_layout(acino_sba* h) {
   { const int64_t g = (s.n_rounds + 7) / 8; s.grid_back = (int)(g < 1 ? 1 : (g < s.grid_back_max ? g : s.grid_back_max)); }
   int rc;
   if ((rc = schur_grow(s.pid, s.cap_pid, (size_t)rounds * 32 + 32))) return rc;
+  if ((rc = schur_grow(s.lamS, s.cap_lam, (size_t)rounds * 32 + 32))) return rc;
+  ACINO_CUDA(cudaMemsetAsync(s.lamS, 0, ((size_t)rounds * 32 + 32) * sizeof(double), h->stream));
   if ((rc = schur_grow(s.uvs, s.cap_uvs, (size_t)orows * SCHUR_ROW + SCHUR_ROW))) return rc;
   if ((rc = schur_grow(s.stg, s.cap_stg, (size_t)rows * SCHUR_ROW + SCHUR_ROW))) return rc;
   if ((rc = schur_grow(s.tiles, s.cap_tiles, tiles.size() + 1))) return rc;
@@ -370,8 +372,13 @@ static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumul
   cudaStream_t st = h->stream;
   cudaEvent_t* ev = s.prof_ev + SchurState::PROF_EV * s.prof_n;
   if (prof) ACINO_CUDA(cudaEventRecord(ev[0], st));
-  DISPATCH_C(C, (schur_linearise_kernel<CC><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
-                    s.cls, s.pid, s.uvs, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.stg, s.lin_partial)));
+  if (prm.refine > 0) {
+    DISPATCH_C(C, (schur_linearise_kernel<CC, true><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
+                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.stg, s.lin_partial, s.lamS)));
+  } else {
+    DISPATCH_C(C, (schur_linearise_kernel<CC, false><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
+                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.stg, s.lin_partial, s.lamS)));
+  }
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(ev[1], st));
   ++s.launches;
@@ -452,19 +459,6 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
     ++s.launches;
   }
   ACINO_CUDA(cudaGetLastError());
-  if (prm.refine > 0) {
-    // per-point refinement with the (just accepted) cameras fixed: K3 on the current buffers, skipped on the device
-    // when the step was rejected. Every point keeps its own damping (h->lam) across calls.
-    LmParams lp;
-    lp.inv_c2 = prm.inv_c2; lp.half_c2 = prm.half_c2; lp.gtol = prm.gtol; lp.xtol = prm.xtol; lp.lambda0 = 1e-4;
-    lp.inner_iters = prm.refine; lp.force = 0; lp.ignore_status = 1;
-    lp.skip_pred = prm.refine_skip;
-    LmPointsCtl ctl{&s.lm->last_accept, &s.lm->cur, s.cams_alt, s.X_alt};
-    DISPATCH_C(C, (lm_points_kernel<CC><<<grid_for(h->P, 128), 128, 0, st>>>(h->uv, h->mask, h->P, h->cams, h->X, h->lam, h->cost_p,
-                                                                          h->status, lp, h->counters, ctl, h->order)));
-    ACINO_CUDA(cudaGetLastError());
-    ++s.launches;
-  }
   return ACINO_OK;
 }
 
@@ -518,6 +512,11 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
     const auto t0 = std::chrono::steady_clock::now();
     ACINO_CUDA(cudaMemsetAsync(h->counters, 0, 8 * sizeof(unsigned long long), h->stream));
     const bool listed = l > 0 && prev_act <= (unsigned long long)cap;
+    // The first launch visits every point (8 iterations) and lists those still active; the listed points - a few
+    // thousand - then take the rest of the iteration budget in ONE launch: the same LM iterations per point as one
+    // launch of 8 after the other, without a launch and a host round trip (50 us) for each.
+    const bool finish = listed;
+    lp.inner_iters = finish ? 8 * (max_launches - l) : 8;
     LmPointsCtl ctl{nullptr, nullptr, nullptr, nullptr, listed ? s.polish_list[(l - 1) & 1] : nullptr, listed ? (int)prev_act : 0,
                     s.polish_list[l & 1], cap};
     const int64_t n_visit = listed ? (int64_t)prev_act : h->P;
@@ -526,12 +525,13 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
                          listed ? nullptr : h->order)));
     ACINO_CUDA(cudaGetLastError());
     ++s.launches;
+    if (finish && !trace) break;          // nothing more to decide: no read-back
     ACINO_CUDA(cudaMemcpyAsync(h->h_counters, h->counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
     ACINO_CUDA(cudaStreamSynchronize(h->stream));
     if (trace)
-      fprintf(stderr, "[acino]   polish launch %d: %llu points still active, %.3f ms\n", l, h->h_counters[0],
-              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
-    if (h->h_counters[0] == 0) break;
+      fprintf(stderr, "[acino]   polish launch %d (%d iterations): %llu points still active, %.3f ms\n", l, lp.inner_iters,
+              h->h_counters[0], std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    if (h->h_counters[0] == 0 || finish) break;
     prev_act = h->h_counters[0];
     lp.ignore_status = 0;
   }
@@ -545,8 +545,12 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
   if (rc) return rc;
   SchurState& s = h->schur;
   ACINO_CUDA(cudaEventRecord(h->e0, h->stream));
+  const auto t_init0 = std::chrono::steady_clock::now();
   rc = schur_init_lm(h, o);
   if (rc) return rc;
+  const double init_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_init0).count();
+  double polish_ms = 0.0;
+  int n_sync = 2;          // the read-back of the class sizes and the end of the set-up
   SchurParams prm = make_schur_params(o);
   int it = 0;
   // Polishing (polish_tol): the joint steps settle the cameras within a few tens of iterations, after which the cost
@@ -569,6 +573,7 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     if (rc) return rc;
     ACINO_CUDA(cudaMemcpyAsync(s.h_lm, s.lm, sizeof(SchurLm), cudaMemcpyDeviceToHost, h->stream));
     ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    ++n_sync;
     if (trace) {
       const auto t = std::chrono::steady_clock::now();
       fprintf(stderr, "[acino] it %d: %.3f ms, status %d accept %d rel_dec %.3g lambda %.3g cost %.6f\n", it,
@@ -597,8 +602,11 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
         if (ended) F_end_polish = s.h_lm->F;
         terminal_polish = creeping && s.h_lm->last_rel_dec <= ftol_eff;
         const int l0 = s.launches;
+        const auto t_pol0 = std::chrono::steady_clock::now();
         rc = schur_polish_points(h, prm, 12);
         if (rc) return rc;
+        polish_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_pol0).count();
+        n_sync += 1;
         if (getenv("ACINO_TRACE"))
           fprintf(stderr, "[acino] polish at iteration %d (%s, rel_dec %.3g, cost %.6f): %d launches\n", it,
                   ended ? "end rule" : "creeping", s.h_lm->last_rel_dec, s.h_lm->F, s.launches - l0);
@@ -620,6 +628,7 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     // the last accepted step was refined: one more linearisation for the cost of the final parameters
     SchurParams pf = prm;
     pf.force = 1;
+    pf.refine = 0;      // evaluation only: the points stay where they are
     const int len = rcs_len(h->C);
     rc = schur_launch_build(h, pf, false, false);      // K4a alone: the cost is its sum
     if (rc) return rc;
@@ -646,6 +655,9 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     st->n_accept = l.n_accept;
     st->lambda_final = l.lambda;
     st->gmax = l.gmax;
+    st->init_ms = init_ms;
+    st->polish_ms = polish_ms;
+    st->syncs = n_sync + 2;      // + the two of schur_sync_current
   }
   return ACINO_OK;
 }

@@ -219,22 +219,38 @@ class ScenePipeline:
         if comm is not None and comm[2] > 1:
             self.solver.comm_init(*comm)
 
-    def run(self, uv, lik, thresh, out_points=None, rvec_t0=None, **solver_opts):
+    def run(self, uv, lik, thresh, out_points=None, rvec_t0=None, breakdown=False, **solver_opts):
+        """``breakdown=True`` synchronises between the phases and adds ``st['breakdown_ms']`` = h2d, tri, init (the
+        once-per-solve set-up of the points+extrinsics solver), lm (joint iterations + per-point refinement), polish,
+        d2h - host clock; the extra synchronisations make such a run a little slower than a plain one."""
+        import time
         L = _capi.lib()
+        t0 = time.perf_counter()
         self.uv_d.upload(uv)
         self.lik_d.upload(lik)
+        t1 = time.perf_counter()
         _capi.check(L.acino_triangulate_ring_dev(self.uv_d.ptr, self.lik_d.ptr, float(thresh), self.P, self.C,
                                                  _capi.ptr(self.cams), self.xyz_d.ptr, self.mask_d.ptr, self.ex_d.ptr,
                                                  ct.c_void_p(self.solver.stream)))
+        if breakdown:
+            _capi.check(L.acino_sync())
+        t2 = time.perf_counter()
         self.solver.set_cameras(*self.cam_args)
         if self.mode == MODE_POINTS_AND_EXTRINSICS and rvec_t0 is not None and rvec_t0[0] is not None:
             self.solver.set_rvec_t(rvec_t0[0], rvec_t0[1])
         self.solver.set_points_dev(self.xyz_d)
         st = self.solver.solve(default_opts(self.mode, **solver_opts))
+        t3 = time.perf_counter()
         if out_points is None:
             out_points = np.empty((self.P, 3))
         _capi.check(L.acino_sba_get_points(self.solver._h, _capi.ptr(out_points)))
+        t4 = time.perf_counter()
         st['points'] = out_points
+        if breakdown:
+            ms = lambda a, b: 1e3 * (b - a)
+            st['breakdown_ms'] = dict(h2d=ms(t0, t1), tri=ms(t1, t2), init=st.get('init_ms', 0.0), polish=st.get('polish_ms', 0.0),
+                                      lm=ms(t2, t3) - st.get('init_ms', 0.0) - st.get('polish_ms', 0.0), d2h=ms(t3, t4),
+                                      total=ms(t0, t4))
         return st
 
     def close(self):

@@ -48,7 +48,69 @@ def parse_args():
     ap.add_argument('--masked-frac', type=float, default=0.5, help='fraction of slots at or below dlc_thresh')
     ap.add_argument('--outlier-frac', type=float, default=0.0, help='fraction of observations with N(0,50 px) outlier noise (C5)')
     ap.add_argument('--e2e-solves', type=int, default=3)
+    ap.add_argument('--min-time', type=float, default=0.5, help='the timed region repeats its K steps until it lasts this many seconds')
+    ap.add_argument('--strong-frames', type=int, default=C4_FRAMES,
+                    help='frames of the ONE scene that is sharded over all ranks for the strong-scaling block (0: skip)')
+    ap.add_argument('--no-c1', action='store_true', help='skip the run-to-completion C1 comparison')
     return ap.parse_args()
+
+
+def kernel_source_sha():
+    """Hash of the CUDA sources: profiles/r02_ncu_counts.json carries the hash of the sources its ncu capture was taken
+    with, and its per-launch DRAM bytes / executed flops are attached to the bench line only when they match."""
+    import hashlib
+    h = hashlib.sha1()
+    d = os.path.join(ROOT, 'acinoset_b200', 'csrc')
+    for name in sorted(os.listdir(d)):
+        with open(os.path.join(d, name), 'rb') as f:
+            h.update(name.encode()); h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def c1_scene():
+    """Config C1: 102 frames x 20 keypoints x 6 cameras, seed 0, dlc_thresh 0.5 - the scene of
+    tests/golden/golden_c1.npz, small enough for the reference's CPU algorithm to run to completion."""
+    from acinoset_b200 import synth
+    return synth.make_rig_scene(102, N_KPTS, seed=0)
+
+
+def c1_native():
+    """C1 to completion through the reference-signature path (app.sba_points_fisheye: DataFrame in, DataFrame out)."""
+    import contextlib, io
+    from acinoset_b200 import app, synth
+    sc = c1_scene()
+    df = synth.dense_to_df(sc['uv'], sc['lik'], N_KPTS)
+    df = df[df['likelihood'] > THRESH]
+    scene = os.path.join(ROOT, 'tests', 'golden', 'scene_6cam.json')
+    out = None
+    secs = []
+    for _ in range(3):                     # first call pays library load / context creation
+        t0 = time.perf_counter()
+        with contextlib.redirect_stdout(io.StringIO()):
+            out_df, res = app.sba_points_fisheye(scene, df)
+        secs.append(time.perf_counter() - t0)
+    from acinoset_b200 import sba as sba_mod
+    st = sba_mod.bundle_adjust_points_only.last_stats if hasattr(sba_mod.bundle_adjust_points_only, 'last_stats') else {}
+    return dict(seconds=float(min(secs)), seconds_first_call=float(secs[0]), iterations=int(st.get('iterations', -1)),
+                rmse=float(np.sqrt(np.mean(res['after'] ** 2))), rmse_before=float(np.sqrt(np.mean(res['before'] ** 2))),
+                n_points=int(len(out_df)), n_obs=int(len(res['after']) // 2),
+                path='app.sba_points_fisheye (DataFrame in -> TRI -> points-only SBA -> DataFrame out), host buffers')
+
+
+def c1_reference():
+    """C1 to completion with the reference's CPU algorithm (oracle/ref_port.py: pandas ring triangulation + per-observation
+    OpenCV projection inside scipy least_squares, src/lib/sba.py:181-195), one core as in the reference."""
+    from oracle import ref_port
+    sc = c1_scene()
+    t0 = time.perf_counter()
+    out = ref_port.sba_points_scene(sc['uv'], sc['lik'], THRESH, sc['k'], sc['d'], sc['r'], sc['t'], f_scale=50.0)
+    dt = time.perf_counter() - t0
+    return dict(seconds=float(dt), tri_seconds=float(out['tri_seconds']), sba_seconds=float(out['sba_seconds']),
+                iterations=int(out['iterations']), nfev=int(out['nfev']),
+                rmse=float(np.sqrt(np.mean(out['residuals']['after'] ** 2))),
+                rmse_before=float(np.sqrt(np.mean(out['residuals']['before'] ** 2))),
+                n_points=int(out['n_points']), n_obs=int(out['n_obs']), cores=1,
+                path='oracle/ref_port.sba_points_scene (the reference algorithm: pandas TRI + cv2 per observation in scipy TRF)')
 
 
 def peaks():
@@ -190,13 +252,27 @@ def native_arm(args):
         tv = t.reshape(C, 3) + rng.normal(0, 3e-3, (C, 3))
         solver.set_rvec_t(rv, tv)
     solver.set_points(xyz0)
+    m = _capi.MODE_POINTS_AND_EXTRINSICS if mode == 'extrinsics' else _capi.MODE_POINTS_ONLY
+    t1_ms = None
+    if world > 1:
+        # the same fixed-work iteration on this rank ALONE (no communicator yet): the single-GPU time the scaling
+        # efficiencies of this run are quoted against
+        o1 = dense.default_opts(m, inner_iters=1, force_iters=1, **(dict(point_refine_iters=0) if mode == 'extrinsics' else {}))
+        for _ in range(5):
+            solver.iterate(o1)
+        e0, e1 = ev(), ev()
+        e0.record(stream)
+        for _ in range(50):
+            solver.iterate(o1)
+        e1.record(stream); e1.synchronize()
+        t1_ms = e0.elapsed_time(e1) / 50
+        solver.reset_state()
     if world > 1:
         uid = [dense.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         solver.comm_init(uid[0], rank, world)
     comm_mode = solver.comm_mode()
 
-    m = _capi.MODE_POINTS_AND_EXTRINSICS if mode == 'extrinsics' else _capi.MODE_POINTS_ONLY
     # full solve from the TRI initialisation (solve ms, iterations to converge); at N > 1 the ranks enter together and the
     # first collective (NCCL connection set-up) is spent before the timed solve
     if world > 1:
@@ -220,34 +296,48 @@ def native_arm(args):
     for _ in range(max(args.warmup, 3)):
         solver.iterate(opts)
     if mode == 'extrinsics':
-        solver.profile(True)          # CUDA events around K4 / K6 on the solver's stream, inside the timed region
+        solver.profile(True)          # CUDA events around K4a / K4b / K5 / K6 on the solver's stream, inside the timed region
     barrier()
-    e0, e1 = ev(), ev()
-    e0.record(stream)
-    for _ in range(args.steps):
-        solver.iterate(opts)
-    e1.record(stream)
-    e1.synchronize()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    # EXACTLY K steps per timed block; the block repeats until the timed region lasts --min-time seconds, so that the
+    # clock sampler (and the driver's) sees the GPU under this load. ms_per_step is the mean over all timed steps.
+    ms, repeats = 0.0, 0
+    t_wall0 = time.perf_counter()
+    while True:
+        e0, e1 = ev(), ev()
+        e0.record(stream)
+        for _ in range(args.steps):
+            solver.iterate(opts)
+        e1.record(stream)
+        e1.synchronize()
+        barrier()
+        ms += e0.elapsed_time(e1)
+        repeats += 1
+        go = torch.tensor([1.0 if (time.perf_counter() - t_wall0) < args.min_time else 0.0], device='cuda')
+        if world > 1:
+            dist.all_reduce(go, op=dist.ReduceOp.MIN)      # every rank takes the same number of blocks
+        if go.item() == 0.0 or repeats >= 10000:
+            break
+    timed_steps = args.steps * repeats
     kern = None
     if mode == 'extrinsics':
         pr = solver.profile_read()
         solver.profile(False)
-        # K4 (build) reads the mask of every slot-group, and for existing points the point and its kept observations
+        # the Schur build (K4a linearisation + K4b accumulation) reads the mask of every slot group and, for existing
+        # points, the point and its kept observations; the back-substitution (K6) the same and writes the trial points
         build_bytes = P * 1 + n_pts * 24 + n_obs * 16
         back_bytes = build_bytes + n_pts * 24
-        kern = dict(name=f'schur_build_kernel<{C}>', ms_per_launch=pr['build_ms'], bytes_per_launch=build_bytes,
-                    launches_per_step=5 if world == 1 else (7 if comm_mode == 'peer' else 8), collective=comm_mode, backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes,
-                    profiled_iterations=pr['iterations'])
+        kern = dict(name=f'schur_accum_kernel<{C}>', ms_per_launch=pr['build_ms'], bytes_per_launch=build_bytes,
+                    launches_per_step=6 if world == 1 else (8 if comm_mode == 'peer' else 9), collective=comm_mode,
+                    backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes, linearise_ms=pr['linearise_ms'],
+                    accumulate_ms=pr['accumulate_ms'], solve_ms=pr['solve_ms'], profiled_iterations=pr['iterations'])
     fp64_peak = dense.fp64_peak_tflops()
     if world > 1:
         tms = torch.tensor([ms], device='cuda', dtype=torch.float64)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
         ms = float(tms.item())
     clk = clocks.stop() if clocks else None
-    ms_per_step = ms / args.steps
-    value = world * args.steps / (ms * 1e-3) * (args.frames / C4_FRAMES)
+    ms_per_step = ms / timed_steps
+    value = world * timed_steps / (ms * 1e-3) * (args.frames / C4_FRAMES)
     return dict(locals())
 
 
@@ -290,6 +380,9 @@ def e2e_arm(args, ctx):
         if i > 0:                     # first solve is the warm-up
             times.append(dt)
             iters += last['iterations']
+    if world > 1:
+        dist.barrier()
+    bd = pipe.run(uv_h.numpy(), lik_h.numpy(), THRESH, out_h.numpy(), rv0, breakdown=True, **opts).get('breakdown_ms')
     pipe.close()
     total = float(np.sum(times))
     if world > 1:
@@ -302,7 +395,136 @@ def e2e_arm(args, ctx):
                 step='one full solve per GPU shard: H2D observations+likelihoods, TRI, LM until the stopping rule, D2H points',
                 solve_ms=1e3 * total / len(times), lm_iters_per_solve=iters / len(times), exit_status=last.get('status'),
                 cost_initial=last['cost_initial'], cost_final=last['cost_final'],
+                launches_per_solve=last.get('launches'), host_syncs_per_solve=last.get('syncs'),
+                breakdown_ms=bd, breakdown_note='one extra solve of this rank with a synchronisation between the phases (host clock); '
+                                                'lm = joint LM iterations + per-point refinement, polish = points to convergence with the cameras fixed',
                 h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h))
+
+
+def strong_arm(args, ctx):
+    """Strong scaling as BASELINE.json states configs 4 and 5: ONE scene of --strong-frames frames (seed 4; 119,490 frames
+    = config C4) sharded by frame over all ranks, the reduced camera system exchanged once per LM iteration. Measured in
+    the same run as the weak numbers: the fixed-work LM iteration (max over ranks, device time), a full collective solve
+    from the TRI start on resident inputs, and the same solve end to end from pinned host buffers."""
+    import torch
+    import torch.distributed as dist
+    from acinoset_b200 import _capi, dense
+    rank, world, C, mode, m = ctx['rank'], ctx['world'], ctx['C'], ctx['mode'], ctx['m']
+    F = args.strong_frames
+    sc = ctx['sc'] if (rank == 0 and F == args.frames) else make_shard(F, seed=4)
+    a, b = dense.frame_shard(F, rank, world)
+    uv = np.ascontiguousarray(sc['uv'].reshape(F, N_KPTS, C, 2)[a:b].reshape(-1, C, 2))
+    lik = np.ascontiguousarray(sc['lik'].reshape(F, N_KPTS, C)[a:b].reshape(-1, C))
+    k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
+    Ps = uv.shape[0]
+    L = _capi.lib()
+    cams = _capi.pack_cams(k, d, r, t)
+    uv_d, lik_d = dense.DeviceArray.from_host(uv), dense.DeviceArray.from_host(lik)
+    xyz_d = dense.DeviceArray((Ps, 3), np.float64)
+    mask_d, ex_d = dense.DeviceArray((Ps,), np.uint8), dense.DeviceArray((Ps,), np.uint8)
+    solver = dense.SbaSolver(C, Ps)
+    stream = torch.cuda.ExternalStream(solver.stream)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    _capi.check(L.acino_triangulate_ring_dev(uv_d.ptr, lik_d.ptr, THRESH, Ps, C, _capi.ptr(cams), xyz_d.ptr, mask_d.ptr, ex_d.ptr,
+                                             ct.c_void_p(solver.stream)))
+    solver.set_cameras(k, d, r, t)
+    solver.set_observations_dev(uv_d, mask_d)
+    if mode == 'extrinsics':
+        solver.set_rvec_t(ctx['rv'], ctx['tv'])
+    solver.set_points(np.nan_to_num(xyz_d.download()))
+    if world > 1:
+        uid = [dense.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        solver.comm_init(uid[0], rank, world)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def rank_max(x):
+        if world == 1:
+            return float(x)
+        tt = torch.tensor([x], device='cuda', dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    fixed = dense.default_opts(m, inner_iters=1, force_iters=1, **(dict(point_refine_iters=0) if mode == 'extrinsics' else {}))
+    for _ in range(5):
+        solver.iterate(fixed)
+    solver.reset_state()
+    barrier()
+    st = solver.solve(dense.default_opts(m, **(dict(ftol=1e-10) if mode == 'extrinsics' else {})))
+    solve_ms = rank_max(st['solve_ms'])
+    solver.reset_state()
+    for _ in range(5):
+        solver.iterate(fixed)
+    if mode == 'extrinsics':
+        solver.profile(True)
+    barrier()
+    ms, steps, t0w = 0.0, 0, time.perf_counter()
+    while True:
+        e0, e1 = ev(), ev()
+        e0.record(stream)
+        for _ in range(50):
+            solver.iterate(fixed)
+        e1.record(stream)
+        e1.synchronize()
+        barrier()
+        ms += e0.elapsed_time(e1)
+        steps += 50
+        go = torch.tensor([1.0 if (time.perf_counter() - t0w) < 0.3 else 0.0], device='cuda')
+        if world > 1:
+            dist.all_reduce(go, op=dist.ReduceOp.MIN)
+        if go.item() == 0.0:
+            break
+    ms_per_step = rank_max(ms / steps)
+    kern = None
+    if mode == 'extrinsics':
+        pr = solver.profile_read()
+        solver.profile(False)
+        kern = dict(linearise_ms=pr['linearise_ms'], accumulate_ms=pr['accumulate_ms'], fold_exchange_solve_ms=pr['solve_ms'],
+                    backsub_ms=pr['backsub_ms'])
+    solver.close()
+    for arr in (uv_d, lik_d, xyz_d, mask_d, ex_d):
+        arr.free()
+    # end to end: pinned host shard -> HBM -> TRI -> collective solve -> points back
+    uv_h, lik_h = torch.from_numpy(uv).pin_memory(), torch.from_numpy(lik).pin_memory()
+    out_h = torch.empty((Ps, 3), dtype=torch.float64).pin_memory()
+    comm = None
+    if world > 1 and mode == 'extrinsics':
+        uid = [dense.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        comm = (uid[0], rank, world)
+    pipe = dense.ScenePipeline(Ps, C, k, d, r, t, m, comm)
+    rv0 = (ctx.get('rv'), ctx.get('tv')) if mode == 'extrinsics' else None
+    opts = dict(ftol=1e-10) if mode == 'extrinsics' else {}
+    times, last = [], None
+    for i in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        last = pipe.run(uv_h.numpy(), lik_h.numpy(), THRESH, out_h.numpy(), rv0, **opts)
+        torch.cuda.synchronize()
+        if i > 0:
+            times.append(time.perf_counter() - t0)
+    pipe.close()
+    e2e_ms = rank_max(1e3 * float(np.mean(times)))
+    # the single-GPU time of the same amount of work: this run's own at N = 1, else the rank-alone iteration over a scene
+    # of the same size measured before the communicator was made (native_arm)
+    t1 = ms_per_step if world == 1 else (ctx.get('t1_ms') if args.frames == F else None)
+    out = dict(frames_total=F, frames_per_rank=b - a, scaling='strong', ms_per_step=ms_per_step,
+               value=1e3 / ms_per_step * (F / C4_FRAMES), unit=UNIT, timed_steps=steps,
+               solve_ms=solve_ms, solve_iterations=st['iterations'], solve_launches=st['launches'], solve_status=st.get('status'),
+               cost_initial=st['cost_initial'], cost_final=st['cost_final'],
+               e2e_solve_ms=e2e_ms, e2e_iterations=last['iterations'], kernels_ms_rank0=kern,
+               single_gpu_ms_per_step=t1,
+               efficiency_vs_n1=(t1 / (world * ms_per_step)) if t1 else None)
+    if kern and t1:
+        work = kern['linearise_ms'] + kern['accumulate_ms'] + kern['backsub_ms']
+        out['fixed_cost_us'] = 1e3 * (ms_per_step - work)
+        out['fixed_cost_note'] = ('ms_per_step minus the three kernels whose time shrinks with the shard (K4a, K4b, K6) on rank 0: fold, '
+                                  'exchange pushes and waits, the 36x36 solve (K5), the decision (K7) and launch gaps')
+    return out
 
 
 def cpu_baseline(frames, mode, full_obs):
@@ -354,6 +576,12 @@ def main():
             vals.append(cb['value'])
         v = float(np.median(vals))
         cb['value'] = v
+        c1 = None
+        if not args.no_c1:
+            try:
+                c1 = c1_reference()
+            except Exception as e:
+                c1 = dict(error=f'{type(e).__name__}: {e}')
         line = dict(impl='reference', metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=len(vals), warmup=0,
                     ms_per_step=1e3 / v, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f64',
                     data='synthetic', config=dict(workload=f'{"C4" if args.frames == C4_FRAMES else "custom"} {"points+extrinsics (Schur)" if mode == "extrinsics" else "points-only"} SBA: '
@@ -362,7 +590,9 @@ def main():
                                                   parallelism=f'frame-shard x{args.gpus}',
                                                   note='reference CPU algorithm on rank 0, single-threaded as in the reference (its per-observation '
                                                        'Python/OpenCV loop has no parallel section); bounded sample scaled to the workload'),
-                    cpu_baseline=cb, e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+                    cpu_baseline=cb, e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0,
+                    c1=c1, c1_note='config C1 (102 frames) run TO COMPLETION, not extrapolated: compare `c1.seconds` with the native '
+                                   "arm's `c1.seconds`; `value` above is the C4 rate scaled from a bounded sample, labelled as such")
         print(json.dumps(line))
         return
 
@@ -371,63 +601,93 @@ def main():
     peak, peak_src = peaks()
     mode, P, C = ctx['mode'], ctx['P'], ctx['C']
     e2e = e2e_arm(args, ctx)
+    strong = strong_arm(args, ctx) if args.strong_frames > 0 else None
     if rank != 0:
         import torch.distributed as dist
         dist.destroy_process_group()
         return
     n_obs, n_pts = ctx['n_obs'], ctx['n_pts']
+    timed_steps = ctx['timed_steps']
     if mode == 'points':
         bytes_step = lm_points_bytes(n_pts, n_obs) + (P - n_pts) * 2
         kern_ms = ctx['ms_per_step']
-        kern_name = 'lm_points_kernel<6>'
-        launches = args.steps
+        kern_name = f'lm_points_kernel<{C}>'
+        launches = timed_steps
     else:
         bytes_step = ctx['kern']['bytes_per_launch']
         kern_ms = ctx['kern']['ms_per_launch']
         kern_name = ctx['kern']['name']
-        launches = ctx['kern']['launches_per_step'] * args.steps
+        launches = ctx['kern']['launches_per_step'] * timed_steps
     achieved = bytes_step / (kern_ms * 1e-3) / 1e9
     roofline = dict(bound='hbm', achieved=achieved, peak=peak, unit='GB/s', frac=achieved / peak, traffic=None,
                     kernel=kern_name, algorithmic_bytes_per_launch=int(bytes_step), kernel_ms=kern_ms, peak_source=peak_src,
-                    fp64_peak_tflops_measured=ctx['fp64_peak'],
-                    note='fp64-pipe bound, not HBM bound: see profiles/ for the ncu pipe utilisation')
+                    fp64_peak_tflops_measured=ctx['fp64_peak'])
     if mode == 'extrinsics':
         k6 = ctx['kern']
-        roofline['backsub_kernel'] = dict(kernel=f'schur_backsub_kernel<{C}>', kernel_ms=k6['backsub_ms'],
-                                          algorithmic_bytes_per_launch=int(k6['backsub_bytes']),
-                                          achieved=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9,
-                                          frac=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9 / peak)
+        roofline['kernel'] = f'schur_linearise_kernel<{C}> + schur_accum_kernel<{C}> (the Schur build, K4a + K4b; K4b dominates)'
+        roofline['note'] = ('the Schur build is bound by the fp64 pipe, not by HBM: `achieved` / `frac` are the ALGORITHMIC bytes of the '
+                            'build (mask + point + observations) over K4a + K4b; see `fp64` for the binding roof and `kernels` '
+                            'for each kernel against its own traffic')
         roofline['step_share_of_kernels'] = (k6['ms_per_launch'] + k6['backsub_ms']) / ctx['ms_per_step']
-    # DRAM traffic and executed fp64 flops per launch come from the committed ncu capture of the same workload
-    # (profiles/r01_ncu_counts.json); they are attached only when this run IS that workload
-    try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r01_ncu_counts.json')) as f:
-            ncu = json.load(f)
-        w = ncu['workload']
-        if (args.frames, args.masked_frac, args.outlier_frac) == (w['frames'], w['masked_frac'], w['outlier_frac']) and mode == 'extrinsics':
-            def fp64_block(name, ms):
-                k = ncu['kernels'][name]
-                tf = k['fp64_flops'] / (ms * 1e-3) / 1e12
-                return dict(flops_per_launch=k['fp64_flops'], achieved_tflops=tf, peak_tflops=ctx['fp64_peak'], frac=tf / ctx['fp64_peak'],
-                            pipe_active_pct_ncu=k['fp64_pipe_pct'], source='executed DFMA x2 + DMUL + DADD, ncu SASS page (profiles/r01_ncu_counts.json)')
-            roofline['traffic'] = ncu['kernels'][kern_name]['dram_bytes']
-            roofline['traffic_source'] = 'ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r01_ncu_counts.json)'
-            roofline['fp64'] = fp64_block(kern_name, kern_ms)
-            roofline['traffic_gbs'] = roofline['traffic'] / (kern_ms * 1e-3) / 1e9
-            roofline['traffic_frac_of_hbm_peak'] = roofline['traffic_gbs'] / peak
-            bk = roofline['backsub_kernel']
-            bk['traffic'] = ncu['kernels'][f'schur_backsub_kernel<{C}>']['dram_bytes']
-            bk['traffic_gbs'] = bk['traffic'] / (ctx['kern']['backsub_ms'] * 1e-3) / 1e9
-            bk['traffic_frac_of_hbm_peak'] = bk['traffic_gbs'] / peak       # K6 is the HBM-bound kernel of the path
-            roofline['backsub_kernel']['fp64'] = fp64_block(f'schur_backsub_kernel<{C}>', ctx['kern']['backsub_ms'])
-    except (OSError, KeyError, ValueError):
-        pass
+        kernels = {
+            f'schur_linearise_kernel<{C}>': dict(kernel_ms=k6['linearise_ms']),
+            f'schur_accum_kernel<{C}>': dict(kernel_ms=k6['accumulate_ms']),
+            f'schur_backsub_kernel<{C}>': dict(kernel_ms=k6['backsub_ms'], algorithmic_bytes_per_launch=int(k6['backsub_bytes']),
+                                               achieved=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9,
+                                               frac=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9 / peak),
+            'fold + exchange + schur_solve_kernel': dict(kernel_ms=k6['solve_ms']),
+        }
+        roofline['kernels'] = kernels
+        # DRAM traffic and executed fp64 flops per launch come from a committed ncu capture of the same workload; they are
+        # attached only when the capture was taken with THESE kernel sources (hash of csrc/) and this workload
+        sha = kernel_source_sha()
+        roofline['kernel_source_sha'] = sha
+        try:
+            with open(os.path.join(ROOT, 'profiles', 'r02_ncu_counts.json')) as f:
+                ncu = json.load(f)
+            w = ncu['workload']
+            same = (args.frames, args.masked_frac, args.outlier_frac) == (w['frames'], w['masked_frac'], w['outlier_frac'])
+            if not same or ncu.get('kernel_source_sha') != sha:
+                roofline['ncu_counts'] = (f"not attached: profiles/r02_ncu_counts.json was captured for sources {ncu.get('kernel_source_sha')} / "
+                                          f"workload {w}, this run is {sha} / frames {args.frames}")
+            else:
+                src = 'profiles/r02_ncu_counts.json (ncu --set full of scripts/profile_target.py, same sources and workload)'
+                flops = dram = 0
+                for name, blk in kernels.items():
+                    kk = ncu['kernels'].get(name)
+                    if not kk:
+                        continue
+                    ms_k = blk['kernel_ms']
+                    blk['traffic'] = kk['dram_bytes']
+                    blk['traffic_gbs'] = kk['dram_bytes'] / (ms_k * 1e-3) / 1e9
+                    blk['traffic_frac_of_hbm_peak'] = blk['traffic_gbs'] / peak
+                    tf = kk['fp64_flops'] / (ms_k * 1e-3) / 1e12
+                    blk['fp64'] = dict(flops_per_launch=kk['fp64_flops'], achieved_tflops=tf, peak_tflops=ctx['fp64_peak'],
+                                       frac=tf / ctx['fp64_peak'], pipe_active_pct_ncu=kk['fp64_pipe_pct'])
+                    if 'linearise' in name or 'accum' in name:
+                        flops += kk['fp64_flops']; dram += kk['dram_bytes']
+                roofline['traffic'] = dram
+                roofline['traffic_source'] = 'ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, K4a + K4b; ' + src
+                roofline['traffic_gbs'] = dram / (kern_ms * 1e-3) / 1e9
+                roofline['traffic_frac_of_hbm_peak'] = roofline['traffic_gbs'] / peak
+                tf = flops / (kern_ms * 1e-3) / 1e12
+                roofline['fp64'] = dict(flops_per_launch=flops, achieved_tflops=tf, peak_tflops=ctx['fp64_peak'], frac=tf / ctx['fp64_peak'],
+                                        source='executed DFMA x2 + DMUL + DADD of K4a + K4b, ncu SASS page; ' + src)
+        except (OSError, KeyError, ValueError) as e:
+            roofline['ncu_counts'] = f'not attached: {type(e).__name__}'
     tri_gbs = tri_bytes(P, C) / (ctx['tri_ms'] * 1e-3) / 1e9
     cb = None
     if not args.no_cpu_baseline and world == 1:
         cb = cpu_baseline(args.cpu_frames, mode, n_obs)
     st = ctx['st_solve']
+    c1 = None
+    if not args.no_c1 and world == 1:
+        try:
+            c1 = c1_native()
+        except Exception as e:          # the headline must not depend on the comparison block
+            c1 = dict(error=f'{type(e).__name__}: {e}')
     line = dict(metric=METRIC, value=ctx['value'], unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+                timed_steps=timed_steps, timed_blocks=ctx['repeats'], timed_region_s=ctx['ms'] * 1e-3,
                 ms_per_step=ctx['ms_per_step'], higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f64',
                 data='synthetic',
                 config=dict(workload=f'{"C4" if args.frames == C4_FRAMES else "custom"} {"points+extrinsics (Schur)" if mode == "extrinsics" else "points-only"} SBA: '
@@ -438,7 +698,12 @@ def main():
                                         'peer': 'NVLink peer-memory exchange fused into K5 / K7 (csrc/acino_sba_xchg.cuh)'}[(ctx['kern'] or {}).get('collective', 'single')]),
                 clocks=ctx['clk'], e2e=e2e, gpu_launches=launches, roofline=roofline, cpu_baseline=cb,
                 solve=dict(ms=st['solve_ms'], iterations=st['iterations'], launches=st['launches'], cost_initial=st['cost_initial'],
-                           cost_final=st['cost_final'], n_unconverged=st['n_unconverged']),
+                           cost_final=st['cost_final'], n_unconverged=st['n_unconverged'], init_ms=st.get('init_ms'),
+                           polish_ms=st.get('polish_ms'), host_syncs=st.get('syncs'),
+                           iterations_per_s=1e3 * st['iterations'] / st['solve_ms'] if st['solve_ms'] else None,
+                           note='full solve from the TRI start on resident inputs (refinement and polishing on): the '
+                                'solve-representative rate; `value` is the fixed-work LM iteration'),
+                strong=strong, c1=c1, single_rank_ms_per_step=ctx.get('t1_ms'),
                 tri=dict(ms=ctx['tri_ms'], points_per_s=P / (ctx['tri_ms'] * 1e-3), gbs=tri_gbs, frac_hbm=tri_gbs / peak,
                          algorithmic_bytes=tri_bytes(P, C)))
     print(json.dumps(line))

@@ -162,6 +162,10 @@ typedef struct {
   double n_accept;         /* accepted LM steps */
   double lambda_final;     /* Marquardt damping at exit */
   double gmax;             /* max |gradient| at the last linearisation */
+  double init_ms;          /* points+extrinsics: of solve_ms, the once-per-solve set-up (points sorted by observation mask,
+                              observations in that layout, tiles; K3's visiting order). Host clock around the synchronised section */
+  double polish_ms;        /* points+extrinsics: of solve_ms, the polishing launches (K3 to convergence, cameras fixed) */
+  double syncs;            /* host synchronisations inside the solve */
 } acino_sba_stats;
 
 void acino_sba_default_opts(acino_sba_opts* o, int mode);
