@@ -319,6 +319,89 @@ __device__ __forceinline__ double schur_cost_point(const double* __restrict__ sc
   return pm1;
 }
 
+// per-launch sums of a linearising thread: robust cost (with the running product of (1+z): sum of log1p(z) = log of the
+// product), sum g^T h, max |g|, max |X|
+struct LinAcc { double cost, gh, gmax, xmax, cprod; };
+
+// One point of the sorted numbering: linearise (rows into blk: the round's staging block), refine it with the cameras fixed when asked to, and write its record. Shared by
+// schur_linearise_kernel and schur_build_kernel.
+template <bool REFINE>
+__device__ __forceinline__ void schur_linearise_one(const double* __restrict__ sc, unsigned m, int k, const double2* __restrict__ ob,
+                                                    double2* __restrict__ blk, unsigned p, bool valid, double X, double Y, double Z,
+                                                    double* __restrict__ Xp, double* __restrict__ lam_slot, double lam, int refine,
+                                                    bool need_cost, const SchurParams& prm, LinAcc& A) {
+  PointLin L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, valid, prm.inv_c2, prm.hfloor);
+  if (REFINE && refine > 0 && valid) {
+    // ---- the point's own LM with the cameras fixed, from the linearisation just taken
+    double lp = lam_slot[0];
+    if (!(lp > 0.0)) lp = 1e-4;
+    double nu = 2.0;
+    bool moved = false;
+#pragma unroll 1
+    for (int it = 0; it < refine; ++it) {
+      const double gm = fmax(fabs(L.g0), fmax(fabs(L.g1), fabs(L.g2)));
+      if (!(gm > prm.gtol)) break;
+      const Sym3Inv iv = damped_inverse3(L.v00, L.v01, L.v02, L.v11, L.v12, L.v22, lp);
+      const double d0 = -fma(iv.i00, L.g0, fma(iv.i01, L.g1, iv.i02 * L.g2));
+      const double d1 = -fma(iv.i01, L.g0, fma(iv.i11, L.g1, iv.i12 * L.g2));
+      const double d2 = -fma(iv.i02, L.g0, fma(iv.i12, L.g1, iv.i22 * L.g2));
+      const double pred = 0.5 * (lp * (iv.D0 * d0 * d0 + iv.D1 * d1 * d1 + iv.D2 * d2 * d2) - (L.g0 * d0 + L.g1 * d1 + L.g2 * d2));
+      const double F = prm.half_c2 * log1p(L.pm1);
+      if (pred <= prm.refine_skip * fmax(F, prm.half_c2)) break;        // nothing to gain
+      const bool last = (it + 1 == refine);       // no further step in this launch: the trial's cost is enough
+      PointLin T;
+      if (last) T.pm1 = schur_cost_point(sc, m, ob, X + d0, Y + d1, Z + d2, prm.inv_c2);
+      else T = schur_lin_point<false>(sc, m, k, ob, blk, X + d0, Y + d1, Z + d2, true, prm.inv_c2, prm.hfloor);
+      const double act = F - prm.half_c2 * log1p(T.pm1);
+      if (act > 0.0 && pred > 0.0) {          // NaN-safe: comparisons fail on a non-finite trial cost
+        const double q = 2.0 * (act / pred) - 1.0;
+        lp = fmax(lp * fmax(1.0 / 3.0, 1.0 - q * q * q), 1e-12);
+        nu = 2.0;
+        const double dmax = fmax(fabs(d0), fmax(fabs(d1), fabs(d2)));
+        const double xmax = fmax(fabs(X), fmax(fabs(Y), fabs(Z)));
+        X += d0; Y += d1; Z += d2;
+        moved = true;
+        if (last) break;
+        L = T;
+        if (dmax <= prm.xtol * (xmax + prm.xtol)) break;
+      } else {
+        lp *= nu;
+        nu *= 2.0;
+        if (lp > 1e16) { lp = 1e16; break; }
+      }
+    }
+    lam_slot[0] = lp;
+    if (moved) {
+      Xp[3 * (size_t)p] = X; Xp[3 * (size_t)p + 1] = Y; Xp[3 * (size_t)p + 2] = Z;
+      L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, true, prm.inv_c2, prm.hfloor);      // the rows at the refined point
+    }
+  }
+  double i00 = 0, i01 = 0, i02 = 0, i11 = 0, i12 = 0, i22 = 0, h0 = 0, h1 = 0, h2 = 0;
+  if (valid) {
+    if (need_cost) {
+      A.cprod *= 1.0 + L.pm1;
+      if (A.cprod > 1e150) { A.cost += prm.half_c2 * log(A.cprod); A.cprod = 1.0; }      // a point contributes up to ~1e100
+    }
+    const Sym3Inv iv = damped_inverse3(L.v00, L.v01, L.v02, L.v11, L.v12, L.v22, lam);
+    i00 = iv.i00; i01 = iv.i01; i02 = iv.i02; i11 = iv.i11; i12 = iv.i12; i22 = iv.i22;
+    h0 = fma(i00, L.g0, fma(i01, L.g1, i02 * L.g2));
+    h1 = fma(i01, L.g0, fma(i11, L.g1, i12 * L.g2));
+    h2 = fma(i02, L.g0, fma(i12, L.g1, i22 * L.g2));
+    // g^T h of the point block: with dX = -(h + V^-1 s) the gradient term of the predicted reduction is
+    // -g^T dX = g^T h + h^T s; the first part is summed here (RCS scalar [1]), the second in K6
+    A.gh += fma(L.g0, h0, fma(L.g1, h1, L.g2 * h2));
+    A.gmax = fmax(A.gmax, fmax(fabs(L.g0), fmax(fabs(L.g1), fabs(L.g2))));
+    A.xmax = fmax(A.xmax, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
+  }
+  double2* __restrict__ pt = blk + (size_t)(4 * k) * SCHUR_ROW;
+  pt[0] = make_double2(X, Y);
+  pt[SCHUR_ROW] = make_double2(Z, i00);
+  pt[2 * SCHUR_ROW] = make_double2(i01, i02);
+  pt[3 * SCHUR_ROW] = make_double2(i11, i12);
+  pt[4 * SCHUR_ROW] = make_double2(i22, h0);
+  pt[5 * SCHUR_ROW] = make_double2(h1, h2);
+}
+
 // ---- K4a: linearisation (+ embedded per-point refinement). One thread per point of the sorted numbering, one warp per
 // round, 16 warps per SM. Residual + Jacobian of the point's k observations (the camera is the same for the whole warp:
 // broadcast reads), V = sum N^T N, g = sum N^T e, damped inverse, h = V^-1 g; everything K4b and K6 need goes to the
@@ -361,8 +444,7 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
   for (int i = tid; i < C * CAM_STRIDE; i += SCHUR_LIN_TB) sc[i] = cams[i];
   for (int i = tid; i <= NCLS; i += SCHUR_LIN_TB) { s_round0[i] = cls->round0[i]; s_blk0[i] = cls->blk0[i]; s_uv0[i] = cls->uv0[i]; }
   __syncthreads();
-  double cost_acc = 0.0, gmax_acc = 0.0, xmax_acc = 0.0, gh_acc = 0.0;
-  double cprod = 1.0;     // running product of (1+z_u)(1+z_v): sum of log1p(z) = log of the product
+  LinAcc A = {0.0, 0.0, 0.0, 0.0, 1.0};
   const unsigned n_rounds = skip ? 0u : s_round0[NCLS];
   for (unsigned r = blockIdx.x * NW + warp; r < n_rounds; r += gridDim.x * NW) {
     const int m = schur_class_of_round(s_round0, NCLS, r);
@@ -375,78 +457,9 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
     const bool valid = p != 0xFFFFFFFFu;
     double X = 0.0, Y = 0.0, Z = 0.0;
     if (valid) { X = Xp[3 * (size_t)p]; Y = Xp[3 * (size_t)p + 1]; Z = Xp[3 * (size_t)p + 2]; }
-    PointLin L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, valid, prm.inv_c2, prm.hfloor);
-    if (REFINE && refine > 0 && valid) {
-      // ---- the point's own LM with the cameras fixed, from the linearisation just taken
-      double lp = lamS[gs];
-      if (!(lp > 0.0)) lp = 1e-4;
-      double nu = 2.0;
-      bool moved = false;
-#pragma unroll 1
-      for (int it = 0; it < refine; ++it) {
-        const double gm = fmax(fabs(L.g0), fmax(fabs(L.g1), fabs(L.g2)));
-        if (!(gm > prm.gtol)) break;
-        const Sym3Inv iv = damped_inverse3(L.v00, L.v01, L.v02, L.v11, L.v12, L.v22, lp);
-        const double d0 = -fma(iv.i00, L.g0, fma(iv.i01, L.g1, iv.i02 * L.g2));
-        const double d1 = -fma(iv.i01, L.g0, fma(iv.i11, L.g1, iv.i12 * L.g2));
-        const double d2 = -fma(iv.i02, L.g0, fma(iv.i12, L.g1, iv.i22 * L.g2));
-        const double pred = 0.5 * (lp * (iv.D0 * d0 * d0 + iv.D1 * d1 * d1 + iv.D2 * d2 * d2) - (L.g0 * d0 + L.g1 * d1 + L.g2 * d2));
-        const double F = prm.half_c2 * log1p(L.pm1);
-        if (pred <= prm.refine_skip * fmax(F, prm.half_c2)) break;        // nothing to gain
-        const bool last = (it + 1 == refine);       // no further step in this launch: the trial's cost is enough
-        PointLin T;
-        if (last) T.pm1 = schur_cost_point(sc, m, ob, X + d0, Y + d1, Z + d2, prm.inv_c2);
-        else T = schur_lin_point<false>(sc, m, k, ob, blk, X + d0, Y + d1, Z + d2, true, prm.inv_c2, prm.hfloor);
-        const double act = F - prm.half_c2 * log1p(T.pm1);
-        if (act > 0.0 && pred > 0.0) {          // NaN-safe: comparisons fail on a non-finite trial cost
-          const double q = 2.0 * (act / pred) - 1.0;
-          lp = fmax(lp * fmax(1.0 / 3.0, 1.0 - q * q * q), 1e-12);
-          nu = 2.0;
-          const double dmax = fmax(fabs(d0), fmax(fabs(d1), fabs(d2)));
-          const double xmax = fmax(fabs(X), fmax(fabs(Y), fabs(Z)));
-          X += d0; Y += d1; Z += d2;
-          moved = true;
-          if (last) break;
-          L = T;
-          if (dmax <= prm.xtol * (xmax + prm.xtol)) break;
-        } else {
-          lp *= nu;
-          nu *= 2.0;
-          if (lp > 1e16) { lp = 1e16; break; }
-        }
-      }
-      lamS[gs] = lp;
-      if (moved) {
-        Xp[3 * (size_t)p] = X; Xp[3 * (size_t)p + 1] = Y; Xp[3 * (size_t)p + 2] = Z;
-        L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, true, prm.inv_c2, prm.hfloor);      // the rows at the refined point
-      }
-    }
-    double i00 = 0, i01 = 0, i02 = 0, i11 = 0, i12 = 0, i22 = 0, h0 = 0, h1 = 0, h2 = 0;
-    if (valid) {
-      if (need_cost) {
-        cprod *= 1.0 + L.pm1;
-        if (cprod > 1e150) { cost_acc += prm.half_c2 * log(cprod); cprod = 1.0; }      // a point contributes up to ~1e100
-      }
-      const Sym3Inv iv = damped_inverse3(L.v00, L.v01, L.v02, L.v11, L.v12, L.v22, lam);
-      i00 = iv.i00; i01 = iv.i01; i02 = iv.i02; i11 = iv.i11; i12 = iv.i12; i22 = iv.i22;
-      h0 = fma(i00, L.g0, fma(i01, L.g1, i02 * L.g2));
-      h1 = fma(i01, L.g0, fma(i11, L.g1, i12 * L.g2));
-      h2 = fma(i02, L.g0, fma(i12, L.g1, i22 * L.g2));
-      // g^T h of the point block: with dX = -(h + V^-1 s) the gradient term of the predicted reduction is
-      // -g^T dX = g^T h + h^T s; the first part is summed here (RCS scalar [1]), the second in K6
-      gh_acc += fma(L.g0, h0, fma(L.g1, h1, L.g2 * h2));
-      gmax_acc = fmax(gmax_acc, fmax(fabs(L.g0), fmax(fabs(L.g1), fabs(L.g2))));
-      xmax_acc = fmax(xmax_acc, fmax(fabs(X), fmax(fabs(Y), fabs(Z))));
-    }
-    double2* __restrict__ pt = blk + (size_t)(4 * k) * SCHUR_ROW;
-    pt[0] = make_double2(X, Y);
-    pt[SCHUR_ROW] = make_double2(Z, i00);
-    pt[2 * SCHUR_ROW] = make_double2(i01, i02);
-    pt[3 * SCHUR_ROW] = make_double2(i11, i12);
-    pt[4 * SCHUR_ROW] = make_double2(i22, h0);
-    pt[5 * SCHUR_ROW] = make_double2(h1, h2);
+    schur_linearise_one<REFINE>(sc, m, k, ob, blk, p, valid, X, Y, Z, Xp, lamS + gs, lam, refine, need_cost, prm, A);
   }
-  cost_acc += prm.half_c2 * log(cprod);
+  double cost_acc = A.cost + prm.half_c2 * log(A.cprod), gh_acc = A.gh, gmax_acc = A.gmax, xmax_acc = A.xmax;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     cost_acc += __shfl_xor_sync(0xffffffffu, cost_acc, o);
@@ -491,6 +504,8 @@ constexpr int kSchurUnroll = SCHUR_UNROLL;
 __host__ __device__ constexpr int schur_round_cost(int k) { return k * (k + 1) + 1; }
 struct SchurTile {
   unsigned row0;             // first staging row
+  unsigned uvrow0;           // first observation row
+  unsigned round0;           // first round (sorted point g = 32 * round + lane)
   unsigned short rounds;     // rounds in the tile (<= SCHUR_BUF_ROWS / schur_rows(k))
   unsigned char mask;        // the class
   unsigned char pad;
@@ -680,7 +695,7 @@ schur_accum_kernel(const SchurTile* __restrict__ tiles, const unsigned* __restri
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  SchurTile tl = {0u, 0, 0, 0}, tn = {0u, 0, 0, 0};
+  SchurTile tl = {0u, 0u, 0u, 0, 0, 0}, tn = {0u, 0u, 0u, 0, 0, 0};
   if (t_a < t_b) {
     tl = tiles[t_a];
     if (warp == 0) schur_load_tile(bufs, stg, tl, lane, &s_full[0]);
@@ -767,11 +782,14 @@ schur_accum_kernel(const SchurTile* __restrict__ tiles, const unsigned* __restri
 // One CTA. partial = [n_partial][LEN] (the build kernel's per-CTA partials, or the single all-reduced vector);
 // maxp = [n_max][2] maxima (|g_p|, |X|).
 template <int C>
-__global__ void __launch_bounds__(1024)
+#ifndef SCHUR_SOLVE_TB
+#define SCHUR_SOLVE_TB 1024
+#endif
+__global__ void __launch_bounds__(SCHUR_SOLVE_TB)
 schur_solve_kernel(const double* __restrict__ partial, int n_partial, const double* __restrict__ maxp, int n_max,
                    const double* __restrict__ cams0, const double* __restrict__ cams1, double* __restrict__ cams_trial0,
                    double* __restrict__ cams_trial1, SchurLm* __restrict__ lm, SchurParams prm,
-                   double* __restrict__ delta_c, const unsigned long long* wait_flags, unsigned long long wait_seq) {
+                   double* __restrict__ delta_c, XchgDev xd, unsigned long long* __restrict__ xcnt) {
   constexpr int NU = rcs_units(C), LEN = rcs_len(C), n = 6 * C;
   __shared__ double r[LEN];
   __shared__ double A[n][n + 1];
@@ -782,15 +800,23 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   __shared__ double rhs_diag;
   __shared__ int fail;
   const int tid = threadIdx.x;
-  if (wait_flags) {
-    // peer exchange (acino_sba_xchg.cuh): partial / maxp are this rank's slots, one row per rank, written by the peers
+  if (xcnt) {
+    // peer exchange (acino_sba_xchg.cuh): the partials are this rank's slots, one row per rank, written by the peers
     // over NVLink; wait for every rank's sequence number, then add the rows in rank order (the same on every rank).
     // The wait comes before the early return: every push is consumed, which is what makes two slot parities enough.
-    const bool ok = xchg_wait(wait_flags, n_partial, wait_seq, tid);
+    const unsigned long long seq = xcnt[0] + 1;
+    unsigned char* own = xd.base[xd.rank];
+    const double* slot = xchg_slot_a(own, xd.nranks, xd.len, (int)(seq & 1));
+    partial = slot;
+    n_partial = xd.nranks;
+    maxp = slot + (size_t)xd.nranks * xd.len;
+    n_max = xd.nranks;
+    const bool ok = xchg_wait(xchg_flags(own, 0), xd.nranks, seq, tid);
     if (__syncthreads_or(!ok)) {
       if (tid == 0) lm->status = 7;      // a peer never arrived: fail the solve instead of hanging
       return;
     }
+    if (tid == 0) xcnt[0] = seq;         // (every thread has read the count before the barrier above)
   }
   if (lm->status != 0 && !prm.force) return;
   for (int i = tid; i < LEN; i += blockDim.x) {
@@ -862,12 +888,12 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   {
     constexpr int NA = n + 1;
     constexpr int NE = NA * (NA + 1) / 2 - 1;          // without the corner (n, n)
-    constexpr int EPT = (NE + 1023) / 1024;
+    constexpr int EPT = (NE + SCHUR_SOLVE_TB - 1) / SCHUR_SOLVE_TB;
     double a[EPT];
     int ei[EPT], ej[EPT];
 #pragma unroll
     for (int t = 0; t < EPT; ++t) {
-      const int e = tid + t * 1024;
+      const int e = tid + t * SCHUR_SOLVE_TB;
       int ii = 0;
       while ((ii + 1) * (ii + 2) / 2 <= e) ++ii;       // row of packed lower-triangular index e
       ei[t] = e < NE ? ii : -1;
@@ -1087,15 +1113,20 @@ schur_backsub_kernel(const SchurClasses* __restrict__ cls, const unsigned* __res
 __global__ void __launch_bounds__(256)
 schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* __restrict__ dx_override,
                     const double* __restrict__ delta_c, int n6, SchurLm* __restrict__ lm, SchurParams prm,
-                    const unsigned long long* wait_flags, unsigned long long wait_seq) {
+                    XchgDev xd, unsigned long long* __restrict__ xcnt) {
   __shared__ double red[3][8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (wait_flags) {      // peer exchange: scal holds one row per rank, written by the peers (waited for even when idle)
-    const bool ok = xchg_wait(wait_flags, n_scal, wait_seq, tid);
+  if (xcnt) {      // peer exchange: one row per rank, written by the peers (waited for even when idle)
+    const unsigned long long seq = xcnt[1] + 1;
+    unsigned char* own = xd.base[xd.rank];
+    scal = xchg_slot_b(own, xd.nranks, xd.len, (int)(seq & 1));
+    n_scal = xd.nranks;
+    const bool ok = xchg_wait(xchg_flags(own, 1), xd.nranks, seq, tid);
     if (__syncthreads_or(!ok)) {
       if (tid == 0) lm->status = 7;
       return;
     }
+    if (tid == 0) xcnt[1] = seq;
   }
   if (lm->status != 0 && !prm.force) return;
   double a = 0, b = 0, c = 0;
@@ -1230,13 +1261,18 @@ __global__ void schur_init_kernel(SchurLm* lm, double lambda0) {
 struct SchurState {
   static constexpr int PROF_MAX = 256, PROF_EV = 6;
   bool ready = false, inited = false, prof_on = false;
+  bool use_graph = true;                   // the iteration replayed as a CUDA graph (ACINO_GRAPH=0: kernel by kernel)
+  cudaGraphExec_t iter_exec = nullptr;     // the captured iteration of the current solve
+  SchurParams iter_prm{};                  // the parameters it was captured with (they are baked into the launches)
+  int iter_launches = 0;                   // kernels in it
+  long long graph_replays = 0;
   int sms = 148;
   int grid_lin = 0, grid_build = 0, grid_back = 0, grid_back_max = 0, launches = 0, prof_n = 0;
   double* cams_alt = nullptr;
   double* X_alt = nullptr;
   double* rcs_partial = nullptr;           // [sms][LEN] per-CTA partial systems of K4b
   double* wpart = nullptr;                 // [sms * SCHUR_NW][LEN] per-warp partial systems of K4b (L2 resident)
-  double* lin_partial = nullptr;           // [4 sms][4] per-CTA rows of K4a
+  double* lin_partial = nullptr;           // [4 sms][4] per-CTA rows of K4a / the fused build
   double* rcs = nullptr;
   double* mx = nullptr;
   double* delta_c = nullptr;

@@ -75,12 +75,12 @@ static bool xchg_barrier(acino_sba* h, int timeout_ms) {
 static void xchg_destroy(acino_sba* h, bool collective) {
   PeerXchg& x = h->xchg;
   if (collective) {
-    if (!xchg_barrier(h, 5000)) { x = PeerXchg(); return; }
+    if (!xchg_barrier(h, 5000)) { if (x.cnt) cudaFree(x.cnt); x = PeerXchg(); return; }
     for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
       if (x.mapped[r]) cudaIpcCloseMemHandle(x.mapped[r]);
       x.mapped[r] = nullptr;
     }
-    if (!xchg_barrier(h, 5000)) { x = PeerXchg(); return; }
+    if (!xchg_barrier(h, 5000)) { if (x.cnt) cudaFree(x.cnt); x = PeerXchg(); return; }
   } else {
     for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
       if (x.mapped[r]) cudaIpcCloseMemHandle(x.mapped[r]);
@@ -88,6 +88,7 @@ static void xchg_destroy(acino_sba* h, bool collective) {
     }
   }
   if (x.local) cudaFree(x.local);
+  if (x.cnt) cudaFree(x.cnt);
   x = PeerXchg();
 }
 
@@ -140,6 +141,9 @@ static int xchg_setup(acino_sba* h) {
   x.dev.rank = h->rank;
   x.dev.nranks = R;
   x.dev.len = len;
+  ACINO_CUDA(cudaMalloc(&x.cnt, 2 * sizeof(unsigned long long)));
+  ACINO_CUDA(cudaMemsetAsync(x.cnt, 0, 2 * sizeof(unsigned long long), h->stream));
+  ACINO_CUDA(cudaStreamSynchronize(h->stream));
   x.enabled = true;
   return ACINO_OK;
 }
@@ -153,6 +157,10 @@ static void comm_destroy(acino_sba* h) {
 // ---- state ---------------------------------------------------------------------------------------------------
 static void schur_free(SchurState& s);
 static int schur_alloc(acino_sba* h);
+static void schur_drop_graph(SchurState& s) {
+  if (s.iter_exec) cudaGraphExecDestroy(s.iter_exec);
+  s.iter_exec = nullptr;
+}
 static int schur_ensure(acino_sba* h) {
   if (h->schur.ready) return ACINO_OK;
   const int rc = schur_alloc(h);
@@ -197,12 +205,14 @@ static int schur_alloc(acino_sba* h) {
   DISPATCH_C(C, (cudaFuncSetAttribute(schur_accum_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)SCHUR_ACCUM_SMEM)));
   ACINO_CUDA(cudaGetLastError());
+  { const char* env = getenv("ACINO_GRAPH"); s.use_graph = !(env && env[0] == '0'); }
   s.ready = true;
   s.inited = false;
   return ACINO_OK;
 }
 
 static void schur_free(SchurState& s) {
+  schur_drop_graph(s);
   cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.wpart); cudaFree(s.lin_partial); cudaFree(s.rcs);
   cudaFree(s.mx); cudaFree(s.delta_c); cudaFree(s.scal_partial); cudaFree(s.scal); cudaFree(s.lm);
   cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.hist); cudaFree(s.cls_starts); cudaFree(s.cls);
@@ -310,6 +320,8 @@ static int schur_build_layout(acino_sba* h) {
           const unsigned long long R = base + (t < rem ? 1 : 0);
           SchurTile tl;
           tl.row0 = (unsigned)(hc.blk0[m] + (r - hc.round0[m]) * schur_rows(k));
+          tl.uvrow0 = (unsigned)(hc.uv0[m] + (r - hc.round0[m]) * k);
+          tl.round0 = (unsigned)r;
           tl.rounds = (unsigned short)R; tl.mask = (unsigned char)m; tl.pad = 0;
           tiles.push_back(tl);
           r += R;
@@ -345,6 +357,7 @@ static int schur_build_layout(acino_sba* h) {
 
 static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
   SchurState& s = h->schur;
+  schur_drop_graph(s);          // grids and buffers of the captured launches belong to the previous layout
   schur_init_kernel<<<1, 1, 0, h->stream>>>(s.lm, o->lambda0);
   ACINO_CUDA(cudaGetLastError());
   // The alternate point buffer starts as a copy of the points: K6 writes trial rows for existing points only, so the
@@ -389,6 +402,8 @@ static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumul
     ++s.launches;
   }
   if (prof) ACINO_CUDA(cudaEventRecord(ev[2], st));
+  // the per-CTA partial systems and K4a's sums, folded in a fixed order by len/32 CTAs (a fold by the last CTA of K4b
+  // was measured: one CTA chasing 148 partials per entry costs 33 us, this launch 8)
   fold_partials_kernel<<<(len + 31) / 32, 256, 0, st>>>(s.rcs_partial, accumulate ? s.grid_build : 0, len, s.rcs, nullptr, 0, 0, 0, 0,
                                                         s.mx, s.lin_partial, s.grid_lin, rcs_units(C) * RCS_UNIT);
   ACINO_CUDA(cudaGetLastError());
@@ -396,27 +411,23 @@ static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumul
   return ACINO_OK;
 }
 
-// one LM iteration on the handle's stream, no host synchronisation
-static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
+// the kernels of one LM iteration, enqueued on the handle's stream (directly, or into a stream capture)
+static int schur_enqueue_iteration(acino_sba* h, const SchurParams& prm, bool prof) {
   SchurState& s = h->schur;
   const int C = h->C, len = rcs_len(C);
   cudaStream_t st = h->stream;
-  const bool prof = s.prof_on && s.prof_n < SchurState::PROF_MAX;
   cudaEvent_t* ev = s.prof_ev + SchurState::PROF_EV * s.prof_n;
   int rc = schur_launch_build(h, prm, true, prof);
   if (rc) return rc;
   PeerXchg& px = h->xchg;
+  const XchgDev none{};
   if (h->nranks > 1 && px.enabled) {
     // peer exchange: push this rank's folded system into every rank's slot; K5 waits for all ranks and adds the rows
-    const unsigned long long seq = ++px.seq_a;
-    xchg_push_rcs_kernel<<<h->nranks, 256, 0, st>>>(px.dev, s.rcs, s.mx, seq);
+    xchg_push_rcs_kernel<<<h->nranks, 256, 0, st>>>(px.dev, s.rcs, s.mx, px.cnt);
     ACINO_CUDA(cudaGetLastError());
     ++s.launches;
-    unsigned char* own = (unsigned char*)px.local;
-    const double* slot = xchg_slot_a(own, h->nranks, len, (int)(seq & 1));
-    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, 1024, 0, st>>>(slot, h->nranks, slot + (size_t)h->nranks * len, h->nranks, h->cams,
-                                                            s.cams_alt, h->cams, s.cams_alt, s.lm, prm, s.delta_c,
-                                                            xchg_flags(own, 0), seq)));
+    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, SCHUR_SOLVE_TB, 0, st>>>(nullptr, 0, nullptr, 0, h->cams, s.cams_alt, h->cams, s.cams_alt,
+                                                                       s.lm, prm, s.delta_c, px.dev, px.cnt)));
   } else {
     if (h->nranks > 1) {
       ACINO_NCCL(g_nccl.GroupStart());
@@ -425,8 +436,8 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
       ACINO_NCCL(g_nccl.GroupEnd());
       ++s.launches;
     }
-    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, 1024, 0, st>>>(s.rcs, 1, s.mx, 1, h->cams, s.cams_alt, h->cams, s.cams_alt, s.lm, prm,
-                                                            s.delta_c, nullptr, 0ull)));
+    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, SCHUR_SOLVE_TB, 0, st>>>(s.rcs, 1, s.mx, 1, h->cams, s.cams_alt, h->cams, s.cams_alt, s.lm,
+                                                                       prm, s.delta_c, none, nullptr)));
   }
   ++s.launches;
   ACINO_CUDA(cudaGetLastError());
@@ -437,12 +448,9 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
   if (prof) { ACINO_CUDA(cudaEventRecord(ev[4], st)); ++s.prof_n; }
   ++s.launches;
   if (h->nranks > 1 && px.enabled) {
-    const unsigned long long seq = ++px.seq_b;
-    unsigned char* own = (unsigned char*)px.local;
-    xchg_push_scal_kernel<<<1, 256, 0, st>>>(px.dev, s.scal_partial, s.grid_back, seq);
+    xchg_push_scal_kernel<<<1, 256, 0, st>>>(px.dev, s.scal_partial, s.grid_back, px.cnt);
     ACINO_CUDA(cudaGetLastError());
-    schur_decide_kernel<<<1, 256, 0, st>>>(xchg_slot_b(own, h->nranks, len, (int)(seq & 1)), h->nranks, nullptr, s.delta_c, 6 * C,
-                                           s.lm, prm, xchg_flags(own, 1), seq);
+    schur_decide_kernel<<<1, 256, 0, st>>>(nullptr, 0, nullptr, s.delta_c, 6 * C, s.lm, prm, px.dev, px.cnt);
     s.launches += 2;
   } else if (h->nranks > 1) {
     fold_partials_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, 4, s.scal, s.scal_partial, s.grid_back, 1, 4, 2,
@@ -452,13 +460,45 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
     ACINO_NCCL(g_nccl.AllReduce(s.scal, s.scal, 4, kNcclDouble, kNcclSum, h->nccl_comm, st));
     ACINO_NCCL(g_nccl.AllReduce(s.scal + 4, s.scal + 4, 1, kNcclDouble, kNcclMax, h->nccl_comm, st));
     ACINO_NCCL(g_nccl.GroupEnd());
-    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal, 1, s.scal + 4, s.delta_c, 6 * C, s.lm, prm, nullptr, 0ull);
+    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal, 1, s.scal + 4, s.delta_c, 6 * C, s.lm, prm, none, nullptr);
     s.launches += 3;
   } else {
-    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm, nullptr, 0ull);
+    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm, none, nullptr);
     ++s.launches;
   }
   ACINO_CUDA(cudaGetLastError());
+  return ACINO_OK;
+}
+
+// One LM iteration on the handle's stream, no host synchronisation. The launches of an iteration do not change within
+// a solve (every decision is taken on the device: LM state, buffer selection, exchange sequence numbers), so they are
+// captured into a CUDA graph at the first iteration of a solve and REPLAYED afterwards: one launch call per iteration
+// and no launch gaps between its kernels. ACINO_GRAPH=0 (or profiling, or the NCCL fallback of the exchange) launches
+// the kernels one by one.
+static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
+  SchurState& s = h->schur;
+  const bool prof = s.prof_on && s.prof_n < SchurState::PROF_MAX;
+  const bool graphs = s.use_graph && !s.prof_on && (h->nranks == 1 || h->xchg.enabled);
+  if (!graphs) return schur_enqueue_iteration(h, prm, prof);
+  if (s.iter_exec && memcmp(&s.iter_prm, &prm, sizeof(SchurParams)) != 0) schur_drop_graph(s);
+  if (!s.iter_exec) {
+    const int l0 = s.launches;
+    cudaGraph_t g = nullptr;
+    ACINO_CUDA(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = schur_enqueue_iteration(h, prm, false);
+    const cudaError_t e = cudaStreamEndCapture(h->stream, &g);
+    if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+    ACINO_CUDA(e);
+    const cudaError_t ei = cudaGraphInstantiate(&s.iter_exec, g, 0);
+    cudaGraphDestroy(g);
+    ACINO_CUDA(ei);
+    s.iter_prm = prm;
+    s.iter_launches = s.launches - l0;
+    s.launches = l0;
+  }
+  ACINO_CUDA(cudaGraphLaunch(s.iter_exec, h->stream));
+  s.launches += s.iter_launches;
+  ++s.graph_replays;
   return ACINO_OK;
 }
 

@@ -36,7 +36,10 @@ struct PeerXchg {
   XchgDev dev{};
   void* local = nullptr;                       // this rank's buffer (cudaMalloc)
   void* mapped[XCHG_MAX_RANKS] = {};           // peers' buffers opened with cudaIpcOpenMemHandle (nullptr for the own rank)
-  unsigned long long seq_a = 0, seq_b = 0;     // collectives issued so far (all ranks issue the same sequence)
+  // collectives completed so far, on the DEVICE: cnt[0] camera systems (K5 counts), cnt[1] trial scalars (K7 counts). All
+  // ranks issue the same sequence, so the counters agree everywhere; keeping them on the device lets the iteration be
+  // replayed as a CUDA graph (a sequence number passed by value would be baked into the captured launches).
+  unsigned long long* cnt = nullptr;
 };
 
 __host__ __device__ inline size_t xchg_a_doubles(int R, int len) { return (size_t)R * len + (size_t)R * 2; }
@@ -83,7 +86,8 @@ __device__ __forceinline__ bool xchg_wait(const unsigned long long* flags, int n
 // Collective A, producer side: CTA b writes this rank's folded camera system (len doubles) and its two maxima into
 // slot [rank] of peer b (b == rank: the own buffer), then publishes sequence number seq on that peer.
 __global__ void __launch_bounds__(256)
-xchg_push_rcs_kernel(XchgDev x, const double* __restrict__ rcs, const double* __restrict__ mx, unsigned long long seq) {
+xchg_push_rcs_kernel(XchgDev x, const double* __restrict__ rcs, const double* __restrict__ mx, const unsigned long long* __restrict__ cnt) {
+  const unsigned long long seq = cnt[0] + 1;          // the consumer of this collective (K5) advances the count
   unsigned char* dst_base = x.base[blockIdx.x];
   double* slot = xchg_slot_a(dst_base, x.nranks, x.len, (int)(seq & 1));
   double* d_rcs = slot + (size_t)x.rank * x.len;
@@ -99,7 +103,8 @@ xchg_push_rcs_kernel(XchgDev x, const double* __restrict__ rcs, const double* __
 // [trial cost, predicted reduction, max |dX|, 0] in a fixed order, write the row into slot [rank] of every peer and
 // publish seq there.
 __global__ void __launch_bounds__(256)
-xchg_push_scal_kernel(XchgDev x, const double* __restrict__ scal_partial, int n_partial, unsigned long long seq) {
+xchg_push_scal_kernel(XchgDev x, const double* __restrict__ scal_partial, int n_partial, const unsigned long long* __restrict__ cnt) {
+  const unsigned long long seq = cnt[1] + 1;          // K7 advances the count
   __shared__ double red[3][8];
   __shared__ double row[4];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

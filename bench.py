@@ -295,8 +295,6 @@ def native_arm(args):
     clocks = ClockSampler(local) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
         solver.iterate(opts)
-    if mode == 'extrinsics':
-        solver.profile(True)          # CUDA events around K4a / K4b / K5 / K6 on the solver's stream, inside the timed region
     barrier()
     # EXACTLY K steps per timed block; the block repeats until the timed region lasts --min-time seconds, so that the
     # clock sampler (and the driver's) sees the GPU under this load. ms_per_step is the mean over all timed steps.
@@ -318,6 +316,19 @@ def native_arm(args):
         if go.item() == 0.0 or repeats >= 10000:
             break
     timed_steps = args.steps * repeats
+    if mode == 'extrinsics':
+        # per-kernel device times: a profiled pass of the same step right after the timed region (CUDA events between the
+        # kernels on the solver's stream; with the events in place the iteration is launched kernel by kernel, the timed
+        # region above replays it as a CUDA graph)
+        solver.profile(True)
+        e0, e1 = ev(), ev()
+        e0.record(stream)
+        for _ in range(max(args.steps, 50)):
+            solver.iterate(opts)
+        e1.record(stream)
+        e1.synchronize()
+        ms_per_step_profiled = e0.elapsed_time(e1) / max(args.steps, 50)
+        barrier()
     kern = None
     if mode == 'extrinsics':
         pr = solver.profile_read()
@@ -329,7 +340,8 @@ def native_arm(args):
         kern = dict(name=f'schur_accum_kernel<{C}>', ms_per_launch=pr['build_ms'], bytes_per_launch=build_bytes,
                     launches_per_step=6 if world == 1 else (8 if comm_mode == 'peer' else 9), collective=comm_mode,
                     backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes, linearise_ms=pr['linearise_ms'],
-                    accumulate_ms=pr['accumulate_ms'], solve_ms=pr['solve_ms'], profiled_iterations=pr['iterations'])
+                    accumulate_ms=pr['accumulate_ms'], solve_ms=pr['solve_ms'], profiled_iterations=pr['iterations'],
+                    ms_per_step_profiled=ms_per_step_profiled)
     fp64_peak = dense.fp64_peak_tflops()
     if world > 1:
         tms = torch.tensor([ms], device='cuda', dtype=torch.float64)
@@ -459,8 +471,6 @@ def strong_arm(args, ctx):
     solver.reset_state()
     for _ in range(5):
         solver.iterate(fixed)
-    if mode == 'extrinsics':
-        solver.profile(True)
     barrier()
     ms, steps, t0w = 0.0, 0, time.perf_counter()
     while True:
@@ -481,6 +491,10 @@ def strong_arm(args, ctx):
     ms_per_step = rank_max(ms / steps)
     kern = None
     if mode == 'extrinsics':
+        solver.profile(True)          # a profiled pass (kernel by kernel, events between the kernels) for the per-kernel times
+        for _ in range(50):
+            solver.iterate(fixed)
+        barrier()
         pr = solver.profile_read()
         solver.profile(False)
         kern = dict(linearise_ms=pr['linearise_ms'], accumulate_ms=pr['accumulate_ms'], fold_exchange_solve_ms=pr['solve_ms'],
@@ -628,7 +642,10 @@ def main():
         roofline['note'] = ('the Schur build is bound by the fp64 pipe, not by HBM: `achieved` / `frac` are the ALGORITHMIC bytes of the '
                             'build (mask + point + observations) over K4a + K4b; see `fp64` for the binding roof and `kernels` '
                             'for each kernel against its own traffic')
-        roofline['step_share_of_kernels'] = (k6['ms_per_launch'] + k6['backsub_ms']) / ctx['ms_per_step']
+        roofline['step_share_of_kernels'] = (k6['ms_per_launch'] + k6['backsub_ms']) / k6['ms_per_step_profiled']
+        roofline['kernel_times_from'] = (f"{k6['profiled_iterations']} profiled iterations right after the timed region (CUDA events between the kernels "
+                                         f"on the solver's stream, kernel-by-kernel launches: {k6['ms_per_step_profiled']:.4f} ms per step; the timed "
+                                         f"region replays the iteration as a CUDA graph: {ctx['ms_per_step']:.4f} ms per step)")
         kernels = {
             f'schur_linearise_kernel<{C}>': dict(kernel_ms=k6['linearise_ms']),
             f'schur_accum_kernel<{C}>': dict(kernel_ms=k6['accumulate_ms']),
