@@ -85,6 +85,7 @@ SIGNATURES = {
     'acino_sba_profile_read': (_I, [_P, ct.POINTER(_D), ct.POINTER(_D), ct.POINTER(_I)]),
     'acino_sba_profile_read_kernels': (_I, [_P, _P, ct.POINTER(_I)]),
     'acino_sba_lm_state': (_I, [_P, _P]),
+    'acino_sba_history': (_I, [_P, _P, _I, ct.POINTER(_I)]),
     'acino_fp64_peak': (_I, [ct.POINTER(_D)]),
     'acino_nccl_unique_id': (_I, [_P]),
     'acino_sba_comm_init': (_I, [_P, _P, _I, _I]),

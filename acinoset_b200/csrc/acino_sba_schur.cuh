@@ -13,6 +13,7 @@
 //   unit C+k (pair c<c')  : [0..35] S_cc' row-major
 //   scalars               : [0] robust cost at the current parameters, [1] sum over the points of g^T h
 #pragma once
+#include <vector>
 #include "acino_common.cuh"
 #include "acino_sba_xchg.cuh"
 
@@ -1297,6 +1298,9 @@ struct SchurState {
   int64_t E = 0;                           // existing points of the current solve
   int64_t n_rounds = 0, n_tiles = 0, n_obs_rows = 0, n_stg_rows = 0;
   cudaEvent_t prof_ev[PROF_EV * PROF_MAX] = {};
+  // acino_sba_solve's iteration log (what scipy prints with verbose=2): rows of 6 doubles
+  // [iteration, cost after the decision, cost reduction (0 when rejected), max |step|, max |gradient|, accepted]
+  std::vector<double> history;
 };
 
 }  // namespace acino

@@ -590,6 +590,8 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
   if (rc) return rc;
   const double init_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_init0).count();
   double polish_ms = 0.0;
+  double F_prev = 0.0;
+  s.history.assign(6, 0.0);      // row 0: the starting point, filled in after the first linearisation
   int n_sync = 2;          // the read-back of the class sizes and the end of the set-up
   SchurParams prm = make_schur_params(o);
   int it = 0;
@@ -614,6 +616,18 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     ACINO_CUDA(cudaMemcpyAsync(s.h_lm, s.lm, sizeof(SchurLm), cudaMemcpyDeviceToHost, h->stream));
     ACINO_CUDA(cudaStreamSynchronize(h->stream));
     ++n_sync;
+    {
+      const SchurLm& l = *s.h_lm;
+      const double row[6] = {(double)l.iter, l.F, l.last_accept ? F_prev - l.F : 0.0, l.dxmax, l.gmax, (double)l.last_accept};
+      s.history.insert(s.history.end(), row, row + 6);
+      if (it == 0) {      // row 0 of the log is the starting point (cost at the first linearisation)
+        s.history[1] = l.F0;
+        s.history[4] = l.gmax;
+        double* r1 = &s.history[6];
+        r1[2] = l.last_accept ? l.F0 - l.F : 0.0;
+      }
+      F_prev = l.F;
+    }
     if (trace) {
       const auto t = std::chrono::steady_clock::now();
       fprintf(stderr, "[acino] it %d: %.3f ms, status %d accept %d rel_dec %.3g lambda %.3g cost %.6f\n", it,
@@ -809,6 +823,17 @@ int acino_sba_profile_read(acino_sba_t* h, double* build_ms, double* backsub_ms,
   if (rc) return rc;
   if (build_ms) *build_ms = ms4[0] + ms4[1];
   if (backsub_ms) *backsub_ms = ms4[3];
+  return ACINO_OK;
+}
+
+int acino_sba_history(acino_sba_t* h, double* rows6, int cap_rows, int* n_rows) {
+  H_CHECK(h);
+  ARG_CHECK(n_rows && cap_rows >= 0 && (cap_rows == 0 || rows6), "history");
+  const std::vector<double>& v = h->schur.history;
+  const int n = (int)(v.size() / 6);
+  *n_rows = n;
+  const int m = n < cap_rows ? n : cap_rows;
+  if (m > 0) memcpy(rows6, v.data(), (size_t)m * 6 * sizeof(double));
   return ACINO_OK;
 }
 

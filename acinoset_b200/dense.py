@@ -169,6 +169,16 @@ class SbaSolver:
         return dict(build_ms=b.value, backsub_ms=k.value, iterations=n.value, linearise_ms=float(ms4[0]),
                     accumulate_ms=float(ms4[1]), solve_ms=float(ms4[2]))
 
+    def history(self):
+        """Iteration log of the latest points+extrinsics solve: (n, 6) = iteration, cost, cost reduction, max |step|,
+        max |gradient|, accepted; row 0 is the starting point."""
+        n = ct.c_int()
+        _capi.check(_capi.lib().acino_sba_history(self._h, None, 0, ct.byref(n)))
+        out = np.zeros((n.value, 6))
+        if n.value:
+            _capi.check(_capi.lib().acino_sba_history(self._h, _capi.ptr(out), n.value, ct.byref(n)))
+        return out
+
     def lm_state(self):
         out = np.empty(16)
         _capi.check(_capi.lib().acino_sba_lm_state(self._h, _capi.ptr(out)))

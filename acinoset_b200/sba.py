@@ -57,12 +57,13 @@ def _lists_to_dense(points_2d, point_3d_indices, camera_indices, n_points, n_cam
     if n_cams > _capi.MAX_CAMS:
         raise NotImplementedError(f'at most {_capi.MAX_CAMS} cameras per scene')
     slot = pidx * n_cams + cidx
-    if np.unique(slot).size != slot.size:
+    present = np.zeros(n_points * n_cams, dtype=bool)
+    present[slot] = True
+    if int(present.sum()) != slot.size:
         raise NotImplementedError('a camera observes a point more than once; the dense slot layout needs unique (point, camera) pairs')
     uv = np.zeros((n_points * n_cams, 2))
     uv[slot] = obs
-    mask = np.zeros(n_points, dtype=np.uint8)
-    np.bitwise_or.at(mask, pidx, (1 << cidx).astype(np.uint8))
+    mask = (present.reshape(n_points, n_cams) * (1 << np.arange(n_cams, dtype=np.uint16))).sum(axis=1).astype(np.uint8)
     return uv.reshape(n_points, n_cams, 2), mask, slot
 
 
@@ -120,6 +121,26 @@ def cost_func_points_extrinsics(params, n_cams, n_points, point_3d_indices, came
 
 # ========== SBA ==========
 
+_TERMINATION = {1.0: '`gtol` termination condition is satisfied.', 2.0: '`ftol` termination condition is satisfied.',
+                3.0: '`xtol` termination condition is satisfied.', 4.0: 'The damping is exhausted: no descent left at double precision.',
+                0.0: 'The maximum number of iterations is exceeded.'}
+
+
+def _print_iteration_table(hist, st):
+    """What scipy.optimize.least_squares prints with verbose=2 (src/lib/sba.py:170,189; core/sba.py tees it into sba.log):
+    one row per LM iteration in scipy's column layout, then its two closing lines. `Step norm` is max |step| (the
+    quantity the xtol rule of this solver tests), `Total nfev` the linearisations so far."""
+    print('{0:^15}{1:^15}{2:^15}{3:^15}{4:^15}{5:^15}'.format('Iteration', 'Total nfev', 'Cost', 'Cost reduction', 'Step norm', 'Optimality'))
+    for i, row in enumerate(hist):
+        if i == 0:
+            print('{0:^15}{1:^15}{2:^15.4e}{3:^15}{4:^15}{5:^15.2e}'.format(0, 1, row[1], '', '', row[4]))
+        else:
+            print('{0:^15}{1:^15}{2:^15.4e}{3:^15.2e}{4:^15.2e}{5:^15.2e}'.format(int(row[0]), int(row[0]) + 1, row[1], row[2], row[3], row[4]))
+    print(_TERMINATION.get(st.get('status'), 'The solver stopped.'))
+    print('Function evaluations {0}, initial cost {1:.4e}, final cost {2:.4e}, first-order optimality {3:.2e}.'.format(
+        st['iterations'] + 1, st['cost_initial'], st['cost_final'], st.get('gmax', float('nan'))))
+
+
 def _print_stats(st):
     print(f"   LM iterations: {st['iterations']}, kernel launches: {st['launches']}, "
           f"cost {st['cost_initial']:.6e} -> {st['cost_final']:.6e}, unconverged: {st['n_unconverged']}, "
@@ -154,9 +175,11 @@ def bundle_adjust_points_only(points_2d, points_3d, point_3d_indices, camera_ind
 
 
 def bundle_adjust_points_and_extrinsics(points_2d, points_3d, point_3d_indices, camera_indices, k_arr, d_arr, r_arr, t_arr,
-                                        project_func, **solver_opts):
-    """src/lib/sba.py:158-178. Parameters [rvecs | tvecs | points] (additive rvec update, as scipy's x + step),
-    Cauchy loss with scipy's default f_scale = 1.0. Returns (obj_pts, r_arr (n,3,3), t_arr (n,3,1), residuals)."""
+                                        project_func, verbose=2, **solver_opts):
+    """src/lib/sba.py:158-178. The reference's parameters are [rvecs | tvecs | points] with scipy's additive update; the
+    solver here steps every camera by a world-frame twist (R <- R Exp(w), t <- t + R tau: the same set of (R, t), the same
+    minimiser) and converts back. Cauchy loss with scipy's default f_scale = 1.0. verbose=2 (the reference's literal)
+    prints scipy's iteration table. Returns (obj_pts, r_arr (n,3,3), t_arr (n,3,1), residuals)."""
     _require_fisheye(project_func)
     points_3d = _capi.f64(points_3d).reshape(-1, 3)
     n_points, n_cams = len(points_3d), len(k_arr)
@@ -173,6 +196,8 @@ def bundle_adjust_points_and_extrinsics(points_2d, points_3d, point_3d_indices, 
         t0 = time()
         st = solver.solve(dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, **solver_opts))
         t1 = time()
+        if verbose and verbose >= 2:
+            _print_iteration_table(solver.history(), st)
         _print_stats(st)
         print(f'\nOptimization took {t1-t0:.2f} seconds')
         obj_pts = solver.get_points()
@@ -330,13 +355,19 @@ def _sba_points(scene_fpath, points_2d_df, triangulate_func, project_func):
     residuals). TRI initialises, the index arrays come from the same inner merge as the reference's (sba.py:296-302),
     the points-only solve runs with f_scale=50."""
     k_arr, d_arr, r_arr, t_arr, _cam_res = load_scene(scene_fpath)
-    points_3d_df = get_pairwise_3d_points_from_df(points_2d_df, k_arr, d_arr.reshape((-1, 4)), r_arr, t_arr, triangulate_func)
+    if not _is_fisheye_triangulate(triangulate_func):
+        raise NotImplementedError('only triangulate_points_fisheye is supported (CUDA path, no fallback)')
+    from .utils import _pairwise_3d_with_index
+    points_3d_df, row3d = _pairwise_3d_with_index(points_2d_df, k_arr, d_arr.reshape((-1, 4)), r_arr, t_arr)
     points_3d_df['point_index'] = points_3d_df.index
     points_3d = np.array(points_3d_df[['x', 'y', 'z']], dtype=np.float64)
-    points_df = points_2d_df.merge(points_3d_df, how='inner', on=['frame', 'marker'], suffixes=('_cam', ''))
-    points_2d = np.array(points_df[['x_cam', 'y_cam']], dtype=np.float64)
-    point_indices = np.array(points_df['point_index'])
-    camera_indices = np.array(points_df['camera'])
+    # The reference builds the index arrays with an inner merge of the 2-D frame with the 3-D frame on (frame, marker)
+    # (sba.py:296-302): the rows of the 2-D frame whose point was triangulated, in the 2-D frame's order, each with the
+    # row number of its point. The lowering above already knows that row for every 2-D row: same arrays, no merge.
+    keep = row3d >= 0
+    points_2d = np.stack([points_2d_df['x'].to_numpy(dtype=np.float64)[keep], points_2d_df['y'].to_numpy(dtype=np.float64)[keep]], axis=1)
+    point_indices = row3d[keep]
+    camera_indices = points_2d_df['camera'].to_numpy()[keep]
     print('bundle_adjust_points_only')
     pts_3d, res = bundle_adjust_points_only(points_2d, points_3d, point_indices, camera_indices, k_arr, d_arr, r_arr, t_arr,
                                             project_func, f_scale=50)

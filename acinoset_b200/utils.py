@@ -38,31 +38,50 @@ def _is_fisheye_triangulate(func):
     return callable(func) and getattr(func, '__name__', '') == 'triangulate_points_fisheye'
 
 
-def df_to_dense(points_2d_df, n_cams):
+def _point_keys(frame, marker):
+    """(frame, marker) rows -> one int64 key per row whose order is the order of sorted (frame, marker-name), i.e. of
+    groupby(['frame', 'marker']) at src/lib/utils.py:348, plus what is needed to map keys back. Integer arithmetic on
+    factorised columns instead of a MultiIndex of (int, str) tuples: 0.5 s instead of 19 s for the 7 M rows of config C4."""
+    m_codes, m_uniq = pd.factorize(np.asarray(marker, dtype=object), sort=True)
+    f_arr = np.asarray(frame)
+    f_codes, f_uniq = pd.factorize(f_arr, sort=True)
+    n_m = max(len(m_uniq), 1)
+    return f_codes.astype(np.int64) * n_m + m_codes.astype(np.int64), f_uniq, np.asarray(m_uniq, dtype=object), n_m
+
+
+def df_to_dense(points_2d_df, n_cams, return_keys=False):
     """Lowers the (already thresholded) DataFrame[frame, camera, marker, x, y, ...] to dense slots.
     Point order = sorted (frame, marker), i.e. the row order of groupby(['frame','marker']) at
-    src/lib/utils.py:348. Returns uv (P,C,2), present (P,C) bool, frames (P,), markers (P,), slot (n_rows,)."""
+    src/lib/utils.py:348. Returns uv (P,C,2), present (P,C) bool, frames (P,), markers (P,), slot (n_rows,)
+    (+ the rows' point ids when return_keys)."""
     df = points_2d_df
     if len(df) == 0:
-        return (np.zeros((0, n_cams, 2)), np.zeros((0, n_cams), bool), np.zeros(0), np.zeros(0, dtype=object),
-                np.zeros(0, dtype=np.int64))
-    keys = pd.MultiIndex.from_arrays([df['frame'].to_numpy(), df['marker'].to_numpy()])
-    codes, uniq = keys.factorize(sort=True)
-    P = len(uniq)
+        out = (np.zeros((0, n_cams, 2)), np.zeros((0, n_cams), bool), np.zeros(0), np.zeros(0, dtype=object),
+               np.zeros(0, dtype=np.int64))
+        return out + (np.zeros(0, dtype=np.int64),) if return_keys else out
+    key, f_uniq, m_uniq, n_m = _point_keys(df['frame'].to_numpy(), df['marker'].to_numpy())
+    # the keys are bounded by (frames x markers): a presence bitmap and its running count give the sorted unique keys
+    # and every row's point id without a sort
+    seen = np.zeros(len(f_uniq) * n_m, dtype=bool)
+    seen[key] = True
+    uniq_keys = np.flatnonzero(seen)
+    codes = (np.cumsum(seen, dtype=np.int64) - 1)[key]
+    P = len(uniq_keys)
     cam = df['camera'].to_numpy().astype(np.int64)
     if cam.min() < 0 or cam.max() >= n_cams:
         raise ValueError('camera index outside the scene')
     slot = codes.astype(np.int64) * n_cams + cam
-    if np.unique(slot).size != slot.size:
+    present = np.zeros(P * n_cams, dtype=bool)
+    present[slot] = True
+    if int(present.sum()) != slot.size:
         raise ValueError('duplicate (frame, marker, camera) rows: each camera may observe a point once')
     uv = np.zeros((P * n_cams, 2))
     uv[slot, 0] = df['x'].to_numpy(dtype=np.float64)
     uv[slot, 1] = df['y'].to_numpy(dtype=np.float64)
-    present = np.zeros(P * n_cams, dtype=bool)
-    present[slot] = True
-    frames = np.asarray(uniq.get_level_values(0))
-    markers = np.asarray(uniq.get_level_values(1))
-    return uv.reshape(P, n_cams, 2), present.reshape(P, n_cams), frames, markers, slot
+    frames = np.asarray(f_uniq)[uniq_keys // n_m]
+    markers = m_uniq[uniq_keys % n_m]
+    out = (uv.reshape(P, n_cams, 2), present.reshape(P, n_cams), frames, markers, slot)
+    return out + (codes.astype(np.int64),) if return_keys else out
 
 
 def get_pairwise_3d_points_from_df(points_2d_df, k_arr, d_arr, r_arr, t_arr, triangulate_func, verbose=True):
@@ -72,8 +91,15 @@ def get_pairwise_3d_points_from_df(points_2d_df, k_arr, d_arr, r_arr, t_arr, tri
     a fisheye triangulation (the reference's or this package's); other camera models are not built."""
     if not _is_fisheye_triangulate(triangulate_func):
         raise NotImplementedError('only triangulate_points_fisheye is supported (CUDA path, no fallback)')
+    out_df, _extra = _pairwise_3d_with_index(points_2d_df, k_arr, d_arr, r_arr, t_arr, verbose)
+    return out_df
+
+
+def _pairwise_3d_with_index(points_2d_df, k_arr, d_arr, r_arr, t_arr, verbose=True):
+    """get_pairwise_3d_points_from_df + what _sba_points needs to build its index arrays without a second relational
+    pass: per row of points_2d_df the row of the returned frame its (frame, marker) went to (-1: not triangulated)."""
     n_cams = len(k_arr)
-    uv, present, frames, markers, _slot = df_to_dense(points_2d_df, n_cams)
+    uv, present, frames, markers, _slot, codes = df_to_dense(points_2d_df, n_cams, return_keys=True)
     if verbose:
         for a in range(n_cams):
             b = (a + 1) % n_cams
@@ -84,10 +110,13 @@ def get_pairwise_3d_points_from_df(points_2d_df, k_arr, d_arr, r_arr, t_arr, tri
                 print(f'No pairwise points between camera {a} and {b}')
         print()
     if uv.shape[0] == 0:
-        return pd.DataFrame({'frame': [], 'marker': [], 'x': [], 'y': [], 'z': []})
+        return pd.DataFrame({'frame': [], 'marker': [], 'x': [], 'y': [], 'z': []}), np.zeros(0, dtype=np.int64)
     xyz, exists, _mask = dense.triangulate_ring(uv, present.astype(np.float64), 0.5, k_arr, d_arr, r_arr, t_arr)
-    return pd.DataFrame({'frame': frames[exists], 'marker': markers[exists],
-                         'x': xyz[exists, 0], 'y': xyz[exists, 1], 'z': xyz[exists, 2]})
+    row_of_point = np.full(len(exists), -1, dtype=np.int64)
+    row_of_point[exists] = np.arange(int(exists.sum()))
+    out_df = pd.DataFrame({'frame': frames[exists], 'marker': markers[exists],
+                           'x': xyz[exists, 0], 'y': xyz[exists, 1], 'z': xyz[exists, 2]})
+    return out_df, row_of_point[codes]
 
 
 def load_points(fpath, verbose=False):

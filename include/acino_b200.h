@@ -198,6 +198,11 @@ int acino_sba_profile_read_kernels(acino_sba_t* h, double* ms4, int* n_iteration
  * [6]=trial cost, [7]=predicted reduction, [8]=gain ratio, [9]=max |dx|, [10]=max |x|, [11]=nu, [12]=relative decrease of
  * the last accepted step, [13]=rejected, [14]=Cholesky failures, [15]=cost at the first linearisation */
 int acino_sba_lm_state(acino_sba_t* h, double* out16);
+/* The iteration log of the latest points+extrinsics acino_sba_solve - what scipy prints with verbose=2
+ * (src/lib/sba.py:170: least_squares(..., verbose=2)): rows of 6 doubles [iteration, cost, cost reduction, max |step|,
+ * max |gradient| (first-order optimality), accepted]; row 0 is the starting point. n_rows receives the number of rows
+ * the log holds, at most cap_rows are copied. */
+int acino_sba_history(acino_sba_t* h, double* rows6, int cap_rows, int* n_rows);
 
 /* multi-GPU (frame-sharded) — one handle per rank (one process per GPU); NCCL is dlopen'ed from the process
  * (libnccl.so.2). Every rank calls solve / iterate collectively; the reduced camera system (6C x 6C + gradient + cost)

@@ -103,3 +103,30 @@ def test_manual_points_preparation(rig):
     assert len(p3) == len(kept) and pidx.max() == len(kept) - 1 and len(p2) == len(pidx) == len(cidx)
     assert np.abs(p3 - X[kept]).max() < 1e-4                   # noise-free pixels triangulate to the truth (f32 storage)
     assert p2.dtype == np.float32 and p3.dtype == np.float32
+
+
+def test_extrinsics_solve_prints_scipy_iteration_table(rig, golden_dir, capsys):
+    """The reference calls least_squares(..., verbose=2) (src/lib/sba.py:170) and core/sba.py tees the table into sba.log:
+    the same columns come out here, one row per LM iteration, with monotone costs on accepted rows."""
+    g = np.load(os.path.join(golden_dir, 'golden_calib.npz'))
+    k, d, r, t, _ = rig
+    sba.bundle_adjust_points_and_extrinsics(g['points_2d'], g['points_3d'], g['point_indices'], g['camera_indices'], k, d,
+                                            g['r0'], g['t0'], calib.project_points_fisheye)
+    st = sba.bundle_adjust_points_and_extrinsics.last_stats
+    lines = capsys.readouterr().out.splitlines()
+    head = [i for i, l in enumerate(lines) if 'Iteration' in l and 'Total nfev' in l and 'Optimality' in l]
+    assert len(head) == 1
+    rows = []
+    for l in lines[head[0] + 1:]:
+        parts = l.split()
+        if not parts or not parts[0].isdigit():
+            break
+        rows.append(parts)
+    assert len(rows) == st['iterations'] + 1
+    assert [int(p[0]) for p in rows] == list(range(st['iterations'] + 1))
+    assert abs(float(rows[0][2]) - st['cost_initial']) <= 1e-4 * st['cost_initial']
+    assert abs(float(rows[-1][2]) - st['cost_final']) <= 1e-3 * st['cost_final']
+    costs = [float(p[2]) for p in rows]
+    assert all(b <= a * (1 + 1e-12) for a, b in zip(costs, costs[1:]))
+    assert any('termination condition is satisfied' in l for l in lines)
+    assert any(l.startswith('Function evaluations') for l in lines)
