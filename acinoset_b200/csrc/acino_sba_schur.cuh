@@ -43,7 +43,26 @@ struct SchurLm {
 struct SchurParams {
   double inv_c2, half_c2, gtol, ftol, xtol, hfloor, refine_skip;
   int force, refine;
+  // limits of the current layout, for the bounds-checked build (-DACINO_BOUNDS): slot groups, rounds, staging rows,
+  // observation rows
+  long long n_points;
+  unsigned n_rounds, n_stg_rows, n_obs_rows, pad;
 };
+
+// -DACINO_BOUNDS: every index the Schur kernels form into the sorted layout is checked against the layout's limits and a
+// violation stops the kernel with a message (compute-sanitizer is closed on the build pool; the GPU suite is run against
+// this build instead: profiles/r02_bounds_build.txt). Compiled out otherwise.
+#ifdef ACINO_BOUNDS
+#define SCHUR_CHECK(cond, code)                                                                                  \
+  do {                                                                                                           \
+    if (!(cond)) {                                                                                               \
+      printf("[acino] bounds check %d failed: %s (block %d thread %d)\n", code, #cond, (int)blockIdx.x, (int)threadIdx.x); \
+      __trap();                                                                                                  \
+    }                                                                                                            \
+  } while (0)
+#else
+#define SCHUR_CHECK(cond, code) do { } while (0)
+#endif
 
 // ---- symmetric 3x3: V + lam*D -> inverse (via LDL^T), D = floored diag(V) --------------------------------
 struct Sym3Inv { double i00, i01, i02, i11, i12, i22, D0, D1, D2; };
@@ -454,8 +473,11 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
     double2* __restrict__ blk = stg + ((size_t)s_blk0[m] + (size_t)rr * schur_rows(k)) * SCHUR_ROW + lane;
     const double2* __restrict__ ob = uvs + ((size_t)s_uv0[m] + (size_t)rr * k) * SCHUR_ROW + lane;
     const size_t gs = (size_t)r * 32 + lane;
+    SCHUR_CHECK(m > 0 && r < prm.n_rounds && (size_t)s_blk0[m] + (size_t)(rr + 1) * schur_rows(k) <= prm.n_stg_rows &&
+                (size_t)s_uv0[m] + (size_t)(rr + 1) * k <= prm.n_obs_rows, 41);
     const unsigned p = pid[gs];
     const bool valid = p != 0xFFFFFFFFu;
+    SCHUR_CHECK(!valid || (long long)p < prm.n_points, 42);
     double X = 0.0, Y = 0.0, Z = 0.0;
     if (valid) { X = Xp[3 * (size_t)p]; Y = Xp[3 * (size_t)p + 1]; Z = Xp[3 * (size_t)p + 2]; }
     schur_linearise_one<REFINE>(sc, m, k, ob, blk, p, valid, X, Y, Z, Xp, lamS + gs, lam, refine, need_cost, prm, A);
@@ -716,6 +738,7 @@ schur_accum_kernel(const SchurTile* __restrict__ tiles, const unsigned* __restri
     }
     const unsigned m = tc.mask;
     const int k = __popc(m), rows = schur_rows(k), R = tc.rounds;
+    SCHUR_CHECK(m > 0 && R > 0 && R * rows <= SCHUR_BUF_ROWS && (size_t)tc.row0 + (size_t)R * rows <= prm.n_stg_rows, 43);
     const unsigned key = (m << 16) | (unsigned)R;
     if (key != sched_key) {
       // decode the warp's piece of a (class, rounds) tile once; consecutive tiles of a class reuse it
@@ -758,6 +781,8 @@ schur_accum_kernel(const SchurTile* __restrict__ tiles, const unsigned* __restri
         cur_unit = gu;
       }
       const int ra = sg.ra_rb & 0xFFFF, rb = sg.ra_rb >> 16;
+      SCHUR_CHECK(gu < rcs_units(C) && ra >= 0 && ra < rb && rb <= R && sg.offN + 3 * SCHUR_ROW <= rows * SCHUR_ROW &&
+                  sg.offX + SCHUR_ROW <= rows * SCHUR_ROW, 44);
       if (sg.gu_diag >> 8) schur_accum_diag(acc, tb + lane, rows, sg.offN, sg.offX, 4 * k * SCHUR_ROW, ra, rb);
       else schur_accum_off(acc, tb + lane, rows, sg.offN, sg.offX, 4 * k * SCHUR_ROW, ra, rb);
     }
@@ -1030,6 +1055,8 @@ schur_backsub_kernel(const SchurClasses* __restrict__ cls, const unsigned* __res
     const double2* __restrict__ blk = stg + ((size_t)s_blk0[m] + (size_t)rr * schur_rows(k)) * SCHUR_ROW + lane;
     const double2* __restrict__ ob = uvs + ((size_t)s_uv0[m] + (size_t)rr * k) * SCHUR_ROW + lane;
     const unsigned p = pid[(size_t)r * 32 + lane];
+    SCHUR_CHECK(m > 0 && r < prm.n_rounds && (size_t)s_blk0[m] + (size_t)(rr + 1) * schur_rows(k) <= prm.n_stg_rows &&
+                (size_t)s_uv0[m] + (size_t)(rr + 1) * k <= prm.n_obs_rows && (p == 0xFFFFFFFFu || (long long)p < prm.n_points), 45);
     const double2* __restrict__ pt = blk + (size_t)(4 * k) * SCHUR_ROW;
     const double2 P0 = pt[0], P1 = pt[SCHUR_ROW];
     const double X = P0.x, Y = P0.y, Z = P1.x;

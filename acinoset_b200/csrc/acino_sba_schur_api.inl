@@ -223,8 +223,13 @@ static void schur_free(SchurState& s) {
   s = SchurState();
 }
 
-static SchurParams make_schur_params(const acino_sba_opts* o) {
+static SchurParams make_schur_params(const acino_sba* h, const acino_sba_opts* o) {
   SchurParams p;
+  memset(&p, 0, sizeof(p));          // (compared bytewise with the captured iteration's parameters)
+  p.n_points = h->P;
+  p.n_rounds = (unsigned)h->schur.n_rounds;
+  p.n_stg_rows = (unsigned)h->schur.n_stg_rows;
+  p.n_obs_rows = (unsigned)h->schur.n_obs_rows;
   p.inv_c2 = 1.0 / (o->f_scale * o->f_scale);
   p.half_c2 = 0.5 * o->f_scale * o->f_scale;
   p.gtol = o->gtol;
@@ -528,7 +533,7 @@ static int schur_iterate(acino_sba* h, const acino_sba_opts* o) {
   int rc = schur_ensure(h);
   if (rc) return rc;
   if (!h->schur.inited) { rc = schur_init_lm(h, o); if (rc) return rc; }
-  return schur_launch_iteration(h, make_schur_params(o));
+  return schur_launch_iteration(h, make_schur_params(h, o));
 }
 
 // the points solved to convergence with the cameras fixed (K3 on the current buffers until no point is active);
@@ -593,7 +598,7 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
   double F_prev = 0.0;
   s.history.assign(6, 0.0);      // row 0: the starting point, filled in after the first linearisation
   int n_sync = 2;          // the read-back of the class sizes and the end of the set-up
-  SchurParams prm = make_schur_params(o);
+  SchurParams prm = make_schur_params(h, o);
   int it = 0;
   // Polishing (polish_tol): the joint steps settle the cameras within a few tens of iterations, after which the cost
   // only creeps down because 10^6 points each finish their own small robust problem two refinement steps at a time.

@@ -423,10 +423,20 @@ def strong_arm(args, ctx):
     from acinoset_b200 import _capi, dense
     rank, world, C, mode, m = ctx['rank'], ctx['world'], ctx['C'], ctx['mode'], ctx['m']
     F = args.strong_frames
-    sc = ctx['sc'] if (rank == 0 and F == args.frames) else make_shard(F, seed=4)
-    a, b = dense.frame_shard(F, rank, world)
-    uv = np.ascontiguousarray(sc['uv'].reshape(F, N_KPTS, C, 2)[a:b].reshape(-1, C, 2))
-    lik = np.ascontiguousarray(sc['lik'].reshape(F, N_KPTS, C)[a:b].reshape(-1, C))
+    if F >= 500000 and F % 8 == 0 and world in (1, 2, 4, 8):
+        # a large scene (config C5) is defined as eight chunks of F/8 frames with seeds 500..507, so that a rank generates
+        # only its own frames (the scene is the same at every GPU count)
+        per = 8 // world
+        parts = [make_shard(F // 8, seed=500 + c) for c in range(rank * per, (rank + 1) * per)]
+        uv = np.concatenate([p_['uv'] for p_ in parts]); lik = np.concatenate([p_['lik'] for p_ in parts])
+        sc = parts[0]
+        a, b = rank * per * (F // 8), (rank + 1) * per * (F // 8)
+        del parts
+    else:
+        sc = ctx['sc'] if (rank == 0 and F == args.frames) else make_shard(F, seed=4)
+        a, b = dense.frame_shard(F, rank, world)
+        uv = np.ascontiguousarray(sc['uv'].reshape(F, N_KPTS, C, 2)[a:b].reshape(-1, C, 2))
+        lik = np.ascontiguousarray(sc['lik'].reshape(F, N_KPTS, C)[a:b].reshape(-1, C))
     k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
     Ps = uv.shape[0]
     L = _capi.lib()
@@ -638,7 +648,7 @@ def main():
                     fp64_peak_tflops_measured=ctx['fp64_peak'])
     if mode == 'extrinsics':
         k6 = ctx['kern']
-        roofline['kernel'] = f'schur_linearise_kernel<{C}> + schur_accum_kernel<{C}> (the Schur build, K4a + K4b; K4b dominates)'
+        roofline['kernel'] = f'schur_linearise_kernel<{C}, false> + schur_accum_kernel<{C}> (the Schur build, K4a + K4b; K4b dominates)'
         roofline['note'] = ('the Schur build is bound by the fp64 pipe, not by HBM: `achieved` / `frac` are the ALGORITHMIC bytes of the '
                             'build (mask + point + observations) over K4a + K4b; see `fp64` for the binding roof and `kernels` '
                             'for each kernel against its own traffic')
@@ -647,7 +657,7 @@ def main():
                                          f"on the solver's stream, kernel-by-kernel launches: {k6['ms_per_step_profiled']:.4f} ms per step; the timed "
                                          f"region replays the iteration as a CUDA graph: {ctx['ms_per_step']:.4f} ms per step)")
         kernels = {
-            f'schur_linearise_kernel<{C}>': dict(kernel_ms=k6['linearise_ms']),
+            f'schur_linearise_kernel<{C}, false>': dict(kernel_ms=k6['linearise_ms']),
             f'schur_accum_kernel<{C}>': dict(kernel_ms=k6['accumulate_ms']),
             f'schur_backsub_kernel<{C}>': dict(kernel_ms=k6['backsub_ms'], algorithmic_bytes_per_launch=int(k6['backsub_bytes']),
                                                achieved=k6['backsub_bytes'] / (k6['backsub_ms'] * 1e-3) / 1e9,

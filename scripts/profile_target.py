@@ -1,5 +1,5 @@
-"""Small fixed workload for ncu: C4-sized scene (119,490 frames), TRI x2, 8 Schur LM iterations, 2 points-only LM
-iterations. Usage: python scripts/profile_target.py [frames]"""
+"""Small fixed workload for ncu: C4-sized scene (119,490 frames), TRI x2, K1 once, 8 Schur LM iterations (embedded
+refinement on from the second one), 2 points-only LM iterations. Usage: python scripts/profile_target.py [frames]"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ctypes as ct
@@ -25,7 +25,11 @@ s.set_cameras(k, d, r, t); s.set_rvec_t(rv, tv)
 s.set_observations_dev(uv_d, mask_d)
 s.set_points(np.nan_to_num(xyz_d.download()))
 o = dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, force_iters=1)
-for _ in range(8):      # the first five steps are rejected while the damping grows; 6-8 are accepted (point refinement runs)
+f = s.residuals()       # K1 (residuals_dense_kernel) once
+o_fixed = dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, force_iters=1, point_refine_iters=0)
+for _ in range(4):      # the bench's fixed-work step: plain linearisation (schur_linearise_kernel<C, false>)
+    s.iterate(o_fixed)
+for _ in range(4):      # a solve's step: embedded refinement on (schur_linearise_kernel<C, true>)
     s.iterate(o)
 print('schur', s.lm_state())
 s.reset_state()

@@ -8,7 +8,13 @@ import numpy as np
 import torch
 from acinoset_b200 import synth, dense, _capi
 
+rank, world, local = (int(os.environ.get(k_, d_)) for k_, d_ in (('RANK', '0'), ('WORLD_SIZE', '1'), ('LOCAL_RANK', '0')))
+torch.cuda.set_device(local)
 L = _capi.lib()
+_capi.check(L.acino_set_device(local))
+if world > 1:
+    import torch.distributed as dist
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
 K, C = 20, 6
 sizes = [int(float(a)) for a in sys.argv[1:]] or [1000, 10000, 100000, 1000000, 10000000]
 block_frames = 100000
@@ -20,7 +26,10 @@ try:
     peak = json.load(open(os.path.join(os.path.dirname(__file__), '..', 'MEASURED_PEAKS.json')))['hbm_gbs']
 except Exception:
     pass
-for F in sizes:
+for F_total in sizes:
+    F = F_total // world             # frames shard across the ranks, no communication
+    if F == 0:
+        continue
     P = F * K
     reps = -(-F // block_frames)
     uv = uv_b.repeat(reps, 1, 1)[:P].contiguous() if reps > 1 else uv_b[:P].contiguous()
@@ -36,14 +45,24 @@ for F in sizes:
         run()
     n = max(3, min(50, int(2e8 / P)))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
     torch.cuda.synchronize(); e0.record()
     for _ in range(n):
         run()
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / n
+    if world > 1:
+        tt = torch.tensor([ms], device='cuda', dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    P = P * world                    # whole-job figures: all ranks' points over the slowest rank's time
     byts = P * 169
-    print(json.dumps(dict(config='C3 TRI sweep', frames=F, points=P, existing=int(ex.sum().item()), ms=ms, points_per_s=P / ms * 1e3,
-                          algorithmic_gbs=byts / ms / 1e6, frac_hbm=byts / ms / 1e6 / peak, launches_timed=n,
-                          note='acino_triangulate_ring_dev incl. its stream synchronisation; inputs resident in HBM')), flush=True)
+    if rank == 0:
+      print(json.dumps(dict(config='C3 TRI sweep', n_gpus=world, frames=F * world, points=P, existing=int(ex.sum().item()), ms=ms, points_per_s=P / ms * 1e3,
+                          algorithmic_gbs=byts / ms / 1e6, frac_hbm=byts / ms / 1e6 / (peak * world), launches_timed=n,
+                          note='acino_triangulate_ring_dev incl. its stream synchronisation; inputs resident in HBM; max over ranks')), flush=True)
     del uv, lik, xyz, mask, ex
     torch.cuda.empty_cache()
+if world > 1:
+    dist.destroy_process_group()
