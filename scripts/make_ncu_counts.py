@@ -44,21 +44,31 @@ for r in rows[2:]:
     a['regs'].append(num(r[col['launch__registers_per_thread']]))
 out = dict(workload=dict(frames=frames, masked_frac=mf, outlier_frac=of), kernel_source_sha=bench.kernel_source_sha(),
            capture=os.path.basename(rep), how='ncu --set full --clock-control none, scripts/profile_target.py; means over the captured launches', kernels={})
+def norm(n):
+    n = n.split('(')[0].replace('void ', '').replace('acino::', '') if '<' not in n else n[:n.index('>') + 1].replace('void ', '').replace('acino::', '')
+    return n.replace('(int)', '').replace('(bool)', '').replace(', 1>', ', true>').replace(', 0>', ', false>')
+
+
+# executed thread-level instructions per kernel NAME (the SASS page lists every captured launch under its full name)
+src = list(csv.reader(io.StringIO(ncu('--page', 'source', '--csv', '--print-source', 'sass'))))
+flops, n_launch = collections.defaultdict(collections.Counter), collections.Counter()
+h, cur = None, None
+for r in src:
+    if len(r) >= 2 and r[0] == 'Kernel Name':
+        cur = norm(r[1]); n_launch[cur] += 1; continue
+    if len(r) > 4 and r[0] == 'Address':
+        h = r; continue
+    if h is None or cur is None or len(r) < 10:
+        continue
+    try:
+        ti = int(r[h.index('Predicated-On Thread Instructions Executed')])
+    except ValueError:
+        continue
+    t = r[1].split()
+    if t:
+        flops[cur][(t[0] if not t[0].startswith('@') else t[1]).split('.')[0]] += ti
 for name, a in agg.items():
-    src = list(csv.reader(io.StringIO(ncu('--page', 'source', '--csv', '--print-source', 'sass', '--kernel-name', 'regex:' + name.split('<')[0]))))
-    h, ops, n_k = None, collections.Counter(), 0
-    for r in src:
-        if len(r) > 4 and r[0] == 'Address':
-            h = r; n_k += 1; continue
-        if h is None or len(r) < 10:
-            continue
-        try:
-            ti = int(r[h.index('Predicated-On Thread Instructions Executed')])
-        except ValueError:
-            continue
-        t = r[1].split()
-        if t:
-            ops[(t[0] if not t[0].startswith('@') else t[1]).split('.')[0]] += ti
+    ops, n_k = flops.get(name, collections.Counter()), n_launch.get(name, 0)
     fl = (2 * ops['DFMA'] + ops['DMUL'] + ops['DADD']) / max(n_k, 1)
     mean = lambda v: sum(v) / len(v)
     out['kernels'][name] = dict(launches=len(a['ms']), ms_under_ncu=mean(a['ms']), dram_bytes=int(mean(a['dram'])), fp64_flops=int(fl),
