@@ -259,6 +259,17 @@ __device__ __forceinline__ int schur_class_of_round(const unsigned* s_round0, in
   return lo;
 }
 
+// Request a contiguous run of rows into L2 ahead of its use (cp.async.bulk.prefetch.L2: one instruction of one lane
+// covers a whole block of rows, no registers or shared memory are tied up while the request is in flight). K4a and K6
+// walk the rounds with a grid stride: while a warp works on round r, the rows of its next round are already on their
+// way, so its loads there find them in L2 instead of waiting for HBM one dependent access after the other.
+#ifndef SCHUR_L2_PREFETCH
+#define SCHUR_L2_PREFETCH 2      // bit 0: K6 (measured slower: 0.182 vs 0.159 ms), bit 1: K4a (0.172 -> 0.168 ms)
+#endif
+__device__ __forceinline__ void l2_prefetch_rows(const void* p, unsigned bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 // the observations in the sorted layout: row j of a round = (u, v) of the class's j-th camera, zeros in padding lanes
 template <int C>
 __global__ void __launch_bounds__(256)
@@ -280,6 +291,40 @@ cls_fill_obs_kernel(const SchurClasses* __restrict__ cls, const unsigned* __rest
       const int c = __ffs(mm) - 1;
       dst[j * SCHUR_ROW] = (p != 0xFFFFFFFFu) ? uv[(size_t)p * C + c] : make_double2(0.0, 0.0);
     }
+  }
+}
+
+// The points of the solve live in the sorted numbering while the LM iterates: two buffers [round][X | Y | Z][lane] of
+// doubles, so that K4a reads and K6 writes them as coalesced rows (in the scene order a warp's 32 points lie ~60 slot
+// groups apart: 24-byte gathers and partial-sector scatters, 2 - 4 x the bytes). The scene-order arrays are brought up
+// to date only when something outside the iteration wants them (polishing, the read-back, the end of a solve).
+// The pair in use is the LM state's current one.
+__global__ void __launch_bounds__(256)
+schur_points_to_sorted_kernel(const unsigned* __restrict__ pid, size_t n_sorted, const double* __restrict__ X0,
+                              const double* __restrict__ X1, double* __restrict__ Xs0, double* __restrict__ Xs1,
+                              const SchurLm* __restrict__ lm) {
+  const int cur = lm->cur;
+  const double* __restrict__ X = cur ? X1 : X0;
+  double* __restrict__ Xs = cur ? Xs1 : Xs0;
+  for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < n_sorted; g += (size_t)gridDim.x * 256) {
+    const unsigned p = pid[g];
+    double x = 0.0, y = 0.0, z = 0.0;
+    if (p != 0xFFFFFFFFu) { x = X[3 * (size_t)p]; y = X[3 * (size_t)p + 1]; z = X[3 * (size_t)p + 2]; }
+    double* d = Xs + (g >> 5) * (3 * SCHUR_ROW) + (g & 31);
+    d[0] = x; d[SCHUR_ROW] = y; d[2 * SCHUR_ROW] = z;
+  }
+}
+__global__ void __launch_bounds__(256)
+schur_points_to_scene_kernel(const unsigned* __restrict__ pid, size_t n_sorted, double* __restrict__ X0, double* __restrict__ X1,
+                             const double* __restrict__ Xs0, const double* __restrict__ Xs1, const SchurLm* __restrict__ lm) {
+  const int cur = lm->cur;
+  double* __restrict__ X = cur ? X1 : X0;
+  const double* __restrict__ Xs = cur ? Xs1 : Xs0;
+  for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < n_sorted; g += (size_t)gridDim.x * 256) {
+    const unsigned p = pid[g];
+    if (p == 0xFFFFFFFFu) continue;
+    const double* d = Xs + (g >> 5) * (3 * SCHUR_ROW) + (g & 31);
+    X[3 * (size_t)p] = d[0]; X[3 * (size_t)p + 1] = d[SCHUR_ROW]; X[3 * (size_t)p + 2] = d[2 * SCHUR_ROW];
   }
 }
 
@@ -347,8 +392,8 @@ struct LinAcc { double cost, gh, gmax, xmax, cprod; };
 // schur_linearise_kernel and schur_build_kernel.
 template <bool REFINE>
 __device__ __forceinline__ void schur_linearise_one(const double* __restrict__ sc, unsigned m, int k, const double2* __restrict__ ob,
-                                                    double2* __restrict__ blk, unsigned p, bool valid, double X, double Y, double Z,
-                                                    double* __restrict__ Xp, double* __restrict__ lam_slot, double lam, int refine,
+                                                    double2* __restrict__ blk, bool valid, double X, double Y, double Z,
+                                                    double* __restrict__ xs_slot, double* __restrict__ lam_slot, double lam, int refine,
                                                     bool need_cost, const SchurParams& prm, LinAcc& A) {
   PointLin L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, valid, prm.inv_c2, prm.hfloor);
   if (REFINE && refine > 0 && valid) {
@@ -392,7 +437,7 @@ __device__ __forceinline__ void schur_linearise_one(const double* __restrict__ s
     }
     lam_slot[0] = lp;
     if (moved) {
-      Xp[3 * (size_t)p] = X; Xp[3 * (size_t)p + 1] = Y; Xp[3 * (size_t)p + 2] = Z;
+      xs_slot[0] = X; xs_slot[SCHUR_ROW] = Y; xs_slot[2 * SCHUR_ROW] = Z;
       L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, true, prm.inv_c2, prm.hfloor);      // the rows at the refined point
     }
   }
@@ -478,9 +523,22 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
     const unsigned p = pid[gs];
     const bool valid = p != 0xFFFFFFFFu;
     SCHUR_CHECK(!valid || (long long)p < prm.n_points, 42);
-    double X = 0.0, Y = 0.0, Z = 0.0;
-    if (valid) { X = Xp[3 * (size_t)p]; Y = Xp[3 * (size_t)p + 1]; Z = Xp[3 * (size_t)p + 2]; }
-    schur_linearise_one<REFINE>(sc, m, k, ob, blk, p, valid, X, Y, Z, Xp, lamS + gs, lam, refine, need_cost, prm, A);
+    double* __restrict__ xs = Xp + (size_t)r * (3 * SCHUR_ROW) + lane;      // the round's points: rows X, Y, Z of 32 doubles
+    const double xl = xs[0], yl = xs[SCHUR_ROW], zl = xs[2 * SCHUR_ROW];
+    const double X = valid ? xl : 0.0, Y = valid ? yl : 0.0, Z = valid ? zl : 0.0;
+#if SCHUR_L2_PREFETCH & 2
+    {      // the next round of this warp: its observation rows, points and ids into L2
+      const unsigned rn = r + gridDim.x * NW;
+      if (rn < n_rounds && lane == 0) {
+        const int mn = schur_class_of_round(s_round0, NCLS, rn);
+        const int kn = __popc(mn);
+        l2_prefetch_rows(uvs + ((size_t)s_uv0[mn] + (size_t)(rn - s_round0[mn]) * kn) * SCHUR_ROW, (unsigned)(kn * SCHUR_ROW * sizeof(double2)));
+        l2_prefetch_rows(Xp + (size_t)rn * (3 * SCHUR_ROW), (unsigned)(3 * SCHUR_ROW * sizeof(double)));
+        l2_prefetch_rows(pid + (size_t)rn * 32, 128u);
+      }
+    }
+#endif
+    schur_linearise_one<REFINE>(sc, m, k, ob, blk, valid, X, Y, Z, xs, lamS + gs, lam, refine, need_cost, prm, A);
   }
   double cost_acc = A.cost + prm.half_c2 * log(A.cprod), gh_acc = A.gh, gmax_acc = A.gmax, xmax_acc = A.xmax;
 #pragma unroll
@@ -1059,6 +1117,23 @@ schur_backsub_kernel(const SchurClasses* __restrict__ cls, const unsigned* __res
                 (size_t)s_uv0[m] + (size_t)(rr + 1) * k <= prm.n_obs_rows && (p == 0xFFFFFFFFu || (long long)p < prm.n_points), 45);
     const double2* __restrict__ pt = blk + (size_t)(4 * k) * SCHUR_ROW;
     const double2 P0 = pt[0], P1 = pt[SCHUR_ROW];
+#if SCHUR_L2_PREFETCH & 1
+    {      // the rows of this warp's next round (Jacobian rows, point record, observations, point ids) into L2
+      const unsigned rn = r + gridDim.x * NW;
+      if (rn < n_rounds) {
+        const int mn = schur_class_of_round(s_round0, NCLS, rn);
+        const int kn = __popc(mn);
+        const unsigned rrn = rn - s_round0[mn];
+        if (lane == 0) {
+          const double2* b = stg + ((size_t)s_blk0[mn] + (size_t)rrn * schur_rows(kn)) * SCHUR_ROW;
+          l2_prefetch_rows(b, (unsigned)(3 * kn * SCHUR_ROW * sizeof(double2)));
+          l2_prefetch_rows(b + (size_t)(4 * kn) * SCHUR_ROW, (unsigned)(6 * SCHUR_ROW * sizeof(double2)));
+          l2_prefetch_rows(uvs + ((size_t)s_uv0[mn] + (size_t)rrn * kn) * SCHUR_ROW, (unsigned)(kn * SCHUR_ROW * sizeof(double2)));
+          l2_prefetch_rows(pid + (size_t)rn * 32, 128u);
+        }
+      }
+    }
+#endif
     const double X = P0.x, Y = P0.y, Z = P1.x;
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, v00 = 0.0, v11 = 0.0, v22 = 0.0;
     double2 ob_n = ob[0];                        // first observation of the trial evaluation: in flight during the sums
@@ -1096,11 +1171,15 @@ schur_backsub_kernel(const SchurClasses* __restrict__ cls, const unsigned* __res
     const double d1 = -(h1 + fma(i01, s0, fma(i11, s1, i12 * s2)));
     const double d2 = -(h2 + fma(i02, s0, fma(i12, s1, i22 * s2)));
     const double xt = X + d0, yt = Y + d1, zt = Z + d2;
+    {      // the trial points in the sorted numbering (padding lanes carry zeros: X = 0, dX = 0)
+      double* __restrict__ xs = Xt + (size_t)r * (3 * SCHUR_ROW) + lane;
+      xs[0] = xt; xs[SCHUR_ROW] = yt; xs[2 * SCHUR_ROW] = zt;
+    }
     if (p != 0xFFFFFFFFu) {
       // predicted reduction over all parameters: 0.5 (lam delta^T D delta - g^T delta) with the undamped gradient g;
       // for the point block -g^T dX = g^T h + h^T s, of which K4a has already summed g^T h (it reaches K7 through K5)
       pred_acc += 0.5 * (lam * (D0 * d0 * d0 + D1 * d1 * d1 + D2 * d2 * d2) + fma(h0, s0, fma(h1, s1, h2 * s2)));
-      Xt[3 * (size_t)p] = xt; Xt[3 * (size_t)p + 1] = yt; Xt[3 * (size_t)p + 2] = zt;
+
       dx_acc = fmax(dx_acc, fmax(fabs(d0), fmax(fabs(d1), fabs(d2))));
       int j = 0;
 #pragma unroll 1
@@ -1317,6 +1396,9 @@ struct SchurState {
   SchurClasses* cls = nullptr;             // device
   unsigned* pid = nullptr;                 // [32 n_rounds] scene index of the sorted point (0xFFFFFFFF: padding)
   double* lamS = nullptr;                  // [32 n_rounds] the points' own damping of the embedded refinement (sorted numbering)
+  double* Xs[2] = {nullptr, nullptr};      // [n_rounds][3][32] the points in the sorted numbering, current / trial (as h->X / X_alt)
+  size_t cap_xs[2] = {0, 0};
+  bool xs_newer = false;                   // the sorted buffers hold newer points than the scene-order arrays
   double2* uvs = nullptr;                  // observation rows
   double2* stg = nullptr;                  // staging rows written by K4a, read by K4b and K6
   SchurTile* tiles = nullptr;

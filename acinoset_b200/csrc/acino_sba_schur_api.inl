@@ -216,7 +216,7 @@ static void schur_free(SchurState& s) {
   cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.wpart); cudaFree(s.lin_partial); cudaFree(s.rcs);
   cudaFree(s.mx); cudaFree(s.delta_c); cudaFree(s.scal_partial); cudaFree(s.scal); cudaFree(s.lm);
   cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.hist); cudaFree(s.cls_starts); cudaFree(s.cls);
-  cudaFree(s.pid); cudaFree(s.lamS); cudaFree(s.uvs); cudaFree(s.stg); cudaFree(s.tiles); cudaFree(s.tile_range);
+  cudaFree(s.pid); cudaFree(s.lamS); cudaFree(s.Xs[0]); cudaFree(s.Xs[1]); cudaFree(s.uvs); cudaFree(s.stg); cudaFree(s.tiles); cudaFree(s.tile_range);
   if (s.h_lm) cudaFreeHost(s.h_lm);
   if (s.h_cls_starts) cudaFreeHost(s.h_cls_starts);
   for (cudaEvent_t e : s.prof_ev) if (e) cudaEventDestroy(e);
@@ -343,6 +343,8 @@ static int schur_build_layout(acino_sba* h) {
   if ((rc = schur_grow(s.pid, s.cap_pid, (size_t)rounds * 32 + 32))) return rc;
   if ((rc = schur_grow(s.lamS, s.cap_lam, (size_t)rounds * 32 + 32))) return rc;
   ACINO_CUDA(cudaMemsetAsync(s.lamS, 0, ((size_t)rounds * 32 + 32) * sizeof(double), h->stream));
+  for (int b = 0; b < 2; ++b)
+    if ((rc = schur_grow(s.Xs[b], s.cap_xs[b], (size_t)rounds * 3 * SCHUR_ROW + 3 * SCHUR_ROW))) return rc;
   if ((rc = schur_grow(s.uvs, s.cap_uvs, (size_t)orows * SCHUR_ROW + SCHUR_ROW))) return rc;
   if ((rc = schur_grow(s.stg, s.cap_stg, (size_t)rows * SCHUR_ROW + SCHUR_ROW))) return rc;
   if ((rc = schur_grow(s.tiles, s.cap_tiles, tiles.size() + 1))) return rc;
@@ -360,6 +362,30 @@ static int schur_build_layout(acino_sba* h) {
   return ACINO_OK;
 }
 
+// scene order -> sorted buffers (current pair), and back; see schur_points_to_sorted_kernel
+static int schur_points_to_sorted(acino_sba* h) {
+  SchurState& s = h->schur;
+  const size_t n = (size_t)s.n_rounds * 32;
+  if (n) {
+    schur_points_to_sorted_kernel<<<grid_for((int64_t)n, 256), 256, 0, h->stream>>>(s.pid, n, h->X, s.X_alt, s.Xs[0], s.Xs[1], s.lm);
+    ACINO_CUDA(cudaGetLastError());
+    ++s.launches;
+  }
+  s.xs_newer = false;
+  return ACINO_OK;
+}
+static int schur_points_to_scene(acino_sba* h) {
+  SchurState& s = h->schur;
+  const size_t n = (size_t)s.n_rounds * 32;
+  if (n && s.xs_newer) {
+    schur_points_to_scene_kernel<<<grid_for((int64_t)n, 256), 256, 0, h->stream>>>(s.pid, n, h->X, s.X_alt, s.Xs[0], s.Xs[1], s.lm);
+    ACINO_CUDA(cudaGetLastError());
+    ++s.launches;
+  }
+  s.xs_newer = false;
+  return ACINO_OK;
+}
+
 static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
   SchurState& s = h->schur;
   schur_drop_graph(s);          // grids and buffers of the captured launches belong to the previous layout
@@ -372,6 +398,8 @@ static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
   // the sorted layout follows from the masks alone: (re)built once per solve (the observation mask may be a borrowed
   // device buffer that changed since the last solve; it must not change during one)
   int rc = schur_build_layout(h);
+  if (rc) return rc;
+  rc = schur_points_to_sorted(h);
   if (rc) return rc;
   if (h->P > 0) {
     rc = ensure_point_order(h, true);      // K3 (refinement, polishing) visits the points by observation count
@@ -390,12 +418,13 @@ static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumul
   cudaStream_t st = h->stream;
   cudaEvent_t* ev = s.prof_ev + SchurState::PROF_EV * s.prof_n;
   if (prof) ACINO_CUDA(cudaEventRecord(ev[0], st));
+  s.xs_newer = true;      // refinement here, the accepted trial of K6 later: the points move in the sorted buffers only
   if (prm.refine > 0) {
     DISPATCH_C(C, (schur_linearise_kernel<CC, true><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
-                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.stg, s.lin_partial, s.lamS)));
+                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, s.Xs[0], s.Xs[1], s.lm, prm, s.stg, s.lin_partial, s.lamS)));
   } else {
     DISPATCH_C(C, (schur_linearise_kernel<CC, false><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
-                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.stg, s.lin_partial, s.lamS)));
+                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, s.Xs[0], s.Xs[1], s.lm, prm, s.stg, s.lin_partial, s.lamS)));
   }
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(ev[1], st));
@@ -448,7 +477,7 @@ static int schur_enqueue_iteration(acino_sba* h, const SchurParams& prm, bool pr
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(ev[3], st));
   DISPATCH_C(C, (schur_backsub_kernel<CC><<<s.grid_back, SCHUR_BACKSUB_TB, 0, st>>>(
-                    s.cls, s.pid, h->cams, s.cams_alt, h->X, s.X_alt, s.lm, prm, s.delta_c, s.scal_partial, s.stg, s.uvs)));
+                    s.cls, s.pid, h->cams, s.cams_alt, s.Xs[0], s.Xs[1], s.lm, prm, s.delta_c, s.scal_partial, s.stg, s.uvs)));
   ACINO_CUDA(cudaGetLastError());
   if (prof) { ACINO_CUDA(cudaEventRecord(ev[4], st)); ++s.prof_n; }
   ++s.launches;
@@ -501,6 +530,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
     s.iter_launches = s.launches - l0;
     s.launches = l0;
   }
+  s.xs_newer = true;
   ACINO_CUDA(cudaGraphLaunch(s.iter_exec, h->stream));
   s.launches += s.iter_launches;
   ++s.graph_replays;
@@ -512,6 +542,7 @@ static int schur_launch_iteration(acino_sba* h, const SchurParams& prm) {
 static int schur_sync_current(acino_sba* h) {
   SchurState& s = h->schur;
   if (!s.ready || !s.inited) return ACINO_OK;
+  { const int rc = schur_points_to_scene(h); if (rc) return rc; }
   ACINO_CUDA(cudaMemcpyAsync(s.h_lm, s.lm, sizeof(SchurLm), cudaMemcpyDeviceToHost, h->stream));
   ACINO_CUDA(cudaStreamSynchronize(h->stream));
   if (s.h_lm->cur == 1) {
@@ -543,6 +574,7 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
   const bool alt = s.h_lm->cur != 0;
   const double* cams = alt ? s.cams_alt : h->cams;
   double* X = alt ? s.X_alt : h->X;
+  { const int rc = schur_points_to_scene(h); if (rc) return rc; }      // K3 works on the scene-order arrays
   LmParams lp;
   lp.inv_c2 = prm.inv_c2; lp.half_c2 = prm.half_c2; lp.gtol = 1e-9; lp.xtol = 1e-13; lp.lambda0 = 1e-4;
   lp.inner_iters = 8; lp.force = 0; lp.ignore_status = 1;
@@ -580,7 +612,7 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
     prev_act = h->h_counters[0];
     lp.ignore_status = 0;
   }
-  return ACINO_OK;
+  return schur_points_to_sorted(h);      // the polished points, for the iterations that follow
 }
 
 static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* st) {
