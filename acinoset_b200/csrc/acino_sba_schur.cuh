@@ -485,8 +485,11 @@ __device__ __forceinline__ void schur_linearise_one(const double* __restrict__ s
 #ifndef SCHUR_LIN_MINB
 #define SCHUR_LIN_MINB 4       // 5 CTAs (96 registers, spills) measured slower: 0.179 vs 0.172 ms
 #endif
+#ifndef SCHUR_LIN_MINB_REFINE
+#define SCHUR_LIN_MINB_REFINE 4
+#endif
 template <int C, bool REFINE>
-__global__ void __launch_bounds__(SCHUR_LIN_TB, SCHUR_LIN_MINB)
+__global__ void __launch_bounds__(SCHUR_LIN_TB, REFINE ? SCHUR_LIN_MINB_REFINE : SCHUR_LIN_MINB)
 schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __restrict__ pid,
                        const double2* __restrict__ uvs, const double* __restrict__ cams0, const double* __restrict__ cams1,
                        double* __restrict__ X0, double* __restrict__ X1, const SchurLm* __restrict__ lm,
@@ -705,22 +708,21 @@ __device__ __forceinline__ void schur_accum_off(double (&acc)[RCS_UNIT], const d
     const double q1x = fma(n1x, i00, fma(n1y, i01, n1z * i02));
     const double q1y = fma(n1x, i01, fma(n1y, i11, n1z * i12));
     const double q1z = fma(n1x, i02, fma(n1y, i12, n1z * i22));
-    double b0[6], b1[6];
-    b0[0] = fma(Y, p0z, -Z * p0y); b0[1] = fma(Z, p0x, -X * p0z); b0[2] = fma(X, p0y, -Y * p0x);
-    b0[3] = p0x; b0[4] = p0y; b0[5] = p0z;
-    b1[0] = fma(Y, p1z, -Z * p1y); b1[1] = fma(Z, p1x, -X * p1z); b1[2] = fma(X, p1y, -Y * p1x);
-    b1[3] = p1x; b1[4] = p1y; b1[5] = p1z;
     const double m00 = -fma(q0x, p0x, fma(q0y, p0y, q0z * p0z));
     const double m01 = -fma(q0x, p1x, fma(q0y, p1y, q0z * p1z));
     const double m10 = -fma(q1x, p0x, fma(q1y, p0y, q1z * p0z));
     const double m11 = -fma(q1x, p1x, fma(q1y, p1y, q1z * p1z));
+    // T = m B with B = N' [X x . | I]: the 2x3 product m N' first, its cross products with X second (the cross
+    // products of the rows of N' themselves are never formed)
+    double t0[6], t1[6];
+    t0[3] = fma(m00, p0x, m01 * p1x); t0[4] = fma(m00, p0y, m01 * p1y); t0[5] = fma(m00, p0z, m01 * p1z);
+    t1[3] = fma(m10, p0x, m11 * p1x); t1[4] = fma(m10, p0y, m11 * p1y); t1[5] = fma(m10, p0z, m11 * p1z);
+    t0[0] = fma(Y, t0[5], -Z * t0[4]); t0[1] = fma(Z, t0[3], -X * t0[5]); t0[2] = fma(X, t0[4], -Y * t0[3]);
+    t1[0] = fma(Y, t1[5], -Z * t1[4]); t1[1] = fma(Z, t1[3], -X * t1[5]); t1[2] = fma(X, t1[4], -Y * t1[3]);
 #pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      const double t0 = fma(m00, b0[j], m01 * b1[j]);
-      const double t1 = fma(m10, b0[j], m11 * b1[j]);
+    for (int j = 0; j < 6; ++j)
 #pragma unroll
-      for (int i = 0; i < 6; ++i) acc[i * 6 + j] = fma(a0[i], t0, fma(a1[i], t1, acc[i * 6 + j]));
-    }
+      for (int i = 0; i < 6; ++i) acc[i * 6 + j] = fma(a0[i], t0[j], fma(a1[i], t1[j], acc[i * 6 + j]));
   }
 }
 
@@ -965,6 +967,9 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
   const double lam = lm->lambda;
   if (tid < n) A[tid][tid] = fma(lam, D[tid], A[tid][tid]);
   __syncthreads();
+  // (Measured and dropped: the factorisation by ONE warp with the matrix in registers, fully unrolled so that every
+  // register index is static: no barriers, but 255 registers + spills at n = 36 and ~10^4 straight-line instructions
+  // fetched once: 45 us against 22.)
   // Cholesky (lower) of the matrix bordered by the right-hand side: one element per thread, in a register. Row n holds
   // b = -rhs, and the updates that turn the rows above into L turn it into y = L^-1 b, so the forward substitution
   // comes with the factorisation. Per column: the diagonal's owner takes one reciprocal square root (MUFU + Newton, no

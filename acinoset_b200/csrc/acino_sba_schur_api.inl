@@ -419,8 +419,10 @@ static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumul
   cudaEvent_t* ev = s.prof_ev + SchurState::PROF_EV * s.prof_n;
   if (prof) ACINO_CUDA(cudaEventRecord(ev[0], st));
   s.xs_newer = true;      // refinement here, the accepted trial of K6 later: the points move in the sorted buffers only
+  // the refining instantiation holds SCHUR_LIN_MINB_REFINE CTAs per SM: its grid is cut to whole waves
+  const int grid_lin = prm.refine > 0 ? std::min(s.grid_lin, SCHUR_LIN_MINB_REFINE * s.sms) : s.grid_lin;
   if (prm.refine > 0) {
-    DISPATCH_C(C, (schur_linearise_kernel<CC, true><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
+    DISPATCH_C(C, (schur_linearise_kernel<CC, true><<<grid_lin, SCHUR_LIN_TB, 0, st>>>(
                       s.cls, s.pid, s.uvs, h->cams, s.cams_alt, s.Xs[0], s.Xs[1], s.lm, prm, s.stg, s.lin_partial, s.lamS)));
   } else {
     DISPATCH_C(C, (schur_linearise_kernel<CC, false><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
@@ -439,7 +441,7 @@ static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumul
   // the per-CTA partial systems and K4a's sums, folded in a fixed order by len/32 CTAs (a fold by the last CTA of K4b
   // was measured: one CTA chasing 148 partials per entry costs 33 us, this launch 8)
   fold_partials_kernel<<<(len + 31) / 32, 256, 0, st>>>(s.rcs_partial, accumulate ? s.grid_build : 0, len, s.rcs, nullptr, 0, 0, 0, 0,
-                                                        s.mx, s.lin_partial, s.grid_lin, rcs_units(C) * RCS_UNIT);
+                                                        s.mx, s.lin_partial, grid_lin, rcs_units(C) * RCS_UNIT);
   ACINO_CUDA(cudaGetLastError());
   ++s.launches;
   return ACINO_OK;
