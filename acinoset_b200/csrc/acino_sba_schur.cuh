@@ -33,15 +33,17 @@ struct SchurLm {
   double pred_cam;
   double last_rel_dec;   // relative cost decrease of the latest accepted step
   int cur;           // which of the two parameter buffers is current
-  int status;        // 0 running, 1 gtol, 2 ftol, 3 xtol, 4 stalled (damping exhausted), 6 step failed (kept running)
+  int status;        // 0 running, 1 gtol, 2 ftol, 3 xtol, 4 stalled (damping exhausted), 5 paused: the accepted steps only creep,
+                     // the host polishes the points and resumes (acino_sba_solve), 7 peer exchange timed out
   int iter, n_accept, n_reject, chol_fail, skip;
   int last_accept;   // 1 when the latest decision accepted the step
   int need_cost;     // 1: the next linearisation must re-evaluate the cost (points were refined after the accepted step)
-  int pad;
+  int last_polish;   // iteration (0-based) after which the host last polished the points; -1000: never
 };
 
 struct SchurParams {
   double inv_c2, half_c2, gtol, ftol, xtol, hfloor, refine_skip;
+  double polish_tol;      // > 0: K7 pauses the solve (status 5) when an accepted step gains less than this (acino_sba_solve only)
   int force, refine;
   // limits of the current layout, for the bounds-checked build (-DACINO_BOUNDS): slot groups, rounds, staging rows,
   // observation rows
@@ -856,9 +858,11 @@ schur_accum_kernel(const SchurTile* __restrict__ tiles, const unsigned* __restri
     double s = 0.0;
     if (e < NU * RCS_UNIT) {
       const int u = e / RCS_UNIT;
-#pragma unroll 1
-      for (int w = 0; w < NW; ++w)
-        if (s_touched[w] >> u & 1ull) s += __ldcg(cpart + (size_t)w * LEN + e);
+      double v[NW];      // all loads requested before the first is used (one L2 round trip instead of NW)
+#pragma unroll
+      for (int w = 0; w < NW; ++w) v[w] = (s_touched[w] >> u & 1ull) ? __ldcg(cpart + (size_t)w * LEN + e) : 0.0;
+#pragma unroll
+      for (int w = 0; w < NW; ++w) s += v[w];
     }
     rcs_partial[(size_t)blockIdx.x * LEN + e] = s;
   }
@@ -1111,6 +1115,9 @@ schur_backsub_kernel(const SchurClasses* __restrict__ cls, const unsigned* __res
   double f_acc = 0.0, pred_acc = 0.0, dx_acc = 0.0;
   double prod = 1.0;
   const unsigned n_rounds = skip ? 0u : s_round0[NCLS];
+  // (Measured and dropped: visiting the rounds in the order of K4b's per-CTA ranges, every range from its end backwards,
+  // so that the ~100 MB K4b read last are found in L2: 148 descending streams cost more DRAM efficiency than the hits
+  // save, 0.131 ms against 0.116.)
   for (unsigned r = blockIdx.x * NW + warp; r < n_rounds; r += gridDim.x * NW) {
     const int m = schur_class_of_round(s_round0, NCLS, r);
     const int k = __popc(m);
@@ -1279,6 +1286,9 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
     if (!prm.force) {
       if (act <= prm.ftol * F && rho > 0.25) lm->status = 2;      // scipy trf check_termination: dF < ftol*F and ratio > 0.25
       else if (c <= prm.xtol * (lm->xmax + prm.xtol)) lm->status = 3;
+      // the accepted steps only creep: pause (the iterations the host has already queued behind this one skip) until
+      // the host has polished the points. Decided here so that the host can read the LM state one iteration late.
+      else if (prm.polish_tol > 0.0 && act / F < prm.polish_tol && (lm->iter - 1) - lm->last_polish >= 4) lm->status = 5;
     }
   } else {
     lm->rho = 0.0;
@@ -1296,34 +1306,39 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
   }
 }
 
-// fold the per-CTA partials (fixed order: deterministic): block = 8 warps x 32 entries; warp w sums the partials
-// b = w, w+8, ... of its 32 entries with two chains in flight, warp 0 combines the eight sums. One pass over
+// fold the per-CTA partials (fixed order: deterministic): block = 32 warps x 32 entries; warp w sums the partials
+// b = w, w+32, ... of its 32 entries, warp 0 combines the 32 sums. One pass over
 // [n_partial][len] with len/32 CTAs instead of one CTA chasing n_partial dependent loads per entry. Block 0 also
 // folds the maxima rows (max_w columns at stride max_stride, offset max_off) and, when `lin` is given, K4a's per-CTA
 // rows [cost, sum g^T h, max |g|, max |X|]: the two sums go to out_sum[scal_off], out_sum[scal_off + 1] (the RCS
 // scalars), the two maxima to out_max[0..1].
-__global__ void __launch_bounds__(256)
+#define FOLD_TB 1024
+__global__ void __launch_bounds__(FOLD_TB)
 fold_partials_kernel(const double* __restrict__ partial, int n_partial, int len, double* __restrict__ out_sum,
                      const double* __restrict__ maxp, int n_max, int max_w, int max_stride, int max_off,
                      double* __restrict__ out_max, const double* __restrict__ lin, int n_lin, int scal_off) {
-  __shared__ double sm[8][33];
+  constexpr int NW = FOLD_TB / 32;
+  __shared__ double sm[NW][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int i = blockIdx.x * 32 + lane;
-  double s0 = 0.0, s1 = 0.0;
+  // warp w takes the partials b = w, w + 32, ...: at 148 partials at most five loads per thread, all requested before
+  // the first is used (8 warps with two chains waited for nine dependent L2 round trips: 7.8 us against 3)
+  double s = 0.0;
   if (i < len) {
-    int b = warp;
-    for (; b + 8 < n_partial; b += 16) {
-      s0 += partial[(size_t)b * len + i];
-      s1 += partial[(size_t)(b + 8) * len + i];
+    for (int b = warp; b < n_partial; b += 8 * NW) {
+      double v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = (b + q * NW < n_partial) ? partial[(size_t)(b + q * NW) * len + i] : 0.0;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) s += v[q];
     }
-    if (b < n_partial) s0 += partial[(size_t)b * len + i];
   }
-  sm[warp][lane] = s0 + s1;
+  sm[warp][lane] = s;
   __syncthreads();
   if (warp == 0 && i < len && !(lin && (i == scal_off || i == scal_off + 1))) {
     double t = 0.0;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) t += sm[w][lane];
+    for (int w = 0; w < NW; ++w) t += sm[w][lane];
     out_sum[i] = t;
   }
   if (blockIdx.x == 0 && warp == 1) {
@@ -1366,6 +1381,7 @@ __global__ void schur_init_kernel(SchurLm* lm, double lambda0) {
   memset(&z, 0, sizeof(z));
   z.lambda = lambda0;
   z.nu = 2.0;
+  z.last_polish = -1000;
   *lm = z;
 }
 
@@ -1392,6 +1408,9 @@ struct SchurState {
   double* scal = nullptr;
   SchurLm* lm = nullptr;
   SchurLm* h_lm = nullptr;
+  static constexpr int RING = 4;
+  SchurLm* h_ring = nullptr;               // pinned: the LM state after each of the last RING iterations (acino_sba_solve reads them one late)
+  cudaEvent_t ring_ev[RING] = {};
   static constexpr int POLISH_CAP = 1 << 18;
   unsigned* polish_list[2] = {nullptr, nullptr};   // still-active points of the previous / this polish launch
   // the sorted numbering (rebuilt by every solve from the masks)

@@ -196,6 +196,8 @@ static int schur_alloc(acino_sba* h) {
   ACINO_CUDA(cudaMalloc(&s.polish_list[0], (size_t)SchurState::POLISH_CAP * sizeof(unsigned)));
   ACINO_CUDA(cudaMalloc(&s.polish_list[1], (size_t)SchurState::POLISH_CAP * sizeof(unsigned)));
   ACINO_CUDA(cudaMallocHost(&s.h_lm, sizeof(SchurLm)));
+  ACINO_CUDA(cudaMallocHost(&s.h_ring, SchurState::RING * sizeof(SchurLm)));
+  for (int i = 0; i < SchurState::RING; ++i) ACINO_CUDA(cudaEventCreateWithFlags(&s.ring_ev[i], cudaEventDisableTiming));
   ACINO_CUDA(cudaMalloc(&s.hist, (size_t)ncls * nb * sizeof(unsigned)));
   ACINO_CUDA(cudaMalloc(&s.cls_starts, (size_t)ncls * sizeof(unsigned)));
   ACINO_CUDA(cudaMallocHost(&s.h_cls_starts, (size_t)ncls * sizeof(unsigned)));
@@ -218,6 +220,8 @@ static void schur_free(SchurState& s) {
   cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.hist); cudaFree(s.cls_starts); cudaFree(s.cls);
   cudaFree(s.pid); cudaFree(s.lamS); cudaFree(s.Xs[0]); cudaFree(s.Xs[1]); cudaFree(s.uvs); cudaFree(s.stg); cudaFree(s.tiles); cudaFree(s.tile_range);
   if (s.h_lm) cudaFreeHost(s.h_lm);
+  if (s.h_ring) cudaFreeHost(s.h_ring);
+  for (cudaEvent_t e : s.ring_ev) if (e) cudaEventDestroy(e);
   if (s.h_cls_starts) cudaFreeHost(s.h_cls_starts);
   for (cudaEvent_t e : s.prof_ev) if (e) cudaEventDestroy(e);
   s = SchurState();
@@ -440,7 +444,7 @@ static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumul
   if (prof) ACINO_CUDA(cudaEventRecord(ev[2], st));
   // the per-CTA partial systems and K4a's sums, folded in a fixed order by len/32 CTAs (a fold by the last CTA of K4b
   // was measured: one CTA chasing 148 partials per entry costs 33 us, this launch 8)
-  fold_partials_kernel<<<(len + 31) / 32, 256, 0, st>>>(s.rcs_partial, accumulate ? s.grid_build : 0, len, s.rcs, nullptr, 0, 0, 0, 0,
+  fold_partials_kernel<<<(len + 31) / 32, FOLD_TB, 0, st>>>(s.rcs_partial, accumulate ? s.grid_build : 0, len, s.rcs, nullptr, 0, 0, 0, 0,
                                                         s.mx, s.lin_partial, grid_lin, rcs_units(C) * RCS_UNIT);
   ACINO_CUDA(cudaGetLastError());
   ++s.launches;
@@ -489,7 +493,7 @@ static int schur_enqueue_iteration(acino_sba* h, const SchurParams& prm, bool pr
     schur_decide_kernel<<<1, 256, 0, st>>>(nullptr, 0, nullptr, s.delta_c, 6 * C, s.lm, prm, px.dev, px.cnt);
     s.launches += 2;
   } else if (h->nranks > 1) {
-    fold_partials_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, 4, s.scal, s.scal_partial, s.grid_back, 1, 4, 2,
+    fold_partials_kernel<<<1, FOLD_TB, 0, st>>>(s.scal_partial, s.grid_back, 4, s.scal, s.scal_partial, s.grid_back, 1, 4, 2,
                                             s.scal + 4, nullptr, 0, 0);
     ACINO_CUDA(cudaGetLastError());
     ACINO_NCCL(g_nccl.GroupStart());
@@ -649,12 +653,34 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     fprintf(stderr, "[acino] init %.3f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_prev).count());
     t_prev = std::chrono::steady_clock::now();
   }
-  for (; it < o->max_iter; ++it) {
-    rc = schur_launch_iteration(h, prm);
-    if (rc) return rc;
-    ACINO_CUDA(cudaMemcpyAsync(s.h_lm, s.lm, sizeof(SchurLm), cudaMemcpyDeviceToHost, h->stream));
-    ACINO_CUDA(cudaStreamSynchronize(h->stream));
-    ++n_sync;
+  // The host reads the LM state ONE ITERATION LATE: while it looks at the state after iteration i, iteration i + 1 is
+  // already queued, so the GPU never waits for the host between iterations. Everything the host decides from that
+  // state is safe to decide late, because a solve that stopped (status != 0) or paused for polishing (status 5, set by
+  // K7) makes the kernels of the queued iteration return at once. Only the iteration right after a polish that may end
+  // the solve is run without a successor (the host itself sets the final status there).
+  prm.polish_tol = polish ? o->polish_tol : 0.0;
+  int launched = 0, seen = 0;       // iterations queued / states read
+  int done_iters = 0;               // iterations whose state has been read
+  bool serial_next = false;
+  for (;;) {
+    const int depth = serial_next ? 1 : 2;
+    while (launched - seen < depth && done_iters + (launched - seen) < o->max_iter) {
+      rc = schur_launch_iteration(h, prm);
+      if (rc) return rc;
+      const int slot = launched % SchurState::RING;
+      ACINO_CUDA(cudaMemcpyAsync(s.h_ring + slot, s.lm, sizeof(SchurLm), cudaMemcpyDeviceToHost, h->stream));
+      ACINO_CUDA(cudaEventRecord(s.ring_ev[slot], h->stream));
+      ++launched;
+    }
+    if (launched == seen) break;      // max_iter reached
+    ACINO_CUDA(cudaEventSynchronize(s.ring_ev[seen % SchurState::RING]));
+    *s.h_lm = s.h_ring[seen % SchurState::RING];
+    ++seen;
+    if (launched == seen) ++n_sync;   // nothing queued behind it: the GPU idles while the host decides
+    serial_next = false;
+    // (every state read belongs to an iteration that ran: a state with status != 0 ends the loop or leads to a polish
+    // that drops the states queued behind it)
+    it = done_iters++;
     {
       const SchurLm& l = *s.h_lm;
       const double row[6] = {(double)l.iter, l.F, l.last_accept ? F_prev - l.F : 0.0, l.dxmax, l.gmax, (double)l.last_accept};
@@ -677,11 +703,13 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
     if (polish) {
       // relative cost changes below 1e-12 are the rounding of the cost sums (10^5 .. 10^7 terms), whatever ftol asks for
       const double ftol_eff = fmax(o->ftol, 1e-12), ftol_abs = ftol_eff * s.h_lm->F;
+      const bool paused = s.h_lm->status == 5;      // K7: an accepted step that gained < polish_tol, >= 4 iterations after the last polish
+      if (paused) s.h_lm->status = 0;
       if (terminal_polish && s.h_lm->status == 0 && it == last_polish + 1 &&
           !(s.h_lm->last_accept && s.h_lm->last_rel_dec > ftol_eff)) {
         // the points were polished after a step that gained <= ftol, and the joint step from the polished points gains
         // nothing either: converged (ftol). Without this rule the damping first has to run up through a series of
-        // rejected steps whose cost differences are rounding noise.
+        // rejected steps whose cost differences are rounding noise. (Nothing is queued behind this iteration.)
         s.h_lm->status = 2;
         ACINO_CUDA(cudaMemcpyAsync(s.lm, s.h_lm, sizeof(SchurLm), cudaMemcpyHostToDevice, h->stream));
       }
@@ -690,22 +718,27 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
       // a second end without any gain since the polish of the first one is the end (otherwise polish -> rejected steps ->
       // end rule -> polish ... runs to max_iter on small scenes)
       if (ended && F_end_polish >= 0.0 && F_end_polish - s.h_lm->F <= ftol_abs) ended = false;
-      const bool creeping = s.h_lm->status == 0 && s.h_lm->last_accept && s.h_lm->last_rel_dec < o->polish_tol && it - last_polish >= 4;
+      const bool creeping = paused && s.h_lm->status == 0;
       if (ended || creeping) {
+        // the iterations queued behind this one have returned at once (status != 0 on the device): their states are
+        // not read, and the stream order puts the polish after them
+        seen = launched;
         if (ended) F_end_polish = s.h_lm->F;
         terminal_polish = creeping && s.h_lm->last_rel_dec <= ftol_eff;
+        serial_next = terminal_polish;
         const int l0 = s.launches;
         const auto t_pol0 = std::chrono::steady_clock::now();
         rc = schur_polish_points(h, prm, 12);
         if (rc) return rc;
         polish_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_pol0).count();
         n_sync += 1;
-        if (getenv("ACINO_TRACE"))
+        if (trace)
           fprintf(stderr, "[acino] polish at iteration %d (%s, rel_dec %.3g, cost %.6f): %d launches\n", it,
                   ended ? "end rule" : "creeping", s.h_lm->last_rel_dec, s.h_lm->F, s.launches - l0);
         last_polish = it;
         s.h_lm->status = 0;
         s.h_lm->need_cost = 1;         // the next linearisation evaluates the cost of the polished points
+        s.h_lm->last_polish = it;
         if (ended) { s.h_lm->lambda = fmin(s.h_lm->lambda, 1e-2); s.h_lm->nu = 2.0; }
         ACINO_CUDA(cudaMemcpyAsync(s.lm, s.h_lm, sizeof(SchurLm), cudaMemcpyHostToDevice, h->stream));
         continue;

@@ -44,3 +44,12 @@ wall = time.perf_counter() - t0
 pr = s.profile_read()
 s.profile(False)
 print(json.dumps(dict(frames=frames, steps=steps, ms_per_step_wall=wall / steps * 1e3, kernels=pr, lm=s.lm_state())))
+# the same iterations replayed as a CUDA graph (no profiling events between the kernels)
+for _ in range(5):
+    s.iterate(o)
+_capi.check(L.acino_sync())
+t0 = time.perf_counter()
+for _ in range(steps):
+    s.iterate(o)
+_capi.check(L.acino_sync())
+print(json.dumps(dict(ms_per_step_graph=(time.perf_counter() - t0) / steps * 1e3)))
