@@ -896,6 +896,18 @@ schur_solve_kernel(const double* __restrict__ partial, int n_partial, const doub
     // The wait comes before the early return: every push is consumed, which is what makes two slot parities enough.
     const unsigned long long seq = xcnt[0] + 1;
     unsigned char* own = xd.base[xd.rank];
+    // producer side, in the same kernel (it used to be a launch of its own): this rank's folded system (`partial`, one
+    // row) and its two maxima go into slot [rank] of every rank's buffer - stores over NVLink -, then the sequence
+    // number is published there
+    for (int q = 0; q < xd.nranks; ++q) {
+      double* dst = xchg_slot_a(xd.base[q], xd.nranks, xd.len, (int)(seq & 1));
+      double* d_rcs = dst + (size_t)xd.rank * xd.len;
+      for (int i = tid; i < xd.len; i += blockDim.x) d_rcs[i] = partial[i];
+      if (tid < 2) dst[(size_t)xd.nranks * xd.len + 2 * xd.rank + tid] = maxp[tid];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < xd.nranks) st_release_sys(xchg_flags(xd.base[tid], 0) + xd.rank, seq);
     const double* slot = xchg_slot_a(own, xd.nranks, xd.len, (int)(seq & 1));
     partial = slot;
     n_partial = xd.nranks;
@@ -1238,6 +1250,36 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
   if (xcnt) {      // peer exchange: one row per rank, written by the peers (waited for even when idle)
     const unsigned long long seq = xcnt[1] + 1;
     unsigned char* own = xd.base[xd.rank];
+    {
+      // producer side, in the same kernel: fold this rank's per-CTA rows (`scal`, n_scal of them) in a fixed order,
+      // write the row into slot [rank] of every rank's buffer and publish the sequence number there
+      __shared__ double pr[3][8];
+      __shared__ double prow[4];
+      double a = 0.0, b = 0.0, c = 0.0;
+      for (int i = tid; i < n_scal; i += blockDim.x) {
+        a += scal[4 * i]; b += scal[4 * i + 1]; c = fmax(c, scal[4 * i + 2]);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+        c = fmax(c, __shfl_xor_sync(0xffffffffu, c, o));
+      }
+      if (lane == 0) { pr[0][warp] = a; pr[1][warp] = b; pr[2][warp] = c; }
+      __syncthreads();
+      if (tid == 0) {
+        a = 0.0; b = 0.0; c = 0.0;
+        for (int w = 0; w < 8; ++w) { a += pr[0][w]; b += pr[1][w]; c = fmax(c, pr[2][w]); }
+        prow[0] = a; prow[1] = b; prow[2] = c; prow[3] = 0.0;
+      }
+      __syncthreads();
+      if (tid < xd.nranks) {
+        double* d = xchg_slot_b(xd.base[tid], xd.nranks, xd.len, (int)(seq & 1)) + 4 * xd.rank;
+        d[0] = prow[0]; d[1] = prow[1]; d[2] = prow[2]; d[3] = prow[3];
+        __threadfence_system();
+        st_release_sys(xchg_flags(xd.base[tid], 1) + xd.rank, seq);
+      }
+    }
     scal = xchg_slot_b(own, xd.nranks, xd.len, (int)(seq & 1));
     n_scal = xd.nranks;
     const bool ok = xchg_wait(xchg_flags(own, 1), xd.nranks, seq, tid);

@@ -462,11 +462,8 @@ static int schur_enqueue_iteration(acino_sba* h, const SchurParams& prm, bool pr
   PeerXchg& px = h->xchg;
   const XchgDev none{};
   if (h->nranks > 1 && px.enabled) {
-    // peer exchange: push this rank's folded system into every rank's slot; K5 waits for all ranks and adds the rows
-    xchg_push_rcs_kernel<<<h->nranks, 256, 0, st>>>(px.dev, s.rcs, s.mx, px.cnt);
-    ACINO_CUDA(cudaGetLastError());
-    ++s.launches;
-    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, SCHUR_SOLVE_TB, 0, st>>>(nullptr, 0, nullptr, 0, h->cams, s.cams_alt, h->cams, s.cams_alt,
+    // peer exchange: K5 pushes this rank's folded system into every rank's slot, waits for all ranks and adds the rows
+    DISPATCH_C(C, (schur_solve_kernel<CC><<<1, SCHUR_SOLVE_TB, 0, st>>>(s.rcs, 1, s.mx, 1, h->cams, s.cams_alt, h->cams, s.cams_alt,
                                                                        s.lm, prm, s.delta_c, px.dev, px.cnt)));
   } else {
     if (h->nranks > 1) {
@@ -488,10 +485,8 @@ static int schur_enqueue_iteration(acino_sba* h, const SchurParams& prm, bool pr
   if (prof) { ACINO_CUDA(cudaEventRecord(ev[4], st)); ++s.prof_n; }
   ++s.launches;
   if (h->nranks > 1 && px.enabled) {
-    xchg_push_scal_kernel<<<1, 256, 0, st>>>(px.dev, s.scal_partial, s.grid_back, px.cnt);
-    ACINO_CUDA(cudaGetLastError());
-    schur_decide_kernel<<<1, 256, 0, st>>>(nullptr, 0, nullptr, s.delta_c, 6 * C, s.lm, prm, px.dev, px.cnt);
-    s.launches += 2;
+    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm, px.dev, px.cnt);
+    ++s.launches;
   } else if (h->nranks > 1) {
     fold_partials_kernel<<<1, FOLD_TB, 0, st>>>(s.scal_partial, s.grid_back, 4, s.scal, s.scal_partial, s.grid_back, 1, 4, 2,
                                             s.scal + 4, nullptr, 0, 0);

@@ -8,7 +8,8 @@
 // sequence number into its flag on that peer. The consumer kernels (K5 for the camera system, K7 for the trial scalars)
 // spin on their LOCAL flags until every rank's sequence number has arrived and then add the slots in rank order - the
 // same order on every rank, so all ranks hold bit-identical sums and take identical decisions without a broadcast.
-// The reduction is thus fused into the kernel that needs the result; nothing but the pushing kernel is launched.
+// The whole collective - push, wait, reduce - is thus fused into the kernel that needs the result (the pushes were
+// separate launches at first: two more kernels per iteration, 6 us).
 //
 // Slots are double buffered by the parity of the sequence number. A rank can start collective n+1 while a peer still
 // reads collective n (other parity), and cannot start n+2 before that peer has pushed n+1, which the peer does only
@@ -83,58 +84,7 @@ __device__ __forceinline__ bool xchg_wait(const unsigned long long* flags, int n
   return ok;
 }
 
-// Collective A, producer side: CTA b writes this rank's folded camera system (len doubles) and its two maxima into
-// slot [rank] of peer b (b == rank: the own buffer), then publishes sequence number seq on that peer.
-__global__ void __launch_bounds__(256)
-xchg_push_rcs_kernel(XchgDev x, const double* __restrict__ rcs, const double* __restrict__ mx, const unsigned long long* __restrict__ cnt) {
-  const unsigned long long seq = cnt[0] + 1;          // the consumer of this collective (K5) advances the count
-  unsigned char* dst_base = x.base[blockIdx.x];
-  double* slot = xchg_slot_a(dst_base, x.nranks, x.len, (int)(seq & 1));
-  double* d_rcs = slot + (size_t)x.rank * x.len;
-  double* d_mx = slot + (size_t)x.nranks * x.len + 2 * x.rank;
-  for (int i = threadIdx.x; i < x.len; i += blockDim.x) d_rcs[i] = rcs[i];
-  if (threadIdx.x < 2) d_mx[threadIdx.x] = mx[threadIdx.x];
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) st_release_sys(xchg_flags(dst_base, 0) + x.rank, seq);
-}
-
-// Collective B, producer side (one CTA): fold the back-substitution kernel's per-CTA partials
-// [trial cost, predicted reduction, max |dX|, 0] in a fixed order, write the row into slot [rank] of every peer and
-// publish seq there.
-__global__ void __launch_bounds__(256)
-xchg_push_scal_kernel(XchgDev x, const double* __restrict__ scal_partial, int n_partial, const unsigned long long* __restrict__ cnt) {
-  const unsigned long long seq = cnt[1] + 1;          // K7 advances the count
-  __shared__ double red[3][8];
-  __shared__ double row[4];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  double a = 0.0, b = 0.0, c = 0.0;
-  for (int i = tid; i < n_partial; i += blockDim.x) {
-    a += scal_partial[4 * i];
-    b += scal_partial[4 * i + 1];
-    c = fmax(c, scal_partial[4 * i + 2]);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    a += __shfl_xor_sync(0xffffffffu, a, o);
-    b += __shfl_xor_sync(0xffffffffu, b, o);
-    c = fmax(c, __shfl_xor_sync(0xffffffffu, c, o));
-  }
-  if (lane == 0) { red[0][warp] = a; red[1][warp] = b; red[2][warp] = c; }
-  __syncthreads();
-  if (tid == 0) {
-    a = 0.0; b = 0.0; c = 0.0;
-    for (int w = 0; w < 8; ++w) { a += red[0][w]; b += red[1][w]; c = fmax(c, red[2][w]); }
-    row[0] = a; row[1] = b; row[2] = c; row[3] = 0.0;
-  }
-  __syncthreads();
-  if (tid < x.nranks) {
-    unsigned char* dst_base = x.base[tid];
-    double* d = xchg_slot_b(dst_base, x.nranks, x.len, (int)(seq & 1)) + 4 * x.rank;
-    d[0] = row[0]; d[1] = row[1]; d[2] = row[2]; d[3] = row[3];
-    __threadfence_system();
-    st_release_sys(xchg_flags(dst_base, 1) + x.rank, seq);
-  }
-}
+// The producer side of both collectives lives in the consuming kernels themselves (K5: schur_solve_kernel, K7:
+// schur_decide_kernel, acino_sba_schur.cuh): push the own row to every rank, publish, wait, add. No launch of its own.
 
 }  // namespace acino

@@ -338,7 +338,7 @@ def native_arm(args):
         build_bytes = P * 1 + n_pts * 24 + n_obs * 16
         back_bytes = build_bytes + n_pts * 24
         kern = dict(name=f'schur_accum_kernel<{C}>', ms_per_launch=pr['build_ms'], bytes_per_launch=build_bytes,
-                    launches_per_step=6 if world == 1 else (8 if comm_mode == 'peer' else 9), collective=comm_mode,
+                    launches_per_step=6 if world == 1 or comm_mode == 'peer' else 9, collective=comm_mode,
                     backsub_ms=pr['backsub_ms'], backsub_bytes=back_bytes, linearise_ms=pr['linearise_ms'],
                     accumulate_ms=pr['accumulate_ms'], solve_ms=pr['solve_ms'], profiled_iterations=pr['iterations'],
                     ms_per_step_profiled=ms_per_step_profiled)
