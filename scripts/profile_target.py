@@ -1,5 +1,6 @@
-"""Small fixed workload for ncu: C4-sized scene (119,490 frames), TRI x2, K1 once, 8 Schur LM iterations (embedded
-refinement on from the second one), 2 points-only LM iterations. Usage: python scripts/profile_target.py [frames]"""
+"""Small fixed workload for ncu: C4-sized scene (119,490 frames), TRI x2, K1 once, n_fixed + n_refine Schur LM iterations
+(plain linearisation / embedded refinement), 2 points-only LM iterations.
+Usage: python scripts/profile_target.py [frames] [n_fixed] [n_refine]"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ctypes as ct
@@ -7,6 +8,8 @@ import numpy as np
 from acinoset_b200 import synth, dense, sba, _capi
 
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 119490
+n_fixed = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+n_refine = int(sys.argv[3]) if len(sys.argv) > 3 else 4
 sc = synth.make_rig_scene(frames, 20, seed=4)
 k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
 P, C = sc['lik'].shape
@@ -27,9 +30,9 @@ s.set_points(np.nan_to_num(xyz_d.download()))
 o = dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, force_iters=1)
 f = s.residuals()       # K1 (residuals_dense_kernel) once
 o_fixed = dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, force_iters=1, point_refine_iters=0)
-for _ in range(4):      # the bench's fixed-work step: plain linearisation (schur_linearise_kernel<C, false>)
+for _ in range(n_fixed):      # the bench's fixed-work step: plain linearisation (schur_linearise_kernel<C, false>)
     s.iterate(o_fixed)
-for _ in range(4):      # a solve's step: embedded refinement on (schur_linearise_kernel<C, true>)
+for _ in range(n_refine):      # a solve's step: embedded refinement on (schur_linearise_kernel<C, true>)
     s.iterate(o)
 print('schur', s.lm_state())
 s.reset_state()
