@@ -165,7 +165,9 @@ typedef struct {
   double init_ms;          /* points+extrinsics: of solve_ms, the once-per-solve set-up (points sorted by observation mask,
                               observations in that layout, tiles; K3's visiting order). Host clock around the synchronised section */
   double polish_ms;        /* points+extrinsics: of solve_ms, the polishing launches (K3 to convergence, cameras fixed) */
-  double syncs;            /* host synchronisations inside the solve */
+  double syncs;            /* host synchronisations inside the solve with nothing queued behind them (the GPU idles while the
+                            * host decides): set-up, polishes, the end. The per-iteration read of the LM state is made one
+                            * iteration late, with the next iteration already queued, and is not counted */
 } acino_sba_stats;
 
 void acino_sba_default_opts(acino_sba_opts* o, int mode);
