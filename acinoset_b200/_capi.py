@@ -21,7 +21,8 @@ class AcinoError(RuntimeError):
 class SbaOpts(ct.Structure):
     _fields_ = [('mode', ct.c_int32), ('max_iter', ct.c_int32), ('inner_iters', ct.c_int32), ('force_iters', ct.c_int32),
                 ('f_scale', ct.c_double), ('gtol', ct.c_double), ('xtol', ct.c_double), ('lambda0', ct.c_double),
-                ('ftol', ct.c_double), ('hess_floor', ct.c_double), ('point_refine_iters', ct.c_double), ('point_refine_skip', ct.c_double), ('polish_tol', ct.c_double)]
+                ('ftol', ct.c_double), ('hess_floor', ct.c_double), ('point_refine_iters', ct.c_double), ('point_refine_skip', ct.c_double), ('polish_tol', ct.c_double),
+                ('lambda_dec', ct.c_double)]
 
 
 class SbaStats(ct.Structure):

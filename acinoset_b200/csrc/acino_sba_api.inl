@@ -179,6 +179,7 @@ void acino_sba_default_opts(acino_sba_opts* o, int mode) {
     o->point_refine_skip = 1e-8;      // scripts/refine_sweep.py: 1e-11 refines every point in every iteration for nothing (24 iterations / 26.8 ms
                                       // at C4 against 21 / 21.6 ms), 1e-6 lets the joint steps creep (37 / 31.6 ms)
     o->polish_tol = 3e-4;
+    o->lambda_dec = 0.2;         // scripts/dec_sweep.py: 1/3 (Nielsen) needs 10-25 % more iterations for a final cost a few 1e-6 lower, 0.1 gets steps rejected
     o->lambda0 = 1.0;            // cautious first steps: a small start lets the first accepted step throw points into worse basins of the robust cost
   } else {
     o->max_iter = 200;

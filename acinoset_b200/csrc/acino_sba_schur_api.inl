@@ -243,6 +243,7 @@ static SchurParams make_schur_params(const acino_sba* h, const acino_sba_opts* o
   p.force = o->force_iters;
   p.refine = o->point_refine_iters > 0 ? (int)o->point_refine_iters : 0;
   p.refine_skip = o->point_refine_skip > 0 ? o->point_refine_skip : 0.0;
+  p.lam_dec = (o->lambda_dec > 0.0 && o->lambda_dec < 1.0) ? o->lambda_dec : 0.2;
   return p;
 }
 
