@@ -52,6 +52,11 @@ SIGNATURES = {
     'acino_h2d': (_I, [_P, _P, _I64]),
     'acino_d2h': (_I, [_P, _P, _I64]),
     'acino_sync': (_I, []),
+    'acino_stream_create': (_I, [ct.POINTER(_P)]),
+    'acino_stream_destroy': (_I, [_P]),
+    'acino_stream_sync': (_I, [_P]),
+    'acino_h2d_async': (_I, [_P, _P, _I64, _P]),
+    'acino_d2h_async': (_I, [_P, _P, _I64, _P]),
     'acino_project': (_I, [_P, _I64, _P, _P]),
     'acino_project_dev': (_I, [_P, _I64, _P, _P, _P]),
     'acino_project_all': (_I, [_P, _I64, _P, _I, _D, _D, _P]),
@@ -74,6 +79,7 @@ SIGNATURES = {
     'acino_sba_set_points': (_I, [_P, _P]),
     'acino_sba_set_points_dev': (_I, [_P, _P]),
     'acino_sba_get_points': (_I, [_P, _P]),
+    'acino_sba_get_points_dev': (_I, [_P, _P]),
     'acino_sba_get_cameras': (_I, [_P, _P]),
     'acino_sba_get_rvec_t': (_I, [_P, _P, _P]),
     'acino_sba_set_rvec_t': (_I, [_P, _P, _P]),

@@ -335,6 +335,17 @@ int acino_sba_get_points(acino_sba_t* h, double* xyz) {
   return ACINO_OK;
 }
 
+int acino_sba_get_points_dev(acino_sba_t* h, double* xyz_dev) {
+  H_CHECK(h);
+  ARG_CHECK(h->P == 0 || xyz_dev, "get_points_dev");
+  { int rc = schur_sync_current(h); if (rc) return rc; }
+  if (h->P) {
+    ACINO_CUDA(cudaMemcpyAsync(xyz_dev, h->X, h->P * 3 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    ACINO_CUDA(cudaStreamSynchronize(h->stream));
+  }
+  return ACINO_OK;
+}
+
 int acino_sba_get_cameras(acino_sba_t* h, double* cams24) {
   H_CHECK(h);
   ARG_CHECK(cams24, "get_cameras");

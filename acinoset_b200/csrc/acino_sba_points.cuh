@@ -247,6 +247,8 @@ lm_points_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs
       cost_p[p] = ne.F;
       status[p] = st;
       still = (st == ST_ACTIVE);
+    } else if (m == 0) {
+      cost_p[p] = 0.0;      // a slot group without observations costs nothing (the mask may have changed since the entry was written)
     }
   }
   const unsigned bal = __ballot_sync(0xffffffffu, still);

@@ -235,6 +235,15 @@ exclusive_scan_kernel(unsigned* __restrict__ v, int64_t n, unsigned long long* _
   if (tid == 0) total[0] = carry;
 }
 
+// dst[i] <- src[i] for a table the host wrote into page-locked memory: the kernel reads it over PCIe itself. A
+// cudaMemcpyAsync of more than a few tens of KB goes through the copy engine, which takes the transfers of ALL streams
+// in the order they were issued - behind a 344 MB upload of the next scene on another stream the solve's set-up waited
+// 5.6 ms for an 86 KB table (dense.ScenePipeline.run_many).
+__global__ void __launch_bounds__(256)
+copy_from_host_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src_host, size_t n16) {
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) dst[i] = src_host[i];
+}
+
 // the scan value at the first block of every class, contiguous for the read-back: out[m] = hist[m * n_blocks]
 __global__ void cls_starts_kernel(const unsigned* __restrict__ hist, int n_blocks, int ncls, unsigned* __restrict__ out) {
   const int m = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1483,6 +1492,8 @@ struct SchurState {
   double2* uvs = nullptr;                  // observation rows
   double2* stg = nullptr;                  // staging rows written by K4a, read by K4b and K6
   SchurTile* tiles = nullptr;
+  SchurTile* h_tiles = nullptr;            // page-locked staging of the tile table (read by copy_from_host_kernel)
+  size_t cap_htiles = 0;
   unsigned* tile_range = nullptr;          // [grid_build + 1]
   size_t cap_pid = 0, cap_lam = 0, cap_uvs = 0, cap_stg = 0, cap_tiles = 0;     // capacities (grow only)
   int64_t E = 0;                           // existing points of the current solve

@@ -221,6 +221,7 @@ static void schur_free(SchurState& s) {
   cudaFree(s.pid); cudaFree(s.lamS); cudaFree(s.Xs[0]); cudaFree(s.Xs[1]); cudaFree(s.uvs); cudaFree(s.stg); cudaFree(s.tiles); cudaFree(s.tile_range);
   if (s.h_lm) cudaFreeHost(s.h_lm);
   if (s.h_ring) cudaFreeHost(s.h_ring);
+  if (s.h_tiles) cudaFreeHost(s.h_tiles);
   for (cudaEvent_t e : s.ring_ev) if (e) cudaEventDestroy(e);
   if (s.h_cls_starts) cudaFreeHost(s.h_cls_starts);
   for (cudaEvent_t e : s.prof_ev) if (e) cudaEventDestroy(e);
@@ -354,7 +355,21 @@ static int schur_build_layout(acino_sba* h) {
   if ((rc = schur_grow(s.stg, s.cap_stg, (size_t)rows * SCHUR_ROW + SCHUR_ROW))) return rc;
   if ((rc = schur_grow(s.tiles, s.cap_tiles, tiles.size() + 1))) return rc;
   ACINO_CUDA(cudaMemcpyAsync(s.cls, &hc, sizeof(hc), cudaMemcpyHostToDevice, h->stream));
-  if (!tiles.empty()) ACINO_CUDA(cudaMemcpyAsync(s.tiles, tiles.data(), tiles.size() * sizeof(SchurTile), cudaMemcpyHostToDevice, h->stream));
+  if (!tiles.empty()) {
+    static_assert(sizeof(SchurTile) == 16, "the tile table is copied in 16-byte words");
+    if (tiles.size() > s.cap_htiles) {
+      if (s.h_tiles) cudaFreeHost(s.h_tiles);
+      s.h_tiles = nullptr; s.cap_htiles = 0;
+      const size_t cap = tiles.size() + tiles.size() / 4 + 64;
+      ACINO_CUDA(cudaMallocHost(&s.h_tiles, cap * sizeof(SchurTile)));
+      s.cap_htiles = cap;
+    }
+    memcpy(s.h_tiles, tiles.data(), tiles.size() * sizeof(SchurTile));
+    const size_t n16 = tiles.size();
+    copy_from_host_kernel<<<(unsigned)std::min<size_t>((n16 + 255) / 256, 64), 256, 0, h->stream>>>(
+        reinterpret_cast<uint4*>(s.tiles), reinterpret_cast<const uint4*>(s.h_tiles), n16);
+    ACINO_CUDA(cudaGetLastError());
+  }
   ACINO_CUDA(cudaMemcpyAsync(s.tile_range, range.data(), range.size() * sizeof(unsigned), cudaMemcpyHostToDevice, h->stream));
   if (rounds > 0) {
     ACINO_CUDA(cudaMemsetAsync(s.pid, 0xFF, (size_t)rounds * 32 * sizeof(unsigned), h->stream));

@@ -263,8 +263,73 @@ class ScenePipeline:
                                       total=ms(t0, t4))
         return st
 
+    def run_many(self, scenes, thresh, out_points=None, rvec_t0=None, **solver_opts):
+        """The same as ``run`` for a sequence of scenes ``[(uv, lik), ...]`` of this pipeline's shape, with the transfers
+        taken off the critical path: the upload of scene i + 1 (one of two input buffers, a copy stream of the
+        pipeline's: ``acino_h2d_async``) and the download of the points of scene i - 1 (a device copy of them,
+        ``acino_sba_get_points_dev``, on a second copy stream) run beside the triangulation and the solve of scene i.
+        The host arrays must be page-locked for that (e.g. ``torch.Tensor.pin_memory``); pageable ones work, without
+        the overlap. Returns the list of solver statistics, all results on the host; ``st['t_solved']`` is the host
+        clock (``time.perf_counter``) when the scene's solve had ended and its download was queued."""
+        import time
+        L = _capi.lib()
+        scenes = list(scenes)
+        n = len(scenes)
+        if n == 0:
+            return []
+        if getattr(self, '_copy_stream', None) is None:
+            sp, sq = ct.c_void_p(), ct.c_void_p()
+            _capi.check(L.acino_stream_create(ct.byref(sp)))
+            _capi.check(L.acino_stream_create(ct.byref(sq)))
+            self._copy_stream, self._down_stream = sp, sq
+            self._uv2 = [self.uv_d, DeviceArray((self.P, self.C, 2), np.float64)]
+            self._lik2 = [self.lik_d, DeviceArray((self.P, self.C), np.float64)]
+            self._out2 = [DeviceArray((self.P, 3), np.float64), DeviceArray((self.P, 3), np.float64)]
+        cs, ds = self._copy_stream, self._down_stream
+        keep = []
+
+        def upload(i):
+            uv = _capi.f64(scenes[i][0]).reshape(self.P, self.C, 2)
+            lik = _capi.f64(scenes[i][1]).reshape(self.P, self.C)
+            keep.append((uv, lik))          # alive until the copy has run
+            _capi.check(L.acino_h2d_async(self._uv2[i & 1].ptr, _capi.ptr(uv), uv.nbytes, cs))
+            _capi.check(L.acino_h2d_async(self._lik2[i & 1].ptr, _capi.ptr(lik), lik.nbytes, cs))
+
+        upload(0)
+        res = []
+        for i in range(n):
+            _capi.check(L.acino_stream_sync(cs))        # scene i is on the device (its copy ran during solve i - 1)
+            if i + 1 < n:
+                upload(i + 1)                           # runs beside everything below
+            uv_d, lik_d = self._uv2[i & 1], self._lik2[i & 1]
+            _capi.check(L.acino_triangulate_ring_dev(uv_d.ptr, lik_d.ptr, float(thresh), self.P, self.C, _capi.ptr(self.cams),
+                                                     self.xyz_d.ptr, self.mask_d.ptr, self.ex_d.ptr, ct.c_void_p(self.solver.stream)))
+            self.solver.set_observations_dev(uv_d, self.mask_d)
+            self.solver.set_cameras(*self.cam_args)
+            if self.mode == MODE_POINTS_AND_EXTRINSICS and rvec_t0 is not None and rvec_t0[0] is not None:
+                self.solver.set_rvec_t(rvec_t0[0], rvec_t0[1])
+            self.solver.set_points_dev(self.xyz_d)
+            st = self.solver.solve(default_opts(self.mode, **solver_opts))
+            out = out_points[i] if out_points is not None else np.empty((self.P, 3))
+            stage = self._out2[i & 1]
+            if i >= 2:
+                _capi.check(L.acino_stream_sync(ds))    # the download of scene i - 2 has left this staging buffer
+            _capi.check(L.acino_sba_get_points_dev(self.solver._h, stage.ptr))
+            _capi.check(L.acino_d2h_async(_capi.ptr(out), stage.ptr, stage.nbytes, ds))     # runs beside scene i + 1
+            st['points'] = out
+            st['t_solved'] = time.perf_counter()
+            res.append(st)
+        _capi.check(L.acino_stream_sync(ds))
+        self.solver.set_observations_dev(self.uv_d, self.mask_d)      # back to the buffer ``run`` uploads into
+        return res
+
     def close(self):
         self.solver.close()
+        if getattr(self, '_copy_stream', None) is not None:
+            _capi.lib().acino_stream_destroy(self._copy_stream)
+            _capi.lib().acino_stream_destroy(self._down_stream)
+            self._uv2[1].free(); self._lik2[1].free(); self._out2[0].free(); self._out2[1].free()
+            self._copy_stream = None
         for a in (self.uv_d, self.lik_d, self.xyz_d, self.mask_d, self.ex_d):
             a.free()
 

@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--masked-frac', type=float, default=0.5, help='fraction of slots at or below dlc_thresh')
     ap.add_argument('--outlier-frac', type=float, default=0.0, help='fraction of observations with N(0,50 px) outlier noise (C5)')
-    ap.add_argument('--e2e-solves', type=int, default=3)
+    ap.add_argument('--e2e-solves', type=int, default=5)
     ap.add_argument('--min-time', type=float, default=0.5, help='the timed region repeats its K steps until it lasts this many seconds')
     ap.add_argument('--strong-frames', type=int, default=C4_FRAMES,
                     help='frames of the ONE scene that is sharded over all ranks for the strong-scaling block (0: skip)')
@@ -380,18 +380,38 @@ def e2e_arm(args, ctx):
     rv0 = (ctx.get('rv'), ctx.get('tv')) if ctx['mode'] == 'extrinsics' else None
     # the reference's own stopping literal for this mode (src/lib/sba.py:170-173 ftol=1e-10); points-only keeps its defaults
     opts = dict(ftol=1e-10) if ctx['mode'] == 'extrinsics' else {}
-    iters, times, last = 0, [], None
-    for i in range(args.e2e_solves + 1):
+    # Throughput: a sequence of solves with the upload of solve i + 1 and the download of solve i - 1 overlapped
+    # with the LM of solve i (ScenePipeline.run_many: two input buffers, two copy streams); the first solve is the warm-up and the clock runs from
+    # its completion to the completion of the last, so every timed solve has its upload, triangulation, LM and
+    # download inside the region.
+    n_seq = args.e2e_solves + 1
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    out2_h = torch.empty((P, 3), dtype=torch.float64).pin_memory()      # consecutive solves download into different arrays
+    outs = [(out_h if i % 2 == 0 else out2_h).numpy() for i in range(n_seq)]
+    res = pipe.run_many([(uv_h.numpy(), lik_h.numpy())] * n_seq, THRESH, outs, rv0, **opts)
+    torch.cuda.synchronize()
+    t_end = time.perf_counter()
+    last = res[-1]
+    # from the end of the warm-up solve (its download queued) to the last result on the host: n_seq - 1 whole solves
+    times = [(t_end - res[0]['t_solved']) / (n_seq - 1)] * (n_seq - 1)
+    iters = sum(r['iterations'] for r in res[1:])
+    # Latency: one solve on its own, nothing overlapped (what the breakdown below splits up)
+    lat = []
+    for i in range(2):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        last = pipe.run(uv_h.numpy(), lik_h.numpy(), THRESH, out_h.numpy(), rv0, **opts)
+        pipe.run(uv_h.numpy(), lik_h.numpy(), THRESH, out_h.numpy(), rv0, **opts)
         torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        if i > 0:                     # first solve is the warm-up
-            times.append(dt)
-            iters += last['iterations']
+        lat.append(time.perf_counter() - t0)
+    latency = min(lat)
+    if world > 1:
+        lt = torch.tensor([latency], device='cuda', dtype=torch.float64)
+        dist.all_reduce(lt, op=dist.ReduceOp.MAX)
+        latency = float(lt.item())
     if world > 1:
         dist.barrier()
     bd = pipe.run(uv_h.numpy(), lik_h.numpy(), THRESH, out_h.numpy(), rv0, breakdown=True, **opts).get('breakdown_ms')
@@ -404,8 +424,13 @@ def e2e_arm(args, ctx):
     h2d = uv_h.numel() * 8 + lik_h.numel() * 8
     d2h = out_h.numel() * 8
     return dict(value=world * iters / total * (args.frames / C4_FRAMES), unit=UNIT,
-                step='one full solve per GPU shard: H2D observations+likelihoods, TRI, LM until the stopping rule, D2H points',
-                solve_ms=1e3 * total / len(times), lm_iters_per_solve=iters / len(times), exit_status=last.get('status'),
+                step='one full solve per GPU shard: H2D observations+likelihoods, TRI, LM until the stopping rule, D2H points; '
+                     'a sequence of solves through dense.ScenePipeline.run_many, which uploads solve i+1 and downloads solve i-1 (copy '
+                     'streams, second buffers) while solve i runs - every timed solve has all four phases inside the region',
+                pipelined=True, solves_timed=len(times),
+                solve_ms=1e3 * total / len(times), latency_ms=1e3 * latency,
+                latency_note='one solve on its own through ScenePipeline.run, nothing overlapped (breakdown_ms splits this one up)',
+                lm_iters_per_solve=iters / len(times), exit_status=last.get('status'),
                 cost_initial=last['cost_initial'], cost_final=last['cost_final'],
                 launches_per_solve=last.get('launches'), host_syncs_per_solve=last.get('syncs'),
                 breakdown_ms=bd, breakdown_note='one extra solve of this rank with a synchronisation between the phases (host clock); '

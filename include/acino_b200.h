@@ -41,6 +41,14 @@ int acino_dev_free(void* dev);
 int acino_h2d(void* dst_dev, const void* src_host, int64_t bytes);
 int acino_d2h(void* dst_host, const void* src_dev, int64_t bytes);
 int acino_sync(void);
+/* The same copies on a stream of the caller's (no counterpart in the reference: plumbing). With page-locked host memory
+ * they return at once, so a host can upload the next scene while the solver works on the current one
+ * (dense.ScenePipeline.run_many); with pageable memory they behave like acino_h2d / acino_d2h. */
+int acino_stream_create(void** out_stream);
+int acino_stream_destroy(void* stream);
+int acino_stream_sync(void* stream);
+int acino_h2d_async(void* dst_dev, const void* src_host, int64_t bytes, void* stream);
+int acino_d2h_async(void* dst_host, const void* src_dev, int64_t bytes, void* stream);
 
 /* K1 — project_points_fisheye, src/lib/calib.py:132-136 (cv::fisheye::projectPoints).
  * X double[N][3] -> uv double[N][2]. Host pointers. */
@@ -183,6 +191,9 @@ int acino_sba_set_observations_dev(acino_sba_t* h, const double* uv_dev, const u
 int acino_sba_set_points(acino_sba_t* h, const double* xyz);                        /* host */
 int acino_sba_set_points_dev(acino_sba_t* h, const double* xyz_dev);                /* d2d copy */
 int acino_sba_get_points(acino_sba_t* h, double* xyz);
+/* the same into a device buffer of the caller's (a copy the caller can download on a stream of its own while the handle
+ * goes on to the next solve: dense.ScenePipeline.run_many) */
+int acino_sba_get_points_dev(acino_sba_t* h, double* xyz_dev);
 int acino_sba_get_cameras(acino_sba_t* h, double* cams24);
 int acino_sba_get_rvec_t(acino_sba_t* h, double* rvecs, double* tvecs);             /* extrinsics mode parameters */
 int acino_sba_set_rvec_t(acino_sba_t* h, const double* rvecs, const double* tvecs);

@@ -130,3 +130,27 @@ def test_extrinsics_solve_prints_scipy_iteration_table(rig, golden_dir, capsys):
     assert all(b <= a * (1 + 1e-12) for a, b in zip(costs, costs[1:]))
     assert any('termination condition is satisfied' in l for l in lines)
     assert any(l.startswith('Function evaluations') for l in lines)
+
+
+def test_scene_pipeline_run_many_equals_run():
+    """dense.ScenePipeline.run_many (uploads and downloads on copy streams beside the solves, second buffers) returns, scene by scene, bit for bit what run returns - in both modes, for scenes that differ, and run
+    still works on the same pipeline afterwards."""
+    from acinoset_b200 import _capi, dense, synth
+    _capi.require_gpu()
+    scs = [synth.make_rig_scene(150, 20, seed=s, masked_frac=0.4) for s in (21, 22, 23)]
+    k, d, r, t = scs[0]['k'], scs[0]['d'], scs[0]['r'], scs[0]['t']
+    P, C = scs[0]['lik'].shape
+    for mode, kw in ((_capi.MODE_POINTS_ONLY, {}), (_capi.MODE_POINTS_AND_EXTRINSICS, dict(ftol=1e-10))):
+        pipe = dense.ScenePipeline(P, C, k, d, r, t, mode)
+        want = [pipe.run(sc['uv'], sc['lik'], 0.5, **kw) for sc in scs]
+        want = [(w['points'].copy(), w['cost_final'], w['iterations']) for w in want]
+        got = pipe.run_many([(sc['uv'], sc['lik']) for sc in scs], 0.5, **kw)
+        assert len(got) == 3
+        for (pw, cw, iw), g in zip(want, got):
+            assert np.array_equal(np.isnan(pw), np.isnan(g['points']))
+            assert np.array_equal(np.nan_to_num(pw), np.nan_to_num(g['points']))
+            assert g['cost_final'] == cw and g['iterations'] == iw
+        again = pipe.run(scs[1]['uv'], scs[1]['lik'], 0.5, **kw)
+        assert np.array_equal(np.nan_to_num(again['points']), np.nan_to_num(want[1][0]))
+        assert pipe.run_many([], 0.5) == []
+        pipe.close()
