@@ -418,7 +418,8 @@ template <bool REFINE>
 __device__ __forceinline__ void schur_linearise_one(const double* __restrict__ sc, unsigned m, int k, const double2* __restrict__ ob,
                                                     double2* __restrict__ blk, bool valid, double X, double Y, double Z,
                                                     double* __restrict__ xs_slot, double* __restrict__ lam_slot, double lam, int refine,
-                                                    bool need_cost, const SchurParams& prm, LinAcc& A) {
+                                                    bool need_cost, const SchurParams& prm, LinAcc& A, bool& unfinished) {
+  unfinished = false;
   PointLin L = schur_lin_point<true>(sc, m, k, ob, blk, X, Y, Z, valid, prm.inv_c2, prm.hfloor);
   if (REFINE && refine > 0 && valid) {
     // ---- the point's own LM with the cameras fixed, from the linearisation just taken
@@ -426,17 +427,18 @@ __device__ __forceinline__ void schur_linearise_one(const double* __restrict__ s
     if (!(lp > 0.0)) lp = 1e-4;
     double nu = 2.0;
     bool moved = false;
+    unfinished = true;        // until one of the convergence exits below is taken: the step budget ran out
 #pragma unroll 1
     for (int it = 0; it < refine; ++it) {
       const double gm = fmax(fabs(L.g0), fmax(fabs(L.g1), fabs(L.g2)));
-      if (!(gm > prm.gtol)) break;
+      if (!(gm > prm.gtol)) { unfinished = false; break; }
       const Sym3Inv iv = damped_inverse3(L.v00, L.v01, L.v02, L.v11, L.v12, L.v22, lp);
       const double d0 = -fma(iv.i00, L.g0, fma(iv.i01, L.g1, iv.i02 * L.g2));
       const double d1 = -fma(iv.i01, L.g0, fma(iv.i11, L.g1, iv.i12 * L.g2));
       const double d2 = -fma(iv.i02, L.g0, fma(iv.i12, L.g1, iv.i22 * L.g2));
       const double pred = 0.5 * (lp * (iv.D0 * d0 * d0 + iv.D1 * d1 * d1 + iv.D2 * d2 * d2) - (L.g0 * d0 + L.g1 * d1 + L.g2 * d2));
       const double F = prm.half_c2 * log1p(L.pm1);
-      if (pred <= prm.refine_skip * fmax(F, prm.half_c2)) break;        // nothing to gain
+      if (pred <= prm.refine_skip * fmax(F, prm.half_c2)) { unfinished = false; break; }        // nothing to gain
       // no further step in this launch: the trial's cost is enough. (Writing the rows with this last trial instead, to
       // spare an accepted point the linearisation after the loop, was measured: the C4 solve takes 21.4 ms instead of 20.0)
       const bool last = (it + 1 == refine);
@@ -454,11 +456,11 @@ __device__ __forceinline__ void schur_linearise_one(const double* __restrict__ s
         moved = true;
         if (last) break;
         L = T;
-        if (dmax <= prm.xtol * (xmax + prm.xtol)) break;
+        if (dmax <= prm.xtol * (xmax + prm.xtol)) { unfinished = false; break; }
       } else {
         lp *= nu;
         nu *= 2.0;
-        if (lp > 1e16) { lp = 1e16; break; }
+        if (lp > 1e16) { lp = 1e16; unfinished = false; break; }
       }
     }
     lam_slot[0] = lp;
@@ -520,7 +522,8 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
                        const double2* __restrict__ uvs, const double* __restrict__ cams0, const double* __restrict__ cams1,
                        double* __restrict__ X0, double* __restrict__ X1, const SchurLm* __restrict__ lm,
                        SchurParams prm, double2* __restrict__ stg, double* __restrict__ lin_partial,
-                       double* __restrict__ lamS) {
+                       double* __restrict__ lamS, unsigned* __restrict__ act_list, unsigned long long* __restrict__ act_cnt,
+                       int act_cap) {
   constexpr int NCLS = 1 << C, NW = SCHUR_LIN_TB / 32;
   __shared__ double sc[C * CAM_STRIDE];
   __shared__ unsigned s_round0[NCLS + 1], s_blk0[NCLS + 1], s_uv0[NCLS + 1];
@@ -567,7 +570,20 @@ schur_linearise_kernel(const SchurClasses* __restrict__ cls, const unsigned* __r
       }
     }
 #endif
-    schur_linearise_one<REFINE>(sc, m, k, ob, blk, valid, X, Y, Z, xs, lamS + gs, lam, refine, need_cost, prm, A);
+    bool unfinished;
+    schur_linearise_one<REFINE>(sc, m, k, ob, blk, valid, X, Y, Z, xs, lamS + gs, lam, refine, need_cost, prm, A, unfinished);
+    if (REFINE && act_list) {
+      // the points whose refinement ran out of steps, listed by scene index (warp-aggregated append; the order does not
+      // matter: the polish treats the points independently): what a polish after this iteration has to finish
+      const unsigned bal = __ballot_sync(0xffffffffu, unfinished);
+      if (bal) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(act_cnt, (unsigned long long)__popc(bal));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        const unsigned long long pos = base + __popc(bal & ((1u << lane) - 1u));
+        if (unfinished && pos < (unsigned long long)act_cap) act_list[pos] = p;
+      }
+    }
   }
   double cost_acc = A.cost + prm.half_c2 * log(A.cprod), gh_acc = A.gh, gmax_acc = A.gmax, xmax_acc = A.xmax;
 #pragma unroll
@@ -1268,7 +1284,7 @@ schur_backsub_kernel(const SchurClasses* __restrict__ cls, const unsigned* __res
 __global__ void __launch_bounds__(256)
 schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* __restrict__ dx_override,
                     const double* __restrict__ delta_c, int n6, SchurLm* __restrict__ lm, SchurParams prm,
-                    XchgDev xd, unsigned long long* __restrict__ xcnt) {
+                    XchgDev xd, unsigned long long* __restrict__ xcnt, unsigned long long* __restrict__ act_cnt) {
   __shared__ double red[3][8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (xcnt) {      // peer exchange: one row per rank, written by the peers (waited for even when idle)
@@ -1370,6 +1386,9 @@ schur_decide_kernel(const double* __restrict__ scal, int n_scal, const double* _
     }
     lm->lambda = l;
   }
+  // K4a's list of points whose refinement ran out of steps: emptied for the next linearisation while the solve runs on,
+  // left alone when it stops or pauses here (the host's polish reads it)
+  if (act_cnt && lm->status == 0) *act_cnt = 0ull;
 }
 
 // fold the per-CTA partials (fixed order: deterministic): block = 32 warps x 32 entries; warp w sums the partials
@@ -1477,8 +1496,11 @@ struct SchurState {
   static constexpr int RING = 4;
   SchurLm* h_ring = nullptr;               // pinned: the LM state after each of the last RING iterations (acino_sba_solve reads them one late)
   cudaEvent_t ring_ev[RING] = {};
-  static constexpr int POLISH_CAP = 1 << 18;
+  static constexpr int POLISH_CAP = 1 << 20;
   unsigned* polish_list[2] = {nullptr, nullptr};   // still-active points of the previous / this polish launch
+  unsigned* act_list = nullptr;                    // [POLISH_CAP] points whose embedded refinement ran out of steps in the latest K4a
+  unsigned long long* act_cnt = nullptr;           // how many (may exceed POLISH_CAP: then the list is incomplete)
+  bool list_polish = true;                         // polish only the listed points when the list is complete (ACINO_POLISH_LIST=0: all points first)
   // the sorted numbering (rebuilt by every solve from the masks)
   unsigned* hist = nullptr;                // [2^C][n_blocks] mask histogram -> exclusive scan
   unsigned* cls_starts = nullptr;          // [2^C] device, scan value at the first block of every class

@@ -195,6 +195,10 @@ static int schur_alloc(acino_sba* h) {
   ACINO_CUDA(cudaMalloc(&s.lm, sizeof(SchurLm)));
   ACINO_CUDA(cudaMalloc(&s.polish_list[0], (size_t)SchurState::POLISH_CAP * sizeof(unsigned)));
   ACINO_CUDA(cudaMalloc(&s.polish_list[1], (size_t)SchurState::POLISH_CAP * sizeof(unsigned)));
+  ACINO_CUDA(cudaMalloc(&s.act_list, (size_t)SchurState::POLISH_CAP * sizeof(unsigned)));
+  ACINO_CUDA(cudaMalloc(&s.act_cnt, sizeof(unsigned long long)));
+  ACINO_CUDA(cudaMemset(s.act_cnt, 0, sizeof(unsigned long long)));
+  { const char* env = getenv("ACINO_POLISH_LIST"); s.list_polish = !(env && env[0] == '0'); }
   ACINO_CUDA(cudaMallocHost(&s.h_lm, sizeof(SchurLm)));
   ACINO_CUDA(cudaMallocHost(&s.h_ring, SchurState::RING * sizeof(SchurLm)));
   for (int i = 0; i < SchurState::RING; ++i) ACINO_CUDA(cudaEventCreateWithFlags(&s.ring_ev[i], cudaEventDisableTiming));
@@ -217,7 +221,7 @@ static void schur_free(SchurState& s) {
   schur_drop_graph(s);
   cudaFree(s.cams_alt); cudaFree(s.X_alt); cudaFree(s.rcs_partial); cudaFree(s.wpart); cudaFree(s.lin_partial); cudaFree(s.rcs);
   cudaFree(s.mx); cudaFree(s.delta_c); cudaFree(s.scal_partial); cudaFree(s.scal); cudaFree(s.lm);
-  cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.hist); cudaFree(s.cls_starts); cudaFree(s.cls);
+  cudaFree(s.polish_list[0]); cudaFree(s.polish_list[1]); cudaFree(s.act_list); cudaFree(s.act_cnt); cudaFree(s.hist); cudaFree(s.cls_starts); cudaFree(s.cls);
   cudaFree(s.pid); cudaFree(s.lamS); cudaFree(s.Xs[0]); cudaFree(s.Xs[1]); cudaFree(s.uvs); cudaFree(s.stg); cudaFree(s.tiles); cudaFree(s.tile_range);
   if (s.h_lm) cudaFreeHost(s.h_lm);
   if (s.h_ring) cudaFreeHost(s.h_ring);
@@ -410,6 +414,7 @@ static int schur_init_lm(acino_sba* h, const acino_sba_opts* o) {
   SchurState& s = h->schur;
   schur_drop_graph(s);          // grids and buffers of the captured launches belong to the previous layout
   schur_init_kernel<<<1, 1, 0, h->stream>>>(s.lm, o->lambda0);
+  ACINO_CUDA(cudaMemsetAsync(s.act_cnt, 0, sizeof(unsigned long long), h->stream));
   ACINO_CUDA(cudaGetLastError());
   // The alternate point buffer starts as a copy of the points: K6 writes trial rows for existing points only, so the
   // rows of points without observations must already hold what the caller set (they are never touched by the solve,
@@ -443,10 +448,12 @@ static int schur_launch_build(acino_sba* h, const SchurParams& prm, bool accumul
   const int grid_lin = prm.refine > 0 ? std::min(s.grid_lin, SCHUR_LIN_MINB_REFINE * s.sms) : s.grid_lin;
   if (prm.refine > 0) {
     DISPATCH_C(C, (schur_linearise_kernel<CC, true><<<grid_lin, SCHUR_LIN_TB, 0, st>>>(
-                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, s.Xs[0], s.Xs[1], s.lm, prm, s.stg, s.lin_partial, s.lamS)));
+                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, s.Xs[0], s.Xs[1], s.lm, prm, s.stg, s.lin_partial, s.lamS,
+                      s.act_list, s.act_cnt, SchurState::POLISH_CAP)));
   } else {
     DISPATCH_C(C, (schur_linearise_kernel<CC, false><<<s.grid_lin, SCHUR_LIN_TB, 0, st>>>(
-                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, s.Xs[0], s.Xs[1], s.lm, prm, s.stg, s.lin_partial, s.lamS)));
+                      s.cls, s.pid, s.uvs, h->cams, s.cams_alt, s.Xs[0], s.Xs[1], s.lm, prm, s.stg, s.lin_partial, s.lamS,
+                      nullptr, nullptr, 0)));
   }
   ACINO_CUDA(cudaGetLastError());
   if (prof) ACINO_CUDA(cudaEventRecord(ev[1], st));
@@ -501,7 +508,7 @@ static int schur_enqueue_iteration(acino_sba* h, const SchurParams& prm, bool pr
   if (prof) { ACINO_CUDA(cudaEventRecord(ev[4], st)); ++s.prof_n; }
   ++s.launches;
   if (h->nranks > 1 && px.enabled) {
-    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm, px.dev, px.cnt);
+    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm, px.dev, px.cnt, s.act_cnt);
     ++s.launches;
   } else if (h->nranks > 1) {
     fold_partials_kernel<<<1, FOLD_TB, 0, st>>>(s.scal_partial, s.grid_back, 4, s.scal, s.scal_partial, s.grid_back, 1, 4, 2,
@@ -511,10 +518,10 @@ static int schur_enqueue_iteration(acino_sba* h, const SchurParams& prm, bool pr
     ACINO_NCCL(g_nccl.AllReduce(s.scal, s.scal, 4, kNcclDouble, kNcclSum, h->nccl_comm, st));
     ACINO_NCCL(g_nccl.AllReduce(s.scal + 4, s.scal + 4, 1, kNcclDouble, kNcclMax, h->nccl_comm, st));
     ACINO_NCCL(g_nccl.GroupEnd());
-    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal, 1, s.scal + 4, s.delta_c, 6 * C, s.lm, prm, none, nullptr);
+    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal, 1, s.scal + 4, s.delta_c, 6 * C, s.lm, prm, none, nullptr, s.act_cnt);
     s.launches += 3;
   } else {
-    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm, none, nullptr);
+    schur_decide_kernel<<<1, 256, 0, st>>>(s.scal_partial, s.grid_back, nullptr, s.delta_c, 6 * C, s.lm, prm, none, nullptr, s.act_cnt);
     ++s.launches;
   }
   ACINO_CUDA(cudaGetLastError());
@@ -602,6 +609,35 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
   // one visits only those (same arithmetic per point, so the same result).
   const int cap = SchurState::POLISH_CAP;
   unsigned long long prev_act = ~0ull;
+  if (s.list_polish && prm.refine > 0) {
+    // The linearisation before this polish has already put every point through `refine` steps of its own LM and listed
+    // those that were not done (K4a, act_list). Only they need more than the next linearisation will give them anyway:
+    // they take the whole iteration budget in ONE launch, and the pass over all points (0.3 - 0.75 ms at C4) goes.
+    ACINO_CUDA(cudaMemcpyAsync(h->h_counters + 6, s.act_cnt, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    ACINO_CUDA(cudaStreamSynchronize(h->stream));
+    const unsigned long long n_act = h->h_counters[6];
+    if (n_act <= (unsigned long long)cap) {
+      const auto t0 = std::chrono::steady_clock::now();
+      if (n_act > 0) {
+        ACINO_CUDA(cudaMemsetAsync(h->counters, 0, 8 * sizeof(unsigned long long), h->stream));
+        lp.inner_iters = 8 * max_launches;
+        LmPointsCtl ctl{nullptr, nullptr, nullptr, nullptr, s.act_list, (int)n_act, s.polish_list[0], cap};
+        DISPATCH_C(h->C, (lm_points_kernel<CC><<<grid_for((int64_t)n_act, 128), 128, 0, h->stream>>>(
+                             h->uv, h->mask, h->P, cams, X, h->lam, h->cost_p, h->status, lp, h->counters, ctl, nullptr)));
+        ACINO_CUDA(cudaGetLastError());
+        ++s.launches;
+      }
+      if (trace) {
+        ACINO_CUDA(cudaMemcpyAsync(h->h_counters, h->counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+        ACINO_CUDA(cudaStreamSynchronize(h->stream));
+        fprintf(stderr, "[acino]   polish of the %llu listed points (%d iterations): %llu still active, %.3f ms\n", n_act, lp.inner_iters,
+                n_act ? h->h_counters[0] : 0ull, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+      }
+      ACINO_CUDA(cudaMemsetAsync(s.act_cnt, 0, sizeof(unsigned long long), h->stream));
+      return schur_points_to_sorted(h);
+    }
+    ACINO_CUDA(cudaMemsetAsync(s.act_cnt, 0, sizeof(unsigned long long), h->stream));
+  }
   for (int l = 0; l < max_launches; ++l) {
     const auto t0 = std::chrono::steady_clock::now();
     ACINO_CUDA(cudaMemsetAsync(h->counters, 0, 8 * sizeof(unsigned long long), h->stream));
