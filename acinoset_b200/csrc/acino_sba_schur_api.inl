@@ -775,7 +775,7 @@ static int solve_schur(acino_sba* h, const acino_sba_opts* o, acino_sba_stats* s
         serial_next = terminal_polish;
         const int l0 = s.launches;
         const auto t_pol0 = std::chrono::steady_clock::now();
-        rc = schur_polish_points(h, prm, 12);
+        rc = schur_polish_points(h, prm, 12);      // 96 LM iterations per listed point; 48 or 24 were measured: the stragglers left behind get the joint steps rejected (26 / 34 iterations instead of 19 at C4), 128 and 192 change nothing
         if (rc) return rc;
         polish_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_pol0).count();
         n_sync += 1;
