@@ -177,6 +177,116 @@ point_order_kernel(const uint8_t* __restrict__ obs_mask, int64_t P, uint16_t* __
   }
 }
 
+// ---- the stragglers of a polish: ONE WARP per listed point ---------------------------------------------------------
+// A polish of the points+extrinsics solve ends with a few points - a dozen to a few thousand - that need tens of LM
+// iterations each. With one thread per point such a launch lasts as long as its slowest point: 96 iterations of k
+// dependent projections, 3 us each, 0.3 ms whatever the length of the list. Here lane c of a warp evaluates the
+// point's observation by camera c (residual, Jacobian, robust weights: one projection deep instead of k), the eleven
+// sums cross the 8 lanes with three shuffle steps, and every lane takes the same 3x3 step: about 1 us per iteration.
+// Same LM as lm_points_kernel (damping rule, tests, status); the sums run in tree order instead of camera order, so
+// the result agrees with it to rounding, not bit for bit.
+__device__ __forceinline__ double warp8_sum(double v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  return v;
+}
+template <int C>
+__device__ __forceinline__ void eval_point_warp(const double* __restrict__ sc, bool has, int c, double2 ob, double X, double Y,
+                                                double Z, double inv_c2, double half_c2, NormalEq& ne) {
+  double q = 1.0, g0 = 0, g1 = 0, g2 = 0, v0 = 0, v1 = 0, v2 = 0, v3 = 0, v4 = 0, v5 = 0;
+  if (has) {
+    const double* cam = sc + c * K3_CAM_STRIDE;
+    double x, y, z, u, v, Ju[3], Jv[3], ju[3], jv[3];
+    to_camera(cam, X, Y, Z, x, y, z);
+    fisheye_uv_jac(cam, x, y, z, u, v, Ju, Jv);
+    mul_R(cam, Ju, ju);
+    mul_R(cam, Jv, jv);
+    const double fu = u - ob.x, fv = v - ob.y;
+    double pm1 = 0.0;
+    const Robust w = cauchy_weights(fu, fv, inv_c2, pm1);
+    q = 1.0 + pm1;
+    const double gu = w.gu * fu, gv = w.gv * fv;
+    g0 = fma(ju[0], gu, jv[0] * gv); g1 = fma(ju[1], gu, jv[1] * gv); g2 = fma(ju[2], gu, jv[2] * gv);
+    const double a0 = w.hu * ju[0], a1 = w.hu * ju[1], a2 = w.hu * ju[2];
+    const double b0 = w.hv * jv[0], b1 = w.hv * jv[1], b2 = w.hv * jv[2];
+    v0 = fma(a0, ju[0], b0 * jv[0]); v1 = fma(a0, ju[1], b0 * jv[1]); v2 = fma(a0, ju[2], b0 * jv[2]);
+    v3 = fma(a1, ju[1], b1 * jv[1]); v4 = fma(a1, ju[2], b1 * jv[2]); v5 = fma(a2, ju[2], b2 * jv[2]);
+  }
+  // prod(1 + z) over the observations: the product of the lanes' factors (lanes without an observation hold 1)
+  q *= __shfl_xor_sync(0xffffffffu, q, 1);
+  q *= __shfl_xor_sync(0xffffffffu, q, 2);
+  q *= __shfl_xor_sync(0xffffffffu, q, 4);
+  ne.F = half_c2 * log(q);
+  ne.g[0] = warp8_sum(g0); ne.g[1] = warp8_sum(g1); ne.g[2] = warp8_sum(g2);
+  ne.V[0] = warp8_sum(v0); ne.V[1] = warp8_sum(v1); ne.V[2] = warp8_sum(v2);
+  ne.V[3] = warp8_sum(v3); ne.V[4] = warp8_sum(v4); ne.V[5] = warp8_sum(v5);
+}
+
+template <int C>
+__global__ void __launch_bounds__(128)
+lm_points_list_warp_kernel(const double2* __restrict__ uv, const uint8_t* __restrict__ obs_mask, const double* __restrict__ cams,
+                           double* __restrict__ Xp, double* __restrict__ lam_p, double* __restrict__ cost_p,
+                           uint8_t* __restrict__ status, LmParams prm, unsigned long long* __restrict__ counters,
+                           const unsigned* __restrict__ list, int n_list) {
+  static_assert(C <= 8, "one lane per camera in groups of 8");
+  __shared__ double sc[C * K3_CAM_STRIDE];
+  for (int i = threadIdx.x; i < C * CAM_STRIDE; i += blockDim.x) sc[(i / CAM_STRIDE) * K3_CAM_STRIDE + i % CAM_STRIDE] = cams[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int idx = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (idx >= n_list) return;
+  const int64_t p = list[idx];
+  const unsigned m = obs_mask[p];
+  if (m == 0) return;
+  const int c = lane & 7;               // the four groups of 8 lanes work redundantly (the shuffles stay inside a group)
+  const bool has = c < C && (m >> c & 1u);
+  const double2 ob = has ? uv[p * C + c] : make_double2(0.0, 0.0);
+  double X = Xp[3 * p], Y = Xp[3 * p + 1], Z = Xp[3 * p + 2];
+  double lam = lam_p[p];
+  if (!(lam > 0.0)) lam = prm.lambda0;
+  NormalEq ne;
+  eval_point_warp<C>(sc, has, c, ob, X, Y, Z, prm.inv_c2, prm.half_c2, ne);
+  double nu = 2.0;
+  uint8_t st = ST_ACTIVE;
+#pragma unroll 1
+  for (int it = 0; it < prm.inner_iters; ++it) {
+    const double gmax = fmax(fabs(ne.g[0]), fmax(fabs(ne.g[1]), fabs(ne.g[2])));
+    if (!prm.force && !(gmax > prm.gtol)) { st = ST_CONVERGED; break; }
+    double d[3];
+    const double pred = lm_step3(ne, lam, d);
+    if (prm.skip_pred > 0.0 && pred <= prm.skip_pred * fmax(ne.F, prm.half_c2)) { st = ST_CONVERGED; break; }
+    NormalEq nt;
+    eval_point_warp<C>(sc, has, c, ob, X + d[0], Y + d[1], Z + d[2], prm.inv_c2, prm.half_c2, nt);
+    const double act = ne.F - nt.F;
+    if (act > 0.0 && pred > 0.0) {
+      const double rho = act / pred;
+      const double q = 2.0 * rho - 1.0;
+      lam = fmax(lam * fmax(1.0 / 3.0, 1.0 - q * q * q), 1e-12);
+      nu = 2.0;
+      const double dmax = fmax(fabs(d[0]), fmax(fabs(d[1]), fabs(d[2])));
+      const double xmax = fmax(fabs(X), fmax(fabs(Y), fabs(Z)));
+      X += d[0]; Y += d[1]; Z += d[2];
+      ne = nt;
+      if (!prm.force && dmax <= prm.xtol * (xmax + prm.xtol)) { st = ST_CONVERGED; break; }
+    } else {
+      lam *= nu;
+      nu *= 2.0;
+      if (lam > 1e16) {
+        if (!prm.force) { st = ST_STALLED; break; }
+        lam = 1e16;
+      }
+    }
+  }
+  if (lane == 0) {
+    Xp[3 * p] = X; Xp[3 * p + 1] = Y; Xp[3 * p + 2] = Z;
+    lam_p[p] = lam;
+    cost_p[p] = ne.F;
+    status[p] = st;
+    if (st == ST_ACTIVE) atomicAdd(&counters[0], 1ull);
+  }
+}
+
 // One launch = up to inner_iters LM iterations of every active point. cost_p[p] = robust cost of the
 // point at exit; counters[0] += points still active at exit.
 template <int C>

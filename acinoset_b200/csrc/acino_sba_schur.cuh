@@ -1500,6 +1500,7 @@ struct SchurState {
   unsigned* polish_list[2] = {nullptr, nullptr};   // still-active points of the previous / this polish launch
   unsigned* act_list = nullptr;                    // [POLISH_CAP] points whose embedded refinement ran out of steps in the latest K4a
   unsigned long long* act_cnt = nullptr;           // how many (may exceed POLISH_CAP: then the list is incomplete)
+  bool warp_polish = true;                         // short lists by one warp per point (ACINO_POLISH_WARP=0: one thread per point)
   bool list_polish = true;                         // polish only the listed points when the list is complete (ACINO_POLISH_LIST=0: all points first)
   // the sorted numbering (rebuilt by every solve from the masks)
   unsigned* hist = nullptr;                // [2^C][n_blocks] mask histogram -> exclusive scan

@@ -199,6 +199,7 @@ static int schur_alloc(acino_sba* h) {
   ACINO_CUDA(cudaMalloc(&s.act_cnt, sizeof(unsigned long long)));
   ACINO_CUDA(cudaMemset(s.act_cnt, 0, sizeof(unsigned long long)));
   { const char* env = getenv("ACINO_POLISH_LIST"); s.list_polish = !(env && env[0] == '0'); }
+  { const char* env = getenv("ACINO_POLISH_WARP"); s.warp_polish = !(env && env[0] == '0'); }
   ACINO_CUDA(cudaMallocHost(&s.h_lm, sizeof(SchurLm)));
   ACINO_CUDA(cudaMallocHost(&s.h_ring, SchurState::RING * sizeof(SchurLm)));
   for (int i = 0; i < SchurState::RING; ++i) ACINO_CUDA(cudaEventCreateWithFlags(&s.ring_ev[i], cudaEventDisableTiming));
@@ -621,9 +622,15 @@ static int schur_polish_points(acino_sba* h, const SchurParams& prm, int max_lau
       if (n_act > 0) {
         ACINO_CUDA(cudaMemsetAsync(h->counters, 0, 8 * sizeof(unsigned long long), h->stream));
         lp.inner_iters = 8 * max_launches;
-        LmPointsCtl ctl{nullptr, nullptr, nullptr, nullptr, s.act_list, (int)n_act, s.polish_list[0], cap};
-        DISPATCH_C(h->C, (lm_points_kernel<CC><<<grid_for((int64_t)n_act, 128), 128, 0, h->stream>>>(
-                             h->uv, h->mask, h->P, cams, X, h->lam, h->cost_p, h->status, lp, h->counters, ctl, nullptr)));
+        if (n_act <= 32768ull && s.warp_polish) {
+          // short lists: one warp per point (the launch lasts as long as its slowest point, a third as long this way)
+          DISPATCH_C(h->C, (lm_points_list_warp_kernel<CC><<<(unsigned)((n_act + 3) / 4), 128, 0, h->stream>>>(
+                               h->uv, h->mask, cams, X, h->lam, h->cost_p, h->status, lp, h->counters, s.act_list, (int)n_act)));
+        } else {
+          LmPointsCtl ctl{nullptr, nullptr, nullptr, nullptr, s.act_list, (int)n_act, s.polish_list[0], cap};
+          DISPATCH_C(h->C, (lm_points_kernel<CC><<<grid_for((int64_t)n_act, 128), 128, 0, h->stream>>>(
+                               h->uv, h->mask, h->P, cams, X, h->lam, h->cost_p, h->status, lp, h->counters, ctl, nullptr)));
+        }
         ACINO_CUDA(cudaGetLastError());
         ++s.launches;
       }
