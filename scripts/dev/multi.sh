@@ -8,7 +8,7 @@ if [ "$N" != "1" ]; then
 run 29601 bench.py --gpus $N --steps 20 --warmup 5 --no-c1 > gpurun_out/r02_bench_n$N.json 2> gpurun_out/r02_bench_n$N.err
 fi
 run 29602 bench.py --gpus $N --frames $((2000000/N)) --masked-frac 0.3 --outlier-frac 0.05 --strong-frames 2000000 --steps 10 --warmup 3 --no-c1 --no-cpu-baseline > gpurun_out/r02_bench_c5_n$N.json 2> gpurun_out/r02_bench_c5_n$N.err
-run 29603 scripts/tri_sweep.py > gpurun_out/r02_tri_sweep_c3_n$N.jsonl 2> gpurun_out/c3_n$N.err
+if [ -n "$WITH_C3" ]; then run 29603 scripts/tri_sweep.py > gpurun_out/r02_tri_sweep_c3_n$N.jsonl 2> gpurun_out/c3_n$N.err; fi
 tail -c 300 gpurun_out/r02_bench_c5_n$N.err
 python - <<PY
 import json
