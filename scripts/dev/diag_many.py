@@ -1,5 +1,5 @@
 import sys, os, time, json
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch, ctypes as ct
 from acinoset_b200 import synth, dense, sba, _capi
 sc = synth.make_rig_scene(119490, 20, seed=4, masked_frac=0.5)
