@@ -39,14 +39,25 @@ def _is_fisheye_triangulate(func):
 
 
 def _point_keys(frame, marker):
-    """(frame, marker) rows -> one int64 key per row whose order is the order of sorted (frame, marker-name), i.e. of
+    """(frame, marker) columns -> one int64 key per row whose order is the order of sorted (frame, marker-name), i.e. of
     groupby(['frame', 'marker']) at src/lib/utils.py:348, plus what is needed to map keys back. Integer arithmetic on
-    factorised columns instead of a MultiIndex of (int, str) tuples: 0.5 s instead of 19 s for the 7 M rows of config C4."""
-    m_codes, m_uniq = pd.factorize(np.asarray(marker, dtype=object), sort=True)
+    factorised columns instead of a MultiIndex of (int, str) tuples: 0.5 s instead of 19 s for the 7 M rows of config C4.
+    The marker column is factorised as the pandas column it is (an Arrow-backed string column is dictionary-encoded in
+    50 ms; as 7 M Python objects it took 0.5 s), and integer frames within a range comparable to the number of rows
+    are their own codes."""
+    m_codes, m_uniq = pd.factorize(marker, sort=True)
+    m_uniq = np.asarray(m_uniq, dtype=object)
     f_arr = np.asarray(frame)
+    if f_arr.dtype.kind in 'iu' and f_arr.size:
+        f_min, f_max = int(f_arr.min()), int(f_arr.max())
+        if f_max - f_min + 1 <= 8 * f_arr.size + 1024:
+            f_codes = f_arr.astype(np.int64) - f_min
+            f_uniq = np.arange(f_min, f_max + 1, dtype=f_arr.dtype)
+            n_m = max(len(m_uniq), 1)
+            return f_codes * n_m + m_codes.astype(np.int64), f_uniq, m_uniq, n_m
     f_codes, f_uniq = pd.factorize(f_arr, sort=True)
     n_m = max(len(m_uniq), 1)
-    return f_codes.astype(np.int64) * n_m + m_codes.astype(np.int64), f_uniq, np.asarray(m_uniq, dtype=object), n_m
+    return f_codes.astype(np.int64) * n_m + m_codes.astype(np.int64), f_uniq, m_uniq, n_m
 
 
 def df_to_dense(points_2d_df, n_cams, return_keys=False):
@@ -59,7 +70,7 @@ def df_to_dense(points_2d_df, n_cams, return_keys=False):
         out = (np.zeros((0, n_cams, 2)), np.zeros((0, n_cams), bool), np.zeros(0), np.zeros(0, dtype=object),
                np.zeros(0, dtype=np.int64))
         return out + (np.zeros(0, dtype=np.int64),) if return_keys else out
-    key, f_uniq, m_uniq, n_m = _point_keys(df['frame'].to_numpy(), df['marker'].to_numpy())
+    key, f_uniq, m_uniq, n_m = _point_keys(df['frame'].to_numpy(), df['marker'])
     # the keys are bounded by (frames x markers): a presence bitmap and its running count give the sorted unique keys
     # and every row's point id without a sort
     seen = np.zeros(len(f_uniq) * n_m, dtype=bool)
@@ -67,21 +78,20 @@ def df_to_dense(points_2d_df, n_cams, return_keys=False):
     uniq_keys = np.flatnonzero(seen)
     codes = (np.cumsum(seen, dtype=np.int64) - 1)[key]
     P = len(uniq_keys)
-    cam = df['camera'].to_numpy().astype(np.int64)
+    cam = df['camera'].to_numpy().astype(np.int64, copy=False)
     if cam.min() < 0 or cam.max() >= n_cams:
         raise ValueError('camera index outside the scene')
-    slot = codes.astype(np.int64) * n_cams + cam
+    slot = codes * n_cams + cam
     present = np.zeros(P * n_cams, dtype=bool)
     present[slot] = True
     if int(present.sum()) != slot.size:
         raise ValueError('duplicate (frame, marker, camera) rows: each camera may observe a point once')
     uv = np.zeros((P * n_cams, 2))
-    uv[slot, 0] = df['x'].to_numpy(dtype=np.float64)
-    uv[slot, 1] = df['y'].to_numpy(dtype=np.float64)
+    uv[slot] = np.column_stack((df['x'].to_numpy(dtype=np.float64), df['y'].to_numpy(dtype=np.float64)))      # one scatter of rows
     frames = np.asarray(f_uniq)[uniq_keys // n_m]
     markers = m_uniq[uniq_keys % n_m]
     out = (uv.reshape(P, n_cams, 2), present.reshape(P, n_cams), frames, markers, slot)
-    return out + (codes.astype(np.int64),) if return_keys else out
+    return out + (codes,) if return_keys else out
 
 
 def get_pairwise_3d_points_from_df(points_2d_df, k_arr, d_arr, r_arr, t_arr, triangulate_func, verbose=True):
