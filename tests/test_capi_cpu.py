@@ -143,3 +143,38 @@ def test_install_rebinds_only_names_the_reference_defines():
         defined = names_of(name)
         patched = {k for k in vars(m) if not k.startswith('__')}
         assert patched and patched <= defined, (name, patched - defined)
+
+
+def test_df_to_dense_key_paths_agree():
+    """utils._point_keys takes a short cut for integer frames in a compact range and factorises the marker column as the
+    pandas column it is; object-dtype markers, widely scattered frame numbers and float frames go the general way. All
+    must give the sorted (frame, marker-name) point order of groupby(['frame', 'marker']) (src/lib/utils.py:348)."""
+    rng = np.random.default_rng(5)
+    n = 4000
+    frames = rng.integers(10, 60, n)
+    markers = rng.choice(np.array(['nose', 'l_eye', 'tail1', 'spine', 'r_hip'], dtype=object), n)
+    cams = rng.integers(0, 6, n)
+    df = pd.DataFrame({'frame': frames, 'camera': cams, 'marker': markers, 'x': rng.normal(size=n), 'y': rng.normal(size=n)})
+    df = df.drop_duplicates(['frame', 'camera', 'marker']).reset_index(drop=True)
+    want_order = sorted(set(zip(df['frame'].tolist(), df['marker'].tolist())))
+    variants = {
+        'compact int frames': df,
+        'object markers': df.assign(marker=df['marker'].astype(object)),
+        'scattered frames': df.assign(frame=df['frame'] * 1_000_003),
+        'float frames': df.assign(frame=df['frame'].astype(np.float64)),
+    }
+    ref = None
+    for name, d in variants.items():
+        uv, present, f, m, slot, codes = utils.df_to_dense(d, 6, return_keys=True)
+        scale = 1_000_003 if name == 'scattered frames' else 1
+        got_order = list(zip((np.asarray(f) // scale).astype(int).tolist(), [str(x) for x in m]))
+        assert got_order == [(int(a), str(b)) for a, b in want_order], name
+        if ref is None:
+            ref = (uv, present, slot, codes)
+        else:
+            assert np.array_equal(uv, ref[0]) and np.array_equal(present, ref[1]), name
+            assert np.array_equal(slot, ref[2]) and np.array_equal(codes, ref[3]), name
+        # every row lands in the slot of its own (frame, marker, camera)
+        rows = np.arange(len(d))
+        assert np.array_equal(uv.reshape(-1, 2)[slot], d[['x', 'y']].to_numpy())
+        assert np.array_equal(slot // 6, codes) and np.array_equal(slot % 6, d['camera'].to_numpy())
