@@ -150,13 +150,15 @@ typedef struct {
   double ftol;             /* points+extrinsics: stop when an accepted step reduces the cost by <= ftol*cost */
   double hess_floor;       /* points+extrinsics: floor of the Gauss-Newton curvature weight relative to rho'
                               (rho' + 2 rho'' f^2 = rho' (1-z)/(1+z) is negative beyond |f| > C): 1.0 = plain IRLS weights */
-  double point_refine_iters; /* points+extrinsics: after every accepted step, this many per-point LM iterations with
-                                the cameras fixed (K3 on the current buffers; each point has its own damping) */
+  double point_refine_iters; /* points+extrinsics: from the second linearisation on, every point takes up to this many LM
+                                iterations of its own with the cameras fixed, inside the linearisation kernel (each point has
+                                its own damping, kept across iterations) */
   double point_refine_skip;  /* the refinement leaves a point alone when its model predicts a cost decrease
                               * <= point_refine_skip * max(cost of the point, f_scale^2/2); 0 = refine every point */
   double polish_tol;         /* points+extrinsics, acino_sba_solve: once an accepted step gains less than polish_tol
-                              * (relative), and again before ftol may end the solve, the points are solved to convergence
-                              * with the cameras fixed (K3 until no point is active); 0 = never */
+                              * (relative), and again before ftol may end the solve, the points whose own refinement ran
+                              * out of steps are solved to convergence with the cameras fixed (96 LM iterations each);
+                              * 0 = never */
   double lambda_dec;         /* points+extrinsics: the smallest factor by which an accepted step may shrink the damping
                               * (lambda <- lambda * max(lambda_dec, 1 - (2 rho - 1)^3)). Nielsen's rule is 1/3; the default
                               * 0.2 reaches the same stopping rule in about 10 % fewer iterations at a final cost a few
