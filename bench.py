@@ -604,6 +604,10 @@ def cpu_baseline(frames, mode, full_obs):
                         f'{what} {out["sba_seconds"]:.2f} s, {out["iterations"]} TRF iterations, '
                         f'{out["nfev"]} nfev, {out["cost_calls"]} cost-function sweeps; iterations/s scaled by observations '
                         f'({out["n_obs"]}/{int(full_obs)}) to the bench workload'),
+                cores_note=('the reference algorithm is one Python loop over the observations (cv2.fisheye.projectPoints per '
+                            'observation) inside one scipy.optimize.least_squares call, src/lib/sba.py:142-178: it uses one '
+                            'thread however many the host has, and the joint points+extrinsics problem cannot be split into '
+                            'independent processes'),
                 host_cpus=os.cpu_count(), sample_seconds=dt, sample_iters_per_s=its_per_s_sample,
                 us_per_obs_per_sweep=1e6 * out['sba_seconds'] / (out['cost_calls'] * out['n_obs']))
 
