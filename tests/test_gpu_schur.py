@@ -178,6 +178,41 @@ def test_polishing_reaches_the_same_minimum_in_fewer_iterations():
     s.close()
 
 
+def test_polish_paths_agree(monkeypatch):
+    """The three ways a polish can run - the points the linearisation listed by one warp per point (the default for short
+    lists), the same list by one thread per point (ACINO_POLISH_WARP=0), and a first pass over all points
+    (ACINO_POLISH_LIST=0, the path a list that overflowed takes) - are the same LM on the same objective: they end with
+    the same status, costs within 1e-8 relative of each other (the sums run in another order; which stragglers a pass
+    sees differs by a few points) and iteration counts within two. The switches are read when a handle is created."""
+    sc = synth.make_rig_scene(3000, 20, seed=21, outlier_frac=0.03)
+    k, d, r, t = sc['k'], sc['d'], sc['r'], sc['t']
+    xyz, exists, mask = dense.triangulate_ring(sc['uv'], sc['lik'], 0.5, k, d, r, t)
+    P, C = sc['lik'].shape
+    rng = np.random.default_rng(5)
+    rv = np.array([sba.rotation_matrix_to_rvec(m) for m in r]) + rng.normal(0, 8e-4, (C, 3))
+    tv = t.reshape(C, 3) + rng.normal(0, 3e-3, (C, 3))
+    sel = ((mask[:, None] >> np.arange(C)) & 1).astype(bool)
+    res = {}
+    for name, env in (('warp', {}), ('thread', {'ACINO_POLISH_WARP': '0'}), ('all', {'ACINO_POLISH_LIST': '0'})):
+        for key in ('ACINO_POLISH_WARP', 'ACINO_POLISH_LIST'):
+            monkeypatch.delenv(key, raising=False)
+        for key, v in env.items():
+            monkeypatch.setenv(key, v)
+        s = dense.SbaSolver(C, P)
+        s.set_observations(sc['uv'], mask)
+        s.set_cameras(k, d, r, t); s.set_rvec_t(rv, tv); s.set_points(np.nan_to_num(xyz))
+        st = s.solve(dense.default_opts(_capi.MODE_POINTS_AND_EXTRINSICS, ftol=1e-10, max_iter=400))
+        c = fe.cauchy_cost(s.residuals()[sel], 1.0)
+        assert abs(st['cost_final'] - c) <= 1e-9 * c, name           # the reported cost is the cost of what comes back
+        assert st['n_unconverged'] == 0, name
+        res[name] = st
+        s.close()
+    for name in ('thread', 'all'):
+        assert res[name]['status'] == res['warp']['status']
+        assert abs(res[name]['cost_final'] - res['warp']['cost_final']) <= 1e-8 * res['warp']['cost_final'], (name, res[name]['cost_final'], res['warp']['cost_final'])
+        assert abs(res[name]['iterations'] - res['warp']['iterations']) <= 2, name
+
+
 def test_board_calibration_ends_by_a_stopping_rule():
     """Config C2 in small: a checkerboard scene converges within a few tens of joint iterations, and the
     solve has to END there by one of scipy's rules. (Polishing used to reset the ftol / stall status each time it ran,
