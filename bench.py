@@ -384,7 +384,7 @@ def e2e_arm(args, ctx):
     # with the LM of solve i (ScenePipeline.run_many: two input buffers, two copy streams); the first solve is the warm-up and the clock runs from
     # its completion to the completion of the last, so every timed solve has its upload, triangulation, LM and
     # download inside the region.
-    n_seq = args.e2e_solves + 1
+    n_seq = max(1, args.e2e_solves) + 1      # at least one timed solve after the warm-up
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
