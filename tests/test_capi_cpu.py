@@ -178,3 +178,30 @@ def test_df_to_dense_key_paths_agree():
         rows = np.arange(len(d))
         assert np.array_equal(uv.reshape(-1, 2)[slot], d[['x', 'y']].to_numpy())
         assert np.array_equal(slot // 6, codes) and np.array_equal(slot % 6, d['camera'].to_numpy())
+
+
+def test_struct_mirrors_follow_the_header():
+    """The ctypes mirrors of acino_sba_opts / acino_sba_stats list the header's fields in the header's order with the
+    header's types (a field added on one side only would shift everything behind it silently)."""
+    import re
+    import ctypes as ct
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'include', 'acino_b200.h')).read()
+    ctype = {'int32_t': ct.c_int32, 'int64_t': ct.c_int64, 'double': ct.c_double}
+
+    def fields(struct_name):
+        end = hdr.index('} ' + struct_name + ';')
+        body = hdr[hdr.rindex('typedef struct {', 0, end) + len('typedef struct {'):end]
+        body = re.sub(r'/\*.*?\*/', '', body, flags=re.S)
+        out = []
+        for decl in body.split(';'):
+            decl = decl.strip()
+            if not decl:
+                continue
+            ty, names = decl.split(None, 1)
+            out += [(n.strip(), ctype[ty]) for n in names.split(',')]
+        return out
+
+    for struct_name, mirror in (('acino_sba_opts', _capi.SbaOpts), ('acino_sba_stats', _capi.SbaStats)):
+        want = fields(struct_name)
+        got = [(n, t) for n, t in mirror._fields_]
+        assert got == want, (struct_name, got, want)
